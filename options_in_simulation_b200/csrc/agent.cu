@@ -1,0 +1,512 @@
+// DDPG agent entry points: act = scaler -> actor MLP -> OU noise -> clamp;
+// update = scaler(train) x2 -> TD target -> critic step -> policy step -> Adam x2 -> polyak x2.
+// Reference: src/my_agents/ddpg.py:215-268 (act), :357-444 (_update); models
+// train/train_kamma_4d_nofifo_random_RLIL.py:21-52; skrl pieces restated in oracle/ref_harness/skrl_shim.py.
+#include <new>
+#include "agent.cuh"
+#include "mlp_fp32.cuh"
+
+namespace ois {
+
+// ------------------------------------------------------------------------------------------- layout
+MlpOffsets mlp_offsets(const OisMlpShape& s) {
+  MlpOffsets o;
+  const int dims[5] = {s.in_dim, s.h0, s.h1, s.h2, s.out_dim};
+  int64_t off = 0;
+  for (int l = 0; l < 4; ++l) {
+    o.w[l] = off;
+    off += (int64_t)dims[l + 1] * dims[l];
+    o.b[l] = off;
+    off += dims[l + 1];
+    o.in[l] = dims[l];
+    o.out[l] = dims[l + 1];
+  }
+  o.total = off;
+  return o;
+}
+
+// ------------------------------------------------------------------------------------------- kernels
+// RunningStandardScaler._compute without train: clamp((x - mean.float()) / (sqrt(var.float()) + eps), +-5)
+__global__ void scaler_apply_kernel(const float* __restrict__ x, float* __restrict__ y, int64_t n, int dim,
+                                    const double* __restrict__ mean, const double* __restrict__ var, int ldy) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n * dim) return;
+  const int64_t row = i / dim;
+  const int c = (int)(i - row * dim);
+  const float mu = (float)mean[c], sd = sqrtf((float)var[c]);
+  const float v = __fdiv_rn(__fsub_rn(x[i], mu), __fadd_rn(sd, 1e-8f));
+  y[row * ldy + c] = fminf(fmaxf(v, -5.0f), 5.0f);
+}
+
+// RunningStandardScaler(x, train=True) on a [B, dim] batch, one CTA: batch mean / unbiased variance
+// (torch.mean / torch.var are float32 results; we accumulate in fp64 and round once), parallel-variance
+// merge into the fp64 running statistics, then standardise with the UPDATED statistics.
+__global__ void __launch_bounds__(256)
+scaler_train_kernel(const float* __restrict__ x, float* __restrict__ y, int B, int dim, double* __restrict__ mean,
+                    double* __restrict__ var, double* __restrict__ count, int ldy) {
+  __shared__ double s_sum[8][16];
+  __shared__ float s_mu[16], s_sd[16];
+  __shared__ double s_bmean[16];
+  const int t = threadIdx.x, lane = t & 31, wp = t >> 5;
+  // pass 1: mean
+  for (int c = 0; c < dim; ++c) {
+    double a = 0.0;
+    for (int r = t; r < B; r += 256) a += (double)x[(size_t)r * dim + c];
+    for (int o = 16; o > 0; o >>= 1) a += __shfl_xor_sync(0xffffffffu, a, o);
+    if (lane == 0) s_sum[wp][c] = a;
+  }
+  __syncthreads();
+  if (t < dim) {
+    double a = 0.0;
+    for (int w = 0; w < 8; ++w) a += s_sum[w][t];
+    s_bmean[t] = a / (double)B;
+  }
+  __syncthreads();
+  // pass 2: centred sum of squares
+  for (int c = 0; c < dim; ++c) {
+    double a = 0.0;
+    const double mu = s_bmean[c];
+    for (int r = t; r < B; r += 256) { const double d = (double)x[(size_t)r * dim + c] - mu; a += d * d; }
+    for (int o = 16; o > 0; o >>= 1) a += __shfl_xor_sync(0xffffffffu, a, o);
+    if (lane == 0) s_sum[wp][c] = a;
+  }
+  __syncthreads();
+  if (t < dim) {
+    double m2 = 0.0;
+    for (int w = 0; w < 8; ++w) m2 += s_sum[w][t];
+    const double in_mean = (double)(float)s_bmean[t];                      // torch.mean -> float32
+    const double in_var = (double)(float)(m2 / (double)(B - 1));           // torch.var (unbiased) -> float32
+    const double cur = count[0];
+    const double tot = cur + (double)B;
+    const double delta = in_mean - mean[t];
+    const double M2 = var[t] * cur + in_var * (double)B + delta * delta * cur * (double)B / tot;
+    const double nm = mean[t] + delta * (double)B / tot;
+    const double nv = M2 / tot;
+    mean[t] = nm;
+    var[t] = nv;
+    s_mu[t] = (float)nm;
+    s_sd[t] = sqrtf((float)nv);
+  }
+  __syncthreads();
+  if (t == 0) count[0] += (double)B;   // every reader of count[0] is past the barrier above
+  for (int i = t; i < B * dim; i += 256) {
+    const int r = i / dim, c = i - r * dim;
+    const float v = __fdiv_rn(__fsub_rn(x[i], s_mu[c]), __fadd_rn(s_sd[c], 1e-8f));
+    y[(size_t)r * ldy + c] = fminf(fmaxf(v, -5.0f), 5.0f);
+  }
+}
+
+// copy [B, w] block into columns [col0, col0+w) of a wider row-major matrix
+__global__ void copy_cols_kernel(const float* __restrict__ src, int lds, float* __restrict__ dst, int ldd, int col0,
+                                 int B, int w) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= B * w) return;
+  const int r = i / w, c = i - r * w;
+  dst[(size_t)r * ldd + col0 + c] = src[(size_t)r * lds + c];
+}
+
+// target_values = rewards + discount * not(terminated | truncated) * target_q      ddpg.py:391-396
+__global__ void td_target_kernel(const float* __restrict__ r, const uint8_t* __restrict__ te,
+                                 const uint8_t* __restrict__ tr, const float* __restrict__ q2, float discount,
+                                 float* __restrict__ y, int B) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= B) return;
+  const float nd = (te[i] | tr[i]) ? 0.0f : 1.0f;
+  y[i] = __fadd_rn(r[i], __fmul_rn(__fmul_rn(discount, nd), q2[i]));
+}
+
+// critic loss = mean((q - y)^2), dq = 2 (q - y) / B; also target stats.   one CTA
+__global__ void __launch_bounds__(256)
+critic_loss_kernel(const float* __restrict__ q, const float* __restrict__ y, float* __restrict__ dq, int B,
+                   float* __restrict__ stats) {
+  __shared__ float s_sum[8], s_ysum[8], s_ymax[8], s_ymin[8];
+  const int t = threadIdx.x, lane = t & 31, wp = t >> 5;
+  float a = 0.f, ys = 0.f, ymx = -INFINITY, ymn = INFINITY;
+  for (int i = t; i < B; i += 256) {
+    const float d = q[i] - y[i];
+    a += d * d;
+    dq[i] = 2.0f * d / (float)B;
+    ys += y[i];
+    ymx = fmaxf(ymx, y[i]);
+    ymn = fminf(ymn, y[i]);
+  }
+  for (int o = 16; o > 0; o >>= 1) {
+    a += __shfl_xor_sync(0xffffffffu, a, o);
+    ys += __shfl_xor_sync(0xffffffffu, ys, o);
+    ymx = fmaxf(ymx, __shfl_xor_sync(0xffffffffu, ymx, o));
+    ymn = fminf(ymn, __shfl_xor_sync(0xffffffffu, ymn, o));
+  }
+  if (lane == 0) { s_sum[wp] = a; s_ysum[wp] = ys; s_ymax[wp] = ymx; s_ymin[wp] = ymn; }
+  __syncthreads();
+  if (t == 0 && stats) {
+    float A = 0.f, Y = 0.f, MX = -INFINITY, MN = INFINITY;
+    for (int w = 0; w < 8; ++w) { A += s_sum[w]; Y += s_ysum[w]; MX = fmaxf(MX, s_ymax[w]); MN = fminf(MN, s_ymin[w]); }
+    stats[0] = A / (float)B;
+    stats[5] = MX; stats[6] = MN; stats[7] = Y / (float)B;
+  }
+}
+
+// policy loss = -mean(q_pi), dq = -1/B; also Q stats.   one CTA
+__global__ void __launch_bounds__(256)
+policy_loss_kernel(const float* __restrict__ q, float* __restrict__ dq, int B, float* __restrict__ stats) {
+  __shared__ float s_sum[8], s_max[8], s_min[8];
+  const int t = threadIdx.x, lane = t & 31, wp = t >> 5;
+  float a = 0.f, mx = -INFINITY, mn = INFINITY;
+  for (int i = t; i < B; i += 256) {
+    a += q[i];
+    mx = fmaxf(mx, q[i]);
+    mn = fminf(mn, q[i]);
+    dq[i] = -1.0f / (float)B;
+  }
+  for (int o = 16; o > 0; o >>= 1) {
+    a += __shfl_xor_sync(0xffffffffu, a, o);
+    mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+    mn = fminf(mn, __shfl_xor_sync(0xffffffffu, mn, o));
+  }
+  if (lane == 0) { s_sum[wp] = a; s_max[wp] = mx; s_min[wp] = mn; }
+  __syncthreads();
+  if (t == 0 && stats) {
+    float A = 0.f, MX = -INFINITY, MN = INFINITY;
+    for (int w = 0; w < 8; ++w) { A += s_sum[w]; MX = fmaxf(MX, s_max[w]); MN = fminf(MN, s_min[w]); }
+    stats[1] = -A / (float)B;
+    stats[2] = MX; stats[3] = MN; stats[4] = A / (float)B;
+  }
+}
+
+// d(pre-activation) of the actor's output layer from d(action): sigmoid' = a (1 - a), tanh' = 1 - a^2
+__global__ void out_act_grad_kernel(const float* __restrict__ da, int ldda, int col0, const float* __restrict__ a,
+                                    float* __restrict__ dz, int B, int A, int act) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= B * A) return;
+  const int r = i / A, c = i - r * A;
+  const float g = da[(size_t)r * ldda + col0 + c], v = a[i];
+  dz[i] = act == OIS_ACT_SIGMOID ? g * v * (1.f - v) : act == OIS_ACT_TANH ? g * (1.f - v * v) : g;
+}
+
+// torch.optim.Adam (single-tensor formulas), flat buffers; g is scaled by grad_scale (1/world_size) first.
+// The step count may live on the device (CUDA-graph replay): bias corrections are then computed here.
+__global__ void __launch_bounds__(256)
+adam_kernel(float* __restrict__ p, float* __restrict__ m, float* __restrict__ v, const float* __restrict__ g, int64_t n,
+            float grad_scale, double lr, double beta1, double beta2, float eps, int64_t step_host,
+            const int64_t* __restrict__ step_dev) {
+  __shared__ float s_step_size, s_bc2_sqrt;
+  if (threadIdx.x == 0) {
+    const double t = (double)(step_dev ? step_dev[0] : step_host);
+    s_step_size = (float)(lr / (1.0 - pow(beta1, t)));
+    s_bc2_sqrt = (float)sqrt(1.0 - pow(beta2, t));
+  }
+  __syncthreads();
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const float w1 = (float)(1.0 - beta1), b2 = (float)beta2, w2 = (float)(1.0 - beta2);
+  const float gi = g[i] * grad_scale;
+  const float mi = m[i] + w1 * (gi - m[i]);            // exp_avg.lerp_(grad, 1 - beta1)
+  const float vi = v[i] * b2 + w2 * gi * gi;           // exp_avg_sq.mul_(beta2).addcmul_(grad, grad, 1 - beta2)
+  const float denom = sqrtf(vi) / s_bc2_sqrt + eps;
+  m[i] = mi;
+  v[i] = vi;
+  p[i] = p[i] - s_step_size * (mi / denom);            // param.addcdiv_(exp_avg, denom, value=-step_size)
+}
+
+// Model.update_parameters: p_t.mul_(1 - polyak); p_t.add_(polyak * p)
+__global__ void polyak_kernel(float* __restrict__ pt, const float* __restrict__ p, int64_t n, float tau) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  pt[i] = __fadd_rn(__fmul_rn(pt[i], 1.0f - tau), __fmul_rn(tau, p[i]));
+}
+
+__device__ __forceinline__ void atomic_max_f(float* addr, float v) {
+  if (v >= 0.f) atomicMax(reinterpret_cast<int*>(addr), __float_as_int(v));
+  else atomicMin(reinterpret_cast<unsigned int*>(addr), __float_as_uint(v));
+}
+__device__ __forceinline__ void atomic_min_f(float* addr, float v) {
+  if (v >= 0.f) atomicMin(reinterpret_cast<int*>(addr), __float_as_int(v));
+  else atomicMax(reinterpret_cast<unsigned int*>(addr), __float_as_uint(v));
+}
+
+// OrnsteinUhlenbeckNoise.sample + ddpg.py:247-255 (scale, add, clamp) or the random_timesteps branch :229-230
+__global__ void __launch_bounds__(256)
+explore_kernel(const __grid_constant__ OisActIO io, int64_t n, int A) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  float nz = 0.f;
+  bool have = false;
+  if (i < n * A) {
+    if (io.random_phase) {   // Uniform(low, high).sample(): rand * (high - low) + low
+      float u;
+      if (io.uniforms) u = io.uniforms[i];
+      else { const uint4 r = Philox(io.philox_seed)((uint64_t)(i >> 2), io.philox_offset * 2 + 1); u = u01(((const uint32_t*)&r)[i & 3]); }
+      io.actions[i] = __fadd_rn(__fmul_rn(u, __fsub_rn(io.clip_high, io.clip_low)), io.clip_low);
+    } else if (io.ou_state) {
+      float z;
+      if (io.normals) z = io.normals[i];
+      else {
+        const uint4 r = Philox(io.philox_seed)((uint64_t)(i >> 2), io.philox_offset * 2);
+        const float2 n01 = normal2(r.x, r.y), n23 = normal2(r.z, r.w);
+        const float zz[4] = {n01.x, n01.y, n23.x, n23.y};
+        z = zz[i & 3];
+      }
+      const float st = io.ou_state[i];
+      const float ns = __fadd_rn(st, __fadd_rn(__fmul_rn(-st, io.theta), __fmul_rn(io.sigma, z)));   // state += -state*theta + sigma*N
+      io.ou_state[i] = ns;
+      if (io.noise_scale >= 0.f) {
+        nz = __fmul_rn(__fmul_rn(io.base_scale, ns), io.noise_scale);
+        have = true;
+        const float a = __fadd_rn(io.actions[i], nz);
+        io.actions[i] = fminf(fmaxf(a, io.clip_low), io.clip_high);
+      }
+    }
+  }
+  if (io.noise_stats && !io.random_phase && io.ou_state && io.noise_scale >= 0.f) {
+    float mx = have ? nz : -INFINITY, mn = have ? nz : INFINITY, sm = have ? nz : 0.f;
+    for (int o = 16; o > 0; o >>= 1) {
+      mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+      mn = fminf(mn, __shfl_xor_sync(0xffffffffu, mn, o));
+      sm += __shfl_xor_sync(0xffffffffu, sm, o);
+    }
+    if ((threadIdx.x & 31) == 0 && mx != -INFINITY) {
+      atomic_max_f(io.noise_stats + 0, mx);
+      atomic_min_f(io.noise_stats + 1, mn);
+      atomicAdd(io.noise_stats + 2, sm);
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------------- host helpers
+static inline int eg(int64_t n, int t) { return (int)((n + t - 1) / t); }
+
+static int epi_for(int act) {
+  return act == OIS_ACT_SIGMOID ? EPI_BIAS_SIGMOID : act == OIS_ACT_TANH ? EPI_BIAS_TANH : EPI_BIAS;
+}
+
+// y = mlp(x), saving hidden activations in h[0..2]
+int mlp_forward_fp32(const OisMlpShape& sh, const float* P, const float* x, int ldx, float* h0, float* h1, float* h2,
+                     float* y, int64_t rows, cudaStream_t s) {
+  const MlpOffsets o = mlp_offsets(sh);
+  const int M = (int)rows;
+  if (int e = gemm_nt(x, P + o.w[0], h0, M, sh.h0, sh.in_dim, ldx, sh.in_dim, sh.h0, EPI_BIAS_ELU, P + o.b[0], nullptr, 0, s)) return e;
+  if (int e = gemm_nt(h0, P + o.w[1], h1, M, sh.h1, sh.h0, sh.h0, sh.h0, sh.h1, EPI_BIAS_ELU, P + o.b[1], nullptr, 0, s)) return e;
+  if (int e = gemm_nt(h1, P + o.w[2], h2, M, sh.h2, sh.h1, sh.h1, sh.h1, sh.h2, EPI_BIAS_ELU, P + o.b[2], nullptr, 0, s)) return e;
+  return gemm_nt(h2, P + o.w[3], y, M, sh.out_dim, sh.h2, sh.h2, sh.h2, sh.out_dim, epi_for(sh.out_act), P + o.b[3], nullptr, 0, s);
+}
+
+// backward of the MLP given dz3 = d(loss)/d(pre-activation of the last layer) [B, out].
+// G != null: parameter gradients are written (flat layout).  dx != null: d(loss)/d(input) [B, in].
+static int mlp_backward_fp32(const OisMlpShape& sh, const float* P, float* G, const float* x, int ldx, const float* h0,
+                             const float* h1, const float* h2, const float* dz3, float* d2, float* d1, float* d0,
+                             float* dx, int B, cudaStream_t s) {
+  const MlpOffsets o = mlp_offsets(sh);
+  if (G) {
+    if (int e = gemm_tn(dz3, h2, G + o.w[3], sh.out_dim, sh.h2, B, sh.out_dim, sh.h2, sh.h2, s)) return e;
+    if (int e = col_sum(dz3, G + o.b[3], B, sh.out_dim, sh.out_dim, s)) return e;
+  }
+  if (int e = gemm_nn(dz3, P + o.w[3], d2, B, sh.h2, sh.out_dim, sh.out_dim, sh.h2, sh.h2, EPI_ELU_GRAD, nullptr, h2, sh.h2, s)) return e;
+  if (G) {
+    if (int e = gemm_tn(d2, h1, G + o.w[2], sh.h2, sh.h1, B, sh.h2, sh.h1, sh.h1, s)) return e;
+    if (int e = col_sum(d2, G + o.b[2], B, sh.h2, sh.h2, s)) return e;
+  }
+  if (int e = gemm_nn(d2, P + o.w[2], d1, B, sh.h1, sh.h2, sh.h2, sh.h1, sh.h1, EPI_ELU_GRAD, nullptr, h1, sh.h1, s)) return e;
+  if (G) {
+    if (int e = gemm_tn(d1, h0, G + o.w[1], sh.h1, sh.h0, B, sh.h1, sh.h0, sh.h0, s)) return e;
+    if (int e = col_sum(d1, G + o.b[1], B, sh.h1, sh.h1, s)) return e;
+  }
+  if (int e = gemm_nn(d1, P + o.w[1], d0, B, sh.h0, sh.h1, sh.h1, sh.h0, sh.h0, EPI_ELU_GRAD, nullptr, h0, sh.h0, s)) return e;
+  if (G) {
+    if (int e = gemm_tn(d0, x, G + o.w[0], sh.h0, sh.in_dim, B, sh.h0, ldx, sh.in_dim, s)) return e;
+    if (int e = col_sum(d0, G + o.b[0], B, sh.h0, sh.h0, s)) return e;
+  }
+  if (dx) {
+    if (int e = gemm_nn(d0, P + o.w[0], dx, B, sh.in_dim, sh.h0, sh.h0, sh.in_dim, sh.in_dim, EPI_NONE, nullptr, nullptr, 0, s)) return e;
+  }
+  return OIS_OK;
+}
+
+static int adam_step(float* p, float* m, float* v, const float* g, int64_t n, float grad_scale, double lr, double b1,
+                     double b2, double eps, int64_t step, const int64_t* step_dev, cudaStream_t s) {
+  adam_kernel<<<eg(n, 256), 256, 0, s>>>(p, m, v, g, n, grad_scale, lr, b1, b2, (float)eps, step, step_dev);
+  OIS_CHECK_LAUNCH();
+  return OIS_OK;
+}
+
+}  // namespace ois
+
+using namespace ois;
+
+// ------------------------------------------------------------------------------------------- C ABI
+extern "C" int ois_agent_create(OisAgent** out, const OisMlpShape* actor, const OisMlpShape* critic, int64_t max_rows,
+                                int32_t batch_size, int32_t precision, void* stream) {
+  OIS_CHECK_ARG(out && actor && critic, "null argument");
+  OIS_CHECK_ARG(max_rows > 0 && batch_size > 0, "max_rows and batch_size must be positive");
+  OIS_CHECK_ARG(precision == OIS_PRECISION_FP32 || precision == OIS_PRECISION_BF16, "unknown precision");
+  OIS_CHECK_ARG(critic->in_dim == actor->in_dim + actor->out_dim, "critic input must be obs + act");
+  OIS_CHECK_ARG(critic->out_dim == 1, "critic output must be 1");
+  OIS_CHECK_ARG(actor->in_dim <= 16 && critic->in_dim <= 16 && actor->out_dim <= 8, "dims exceed the supported MLP family");
+  OisAgent* a = new (std::nothrow) OisAgent();
+  OIS_CHECK_ARG(a, "out of host memory");
+  a->actor = *actor;
+  a->critic = *critic;
+  a->max_rows = max_rows;
+  a->batch = batch_size;
+  a->precision = precision;
+  const int hmax0 = actor->h0 > critic->h0 ? actor->h0 : critic->h0;
+  const int hmax1 = actor->h1 > critic->h1 ? actor->h1 : critic->h1;
+  const int hmax2 = actor->h2 > critic->h2 ? actor->h2 : critic->h2;
+  const int64_t B = batch_size;
+  size_t bytes = 0;
+  auto take = [&](int64_t n) { size_t off = bytes; bytes += ((size_t)n * sizeof(float) + 255) / 256 * 256; return off; };
+  // update workspace (batch rows)
+  const size_t o_sn = take(B * actor->in_dim), o_s2n = take(B * actor->in_dim), o_x = take(B * critic->in_dim);
+  const size_t o_a = take(B * actor->out_dim), o_q = take(B), o_q2 = take(B), o_y = take(B), o_dq = take(B);
+  const size_t o_ah0 = take(B * hmax0), o_ah1 = take(B * hmax1), o_ah2 = take(B * hmax2);
+  const size_t o_ch0 = take(B * hmax0), o_ch1 = take(B * hmax1), o_ch2 = take(B * hmax2);
+  const size_t o_d0 = take(B * hmax0), o_d1 = take(B * hmax1), o_d2 = take(B * hmax2);
+  const size_t o_dx = take(B * critic->in_dim), o_dz = take(B * actor->out_dim);
+  // act workspace (fp32 path): normalised states + three activation buffers for max_rows rows
+  size_t o_xn = 0, o_h0 = 0, o_h1 = 0, o_h2 = 0;
+  o_xn = take(max_rows * actor->in_dim);
+  if (precision == OIS_PRECISION_FP32) {
+    o_h0 = take(max_rows * actor->h0);
+    o_h1 = take(max_rows * actor->h1);
+    o_h2 = take(max_rows * actor->h2);
+  }
+  cudaError_t ce = cudaMalloc(&a->ws, bytes);
+  if (ce != cudaSuccess) {
+    delete a;
+    set_error("ois_agent_create: cudaMalloc(%zu) -> %s", bytes, cudaGetErrorString(ce));
+    return OIS_ERR_CUDA;
+  }
+  a->ws_bytes = bytes;
+  char* base = (char*)a->ws;
+  auto at = [&](size_t off) { return (float*)(base + off); };
+  a->u_sn = at(o_sn); a->u_s2n = at(o_s2n); a->u_x = at(o_x); a->u_a = at(o_a); a->u_q = at(o_q); a->u_q2 = at(o_q2);
+  a->u_y = at(o_y); a->u_dq = at(o_dq);
+  a->ah0 = at(o_ah0); a->ah1 = at(o_ah1); a->ah2 = at(o_ah2);
+  a->ch0 = at(o_ch0); a->ch1 = at(o_ch1); a->ch2 = at(o_ch2);
+  a->d0 = at(o_d0); a->d1 = at(o_d1); a->d2 = at(o_d2); a->u_dx = at(o_dx); a->u_dz = at(o_dz);
+  a->xn = at(o_xn);
+  if (precision == OIS_PRECISION_FP32) { a->h0 = at(o_h0); a->h1 = at(o_h1); a->h2 = at(o_h2); }
+  if (precision == OIS_PRECISION_BF16) {
+    if (int e = tc_agent_init(a, (cudaStream_t)stream)) {
+      cudaFree(a->ws);
+      delete a;
+      return e;
+    }
+  }
+  *out = a;
+  return OIS_OK;
+}
+
+extern "C" int ois_agent_destroy(OisAgent* a) {
+  if (!a) return OIS_OK;
+  tc_agent_free(a);
+  if (a->ws) cudaFree(a->ws);
+  delete a;
+  return OIS_OK;
+}
+
+extern "C" int ois_mlp_forward(OisAgent* a, const OisMlpShape* shape, const float* params, const float* x, float* y,
+                               int64_t n_rows, void* stream) {
+  OIS_CHECK_ARG(a && shape && params && x && y, "null argument");
+  OIS_CHECK_ARG(n_rows >= 0 && n_rows <= a->max_rows, "n_rows exceeds the agent's max_rows");
+  OIS_CHECK_ARG(a->precision == OIS_PRECISION_FP32, "ois_mlp_forward is the fp32 path; use ois_agent_act for bf16");
+  OIS_CHECK_ARG(shape->h0 <= a->actor.h0 && shape->h1 <= a->actor.h1 && shape->h2 <= a->actor.h2, "hidden sizes exceed workspace");
+  if (n_rows == 0) return OIS_OK;
+  return mlp_forward_fp32(*shape, params, x, shape->in_dim, a->h0, a->h1, a->h2, y, n_rows, (cudaStream_t)stream);
+}
+
+extern "C" int ois_agent_act(OisAgent* a, const float* actor_params, const OisScaler* scaler, const OisActIO* io,
+                             int64_t n_rows, void* stream) {
+  OIS_CHECK_ARG(a && actor_params && io, "null argument");
+  OIS_CHECK_ARG(io->states && io->actions, "null states/actions");
+  OIS_CHECK_ARG(n_rows >= 0 && n_rows <= a->max_rows, "n_rows exceeds the agent's max_rows");
+  if (n_rows == 0) return OIS_OK;
+  cudaStream_t s = (cudaStream_t)stream;
+  const int A = a->actor.out_dim, D = a->actor.in_dim;
+  if (!io->random_phase) {
+    if (a->precision == OIS_PRECISION_BF16) {
+      if (int e = tc_actor_forward(a, actor_params, scaler, io->states, io->actions, n_rows, s)) return e;
+    } else {
+      const float* x = io->states;
+      if (scaler && scaler->running_mean) {
+        scaler_apply_kernel<<<eg(n_rows * D, 256), 256, 0, s>>>(io->states, a->xn, n_rows, D, scaler->running_mean,
+                                                               scaler->running_variance, D);
+        OIS_CHECK_LAUNCH();
+        x = a->xn;
+      }
+      if (int e = mlp_forward_fp32(a->actor, actor_params, x, D, a->h0, a->h1, a->h2, io->actions, n_rows, s)) return e;
+    }
+  }
+  if (io->random_phase || io->ou_state) {
+    explore_kernel<<<eg(n_rows * A, 256), 256, 0, s>>>(*io, n_rows, A);
+    OIS_CHECK_LAUNCH();
+  }
+  return OIS_OK;
+}
+
+extern "C" int ois_ddpg_update_phase(OisAgent* a, const OisScaler* scaler, const OisUpdateIO* io, int32_t phase,
+                                     float grad_scale, void* stream) {
+  OIS_CHECK_ARG(a && io, "null argument");
+  OIS_CHECK_ARG(phase >= 0 && phase <= 2, "phase must be 0, 1 or 2");
+  OIS_CHECK_ARG(io->actor && io->actor_target && io->critic && io->critic_target, "null parameter buffer");
+  OIS_CHECK_ARG(io->actor_grad && io->critic_grad && io->actor_m && io->actor_v && io->critic_m && io->critic_v,
+                "null optimizer buffer");
+  cudaStream_t s = (cudaStream_t)stream;
+  const int B = a->batch, D = a->actor.in_dim, A = a->actor.out_dim, CI = a->critic.in_dim;
+  const MlpOffsets oa = mlp_offsets(a->actor), oc = mlp_offsets(a->critic);
+  if (phase == 0) {
+    OIS_CHECK_ARG(io->states && io->actions && io->rewards && io->next_states && io->terminated && io->truncated,
+                  "null batch tensor");
+    // ddpg.py:381-382  scaler(train=True) on states, then on next_states
+    if (scaler && scaler->running_mean) {
+      scaler_train_kernel<<<1, 256, 0, s>>>(io->states, a->u_sn, B, D, scaler->running_mean, scaler->running_variance,
+                                            scaler->current_count, D);
+      scaler_train_kernel<<<1, 256, 0, s>>>(io->next_states, a->u_s2n, B, D, scaler->running_mean,
+                                            scaler->running_variance, scaler->current_count, D);
+      OIS_CHECK_LAUNCH();
+    } else {
+      OIS_CHECK_CUDA(cudaMemcpyAsync(a->u_sn, io->states, sizeof(float) * B * D, cudaMemcpyDeviceToDevice, s));
+      OIS_CHECK_CUDA(cudaMemcpyAsync(a->u_s2n, io->next_states, sizeof(float) * B * D, cudaMemcpyDeviceToDevice, s));
+    }
+    // ddpg.py:385-396  target actor / target critic / TD target
+    if (int e = mlp_forward_fp32(a->actor, io->actor_target, a->u_s2n, D, a->ah0, a->ah1, a->ah2, a->u_a, B, s)) return e;
+    copy_cols_kernel<<<eg(B * D, 256), 256, 0, s>>>(a->u_s2n, D, a->u_x, CI, 0, B, D);
+    copy_cols_kernel<<<eg(B * A, 256), 256, 0, s>>>(a->u_a, A, a->u_x, CI, D, B, A);
+    if (int e = mlp_forward_fp32(a->critic, io->critic_target, a->u_x, CI, a->ch0, a->ch1, a->ch2, a->u_q2, B, s)) return e;
+    td_target_kernel<<<eg(B, 256), 256, 0, s>>>(io->rewards, io->terminated, io->truncated, a->u_q2, io->discount, a->u_y, B);
+    // ddpg.py:399-407  critic forward, MSE, backward
+    copy_cols_kernel<<<eg(B * D, 256), 256, 0, s>>>(a->u_sn, D, a->u_x, CI, 0, B, D);
+    copy_cols_kernel<<<eg(B * A, 256), 256, 0, s>>>(io->actions, A, a->u_x, CI, D, B, A);
+    if (int e = mlp_forward_fp32(a->critic, io->critic, a->u_x, CI, a->ch0, a->ch1, a->ch2, a->u_q, B, s)) return e;
+    critic_loss_kernel<<<1, 256, 0, s>>>(a->u_q, a->u_y, a->u_dq, B, io->stats);
+    OIS_CHECK_LAUNCH();
+    return mlp_backward_fp32(a->critic, io->critic, io->critic_grad, a->u_x, CI, a->ch0, a->ch1, a->ch2, a->u_dq, a->d2,
+                             a->d1, a->d0, nullptr, B, s);
+  }
+  if (phase == 1) {
+    // ddpg.py:416  critic optimizer step
+    if (int e = adam_step(io->critic, io->critic_m, io->critic_v, io->critic_grad, oc.total, grad_scale, io->critic_lr,
+                          io->beta1, io->beta2, io->adam_eps, io->adam_step, io->adam_step_dev, s)) return e;
+    // ddpg.py:420-429  policy loss through the (updated) critic
+    if (int e = mlp_forward_fp32(a->actor, io->actor, a->u_sn, D, a->ah0, a->ah1, a->ah2, a->u_a, B, s)) return e;
+    copy_cols_kernel<<<eg(B * D, 256), 256, 0, s>>>(a->u_sn, D, a->u_x, CI, 0, B, D);
+    copy_cols_kernel<<<eg(B * A, 256), 256, 0, s>>>(a->u_a, A, a->u_x, CI, D, B, A);
+    if (int e = mlp_forward_fp32(a->critic, io->critic, a->u_x, CI, a->ch0, a->ch1, a->ch2, a->u_q, B, s)) return e;
+    policy_loss_kernel<<<1, 256, 0, s>>>(a->u_q, a->u_dq, B, io->stats);
+    OIS_CHECK_LAUNCH();
+    // dgrad only through the critic (its parameter gradients from this pass are discarded by the reference at
+    // the next critic_optimizer.zero_grad(), ddpg.py:406), then the actor's full backward
+    if (int e = mlp_backward_fp32(a->critic, io->critic, nullptr, a->u_x, CI, a->ch0, a->ch1, a->ch2, a->u_dq, a->d2, a->d1,
+                                  a->d0, a->u_dx, B, s)) return e;
+    out_act_grad_kernel<<<eg(B * A, 256), 256, 0, s>>>(a->u_dx, CI, D, a->u_a, a->u_dz, B, A, a->actor.out_act);
+    OIS_CHECK_LAUNCH();
+    return mlp_backward_fp32(a->actor, io->actor, io->actor_grad, a->u_sn, D, a->ah0, a->ah1, a->ah2, a->u_dz, a->d2, a->d1,
+                             a->d0, nullptr, B, s);
+  }
+  // phase 2: ddpg.py:438 actor optimizer step, :443-444 polyak
+  if (int e = adam_step(io->actor, io->actor_m, io->actor_v, io->actor_grad, oa.total, grad_scale, io->actor_lr, io->beta1,
+                        io->beta2, io->adam_eps, io->adam_step, io->adam_step_dev, s)) return e;
+  polyak_kernel<<<eg(oa.total, 256), 256, 0, s>>>(io->actor_target, io->actor, oa.total, io->polyak);
+  polyak_kernel<<<eg(oc.total, 256), 256, 0, s>>>(io->critic_target, io->critic, oc.total, io->polyak);
+  OIS_CHECK_LAUNCH();
+  if (a->precision == OIS_PRECISION_BF16) tc_invalidate_weights(a);
+  return OIS_OK;
+}

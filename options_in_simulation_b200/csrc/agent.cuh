@@ -1,0 +1,41 @@
+// Internal agent handle shared by agent.cu (fp32 path, update) and mlp_tc.cu (bf16 tcgen05 path).
+#pragma once
+#include "ois_common.cuh"
+
+struct OisAgent {
+  OisMlpShape actor, critic;
+  int64_t max_rows = 0;
+  int batch = 0;
+  int precision = 0;
+  void* ws = nullptr;
+  size_t ws_bytes = 0;
+  // update workspace (batch rows)
+  float *u_sn = nullptr, *u_s2n = nullptr, *u_x = nullptr, *u_a = nullptr, *u_q = nullptr, *u_q2 = nullptr;
+  float *u_y = nullptr, *u_dq = nullptr, *u_dx = nullptr, *u_dz = nullptr;
+  float *ah0 = nullptr, *ah1 = nullptr, *ah2 = nullptr, *ch0 = nullptr, *ch1 = nullptr, *ch2 = nullptr;
+  float *d0 = nullptr, *d1 = nullptr, *d2 = nullptr;
+  // act workspace
+  float *xn = nullptr, *h0 = nullptr, *h1 = nullptr, *h2 = nullptr;
+  // bf16 tensor-core path (mlp_tc.cu)
+  void* tc = nullptr;
+};
+
+namespace ois {
+
+struct MlpOffsets {
+  int64_t w[4], b[4], total;
+  int in[4], out[4];
+};
+MlpOffsets mlp_offsets(const OisMlpShape& s);
+
+int mlp_forward_fp32(const OisMlpShape& sh, const float* P, const float* x, int ldx, float* h0, float* h1, float* h2,
+                     float* y, int64_t rows, cudaStream_t s);
+
+// bf16 tcgen05 + TMA fused actor (mlp_tc.cu)
+int tc_agent_init(OisAgent* a, cudaStream_t s);
+void tc_agent_free(OisAgent* a);
+void tc_invalidate_weights(OisAgent* a);
+int tc_actor_forward(OisAgent* a, const float* actor_params, const OisScaler* scaler, const float* states,
+                     float* actions, int64_t rows, cudaStream_t s);
+
+}  // namespace ois

@@ -1,0 +1,528 @@
+// Fused environment step for TorqueDistributionTask.
+//
+// One thread per env; every state field is a [N,4] float array so each access is one coalesced 16-byte
+// load/store (512 contiguous bytes per warp instruction); int64 counters are 8-byte accesses.  The ten
+// physics sub-steps run in registers: state makes exactly one HBM round trip per policy step.
+//
+// Arithmetic contract
+//   * the reference's tensor math (pre_physics_step / is_done / calculate_metrics / reset_idx /
+//     get_observations) is evaluated op by op in the reference's order with non-contracting intrinsics
+//     (__fmul_rn, __fadd_rn, __fdiv_rn ...), so it is bit-identical to CPU torch / the numpy oracle;
+//   * the skid-steer sub-steps (no reference code exists: PhysX) use FMA contraction and MUFU
+//     reciprocals; they are held to <= 1e-6 of the float64 twin (oracle/dynamics_twin.py).
+#include "ois_common.cuh"
+
+namespace ois {
+
+__device__ __forceinline__ float mul(float a, float b) { return __fmul_rn(a, b); }
+__device__ __forceinline__ float add(float a, float b) { return __fadd_rn(a, b); }
+__device__ __forceinline__ float sub(float a, float b) { return __fsub_rn(a, b); }
+__device__ __forceinline__ float dvd(float a, float b) { return __fdiv_rn(a, b); }
+__device__ __forceinline__ float clipf(float x, float lo, float hi) { return fminf(fmaxf(x, lo), hi); }
+
+// torch.clamp(1.0 - (sim_steps.float() / max_sim_steps), min=0.0)   KAMMA_medium.py:627-628
+__device__ __forceinline__ float gamma_assist(int mode, float constant, int64_t sim_steps, float max_sim_steps) {
+  if (mode == OIS_GAMMA_DECAY) return fmaxf(sub(1.0f, dvd((float)sim_steps, max_sim_steps)), 0.0f);
+  return constant;
+}
+
+struct Skid {
+  float px, py, yaw, vx, vy, r;
+  float w[4];
+};
+
+// ---------------------------------------------------------------------------------------------
+// `decimation` linearly-implicit sub-steps of the planar skid-steer model under constant torques.
+// Equations: oracle/dynamics_twin.py (increment form).  Wheel order fl, rl, fr, rr:
+// x = (+a, -a, +a, -a), y = (+b, +b, -b, -b).
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ void skid_steps(Skid& s, const float tau[4], const OisEnvParams& p) {
+  const float h = p.sim_dt, R = p.wheel_radius, c = p.wheel_damping;
+  const float a = p.half_wheelbase, b = p.half_track;
+  const float m = p.mass;
+  const float m_h = m / h, J_h = p.yaw_inertia / h, Iw_h = p.wheel_inertia / h + c;
+  const float eps2 = p.slip_eps * p.slip_eps, R2 = R * R, aa = a * a, bb = b * b;
+  const float wmax = p.wheel_speed_max;
+  float sn, cs;
+  sincosf(s.yaw, &sn, &cs);
+#pragma unroll 1
+  for (int it = 0; it < p.decimation; ++it) {
+    const float vx = s.vx, vy = s.vy, r = s.r;
+    const float uL = vx - r * b, uR = vx + r * b;   // contact longitudinal speed, left (y=+b) / right (y=-b)
+    const float lF = vy + r * a, lB = vy - r * a;   // contact lateral speed, front (x=+a) / rear (x=-a)
+    float A00 = m_h, A11 = m_h, A22 = J_h, A02 = 0.f, A12 = 0.f;
+    float b0 = m * (r * vy), b1 = -(m * (r * vx)), b2 = 0.f;
+    float al[4], be[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const float xi = (i & 1) ? -a : a;
+      const float yi = (i & 2) ? -b : b;
+      const float u = (i & 2) ? uR : uL;
+      const float l = (i & 1) ? lB : lF;
+      const float sx = R * s.w[i] - u;
+      const float k = p.mu_n * rsqrtf(sx * sx + l * l + eps2);
+      const float invE = __frcp_rn(Iw_h + R2 * k);
+      const float Rk = R * k;
+      al[i] = (tau[i] - c * s.w[i] - Rk * sx) * invE;
+      be[i] = Rk * invE;
+      const float g = k * Iw_h * invE;
+      const float phi = k * (sx + R * al[i]);
+      const float kl = k * l;
+      A00 += g;
+      A11 += k;
+      A22 += aa * k + bb * g;
+      A02 -= yi * g;
+      A12 += xi * k;
+      b0 += phi;
+      b1 -= kl;
+      b2 -= xi * kl + yi * phi;
+    }
+    const float i00 = __frcp_rn(A00), i11 = __frcp_rn(A11);
+    const float s22 = A22 - A02 * A02 * i00 - A12 * A12 * i11;
+    const float dr = (b2 - A02 * b0 * i00 - A12 * b1 * i11) * __frcp_rn(s22);
+    const float dvx = (b0 - A02 * dr) * i00;
+    const float dvy = (b1 - A12 * dr) * i11;
+    s.vx = vx + dvx;
+    s.vy = vy + dvy;
+    s.r = r + dr;
+    const float duL = dvx - dr * b, duR = dvx + dr * b;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) s.w[i] = clipf(s.w[i] + (al[i] + be[i] * ((i & 2) ? duR : duL)), -wmax, wmax);
+    // heading: rotate (cos, sin) by d = h*r' with a Taylor pair (|d| < 0.7 always: |r'| <= wheel slip limits)
+    const float d = h * s.r, d2 = d * d;
+    const float sd = d * (1.f + d2 * (-1.f / 6.f + d2 * (1.f / 120.f + d2 * (-1.f / 5040.f + d2 * (1.f / 362880.f)))));
+    const float cd = 1.f + d2 * (-0.5f + d2 * (1.f / 24.f + d2 * (-1.f / 720.f + d2 * (1.f / 40320.f))));
+    const float cn = cs * cd - sn * sd;
+    sn = sn * cd + cs * sd;
+    cs = cn;
+    s.yaw += d;
+    s.px += h * (s.vx * cs - s.vy * sn);
+    s.py += h * (s.vx * sn + s.vy * cs);
+  }
+}
+
+// warp-level sum
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+
+// reset_idx draws in reference order: pos x, pos y, angle, cmd x, cmd y, heading, loop x  (KAMMA_medium.py:424-456,571)
+struct ResetDraws {
+  float u[7];
+};
+
+__device__ __forceinline__ void apply_reset(const OisEnvParams& p, const ResetDraws& d, int64_t sim_after, Skid& s,
+                                            float4& cmd) {
+  // pose: base_init_state pos (0,0) + U(-0.5,0.5)^2 ; yaw = U(0, 2*pi)   KAMMA_medium.py:422-434
+  s.px = add(0.0f, add(mul(1.0f, d.u[0]), -0.5f));
+  s.py = add(0.0f, add(mul(1.0f, d.u[1]), -0.5f));
+  s.yaw = add(mul(6.2831855f, d.u[2]), 0.0f);
+  s.vx = 0.f; s.vy = 0.f; s.r = 0.f;                                     // :435-446
+  s.w[0] = s.w[1] = s.w[2] = s.w[3] = 0.f;
+  // commands :448-460
+  const float cx = add(mul(p.x_range, d.u[3]), p.x_lo);
+  const float cy = add(mul(p.y_range, d.u[4]), p.y_lo);
+  const float ch = add(mul(p.h_range, d.u[5]), p.h_lo);
+  const float keep = sqrtf(add(mul(cx, cx), mul(cy, cy))) > 0.25f ? 1.0f : 0.0f;
+  cmd.y = mul(cy, keep);
+  cmd.w = mul(ch, keep);
+  // per-env command via sample_velocity_command :490-496
+  float x;
+  if (p.command_mode == OIS_CMD_RAND) {            // :569-575
+    x = add(mul(p.x_range, d.u[6]), p.x_lo);
+  } else if (p.command_mode == OIS_CMD_GV) {       // KAMMA_curr1.py:577-599, per-env progress
+    const float progress = fminf(1.0f, dvd((float)sim_after, p.max_sim_steps));
+    const float factor = add(0.1f, mul(0.9f, progress));
+    const float c = (float)(((double)p.x_lo + (double)p.x_hi) / 2.0);
+    const float xmin = sub(c, mul((float)((double)c - (double)p.x_lo), factor));
+    const float xmax = add(c, mul((float)((double)p.x_hi - (double)c), factor));
+    x = add(mul(sub(xmax, xmin), d.u[6]), xmin);
+  } else {                                          // KAMMA_eval.py:545-550
+    const float progress = clipf(dvd((float)sim_after, p.max_sim_steps), 0.0f, 1.0f);
+    x = add(1.0f, mul(progress, 1.0f));
+  }
+  cmd.x = fmaxf(x, 0.0f);
+  cmd.z = 0.0f;
+}
+
+__device__ __forceinline__ ResetDraws philox_reset_draws(uint64_t seed, uint64_t offset, int64_t env, uint4 first) {
+  ResetDraws d;
+  const uint4 second = Philox(seed)((uint64_t)env, offset * 4 + 1);
+  d.u[0] = u01(first.y); d.u[1] = u01(first.z); d.u[2] = u01(first.w);
+  d.u[3] = u01(second.x); d.u[4] = u01(second.y); d.u[5] = u01(second.z); d.u[6] = u01(second.w);
+  return d;
+}
+
+constexpr int kEnvThreads = 128;
+
+__global__ void __launch_bounds__(kEnvThreads)
+env_step_kernel(const __grid_constant__ OisEnvParams p, const __grid_constant__ OisEnvState st,
+                const __grid_constant__ OisEnvIO io, const int64_t n) {
+  __shared__ float s_stats[OIS_EP_STATS_LEN];
+  const bool want_stats = io.ep_stats != nullptr;
+  if (want_stats) {
+    if (threadIdx.x < OIS_EP_STATS_LEN) s_stats[threadIdx.x] = 0.f;
+    __syncthreads();
+  }
+  float acc[OIS_EP_STATS_LEN];
+  if (want_stats) {
+#pragma unroll
+    for (int k = 0; k < OIS_EP_STATS_LEN; ++k) acc[k] = 0.f;
+  }
+  int any_reset_local = 0;
+  const bool eval = p.eval_sums != 0;
+  const bool zero_old = eval && io.any_reset_flags != nullptr && io.any_reset_flags[io.flag_slot] != 0;
+
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    // ------------------------------------------------------------------ loads (all independent, issued up front)
+    const float4 pv = ld_stream4(st.pose_vx + 4 * i);
+    const float4 tp = ld_stream4(st.twist_prev + 4 * i);
+    const float4 wv = ld_stream4(st.wheel_speed + 4 * i);
+    float4 cmd = ld_stream4(st.commands + 4 * i);
+    float4 sa = ld_stream4(st.sums_a + 4 * i);
+    float4 sb = ld_stream4(st.sums_b + 4 * i);
+    int64_t sim = __ldcs(st.sim_steps + i);
+    int64_t eb = __ldcs(st.episode_buf + i);
+    float4 se = make_float4(0.f, 0.f, 0.f, 0.f), ot = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (eval) {
+      se = ld_stream4(st.sums_eval + 4 * i);
+      ot = ld_stream4(st.old_torques + 4 * i);
+      if (zero_old) ot = make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+    float a4[4];
+    if (p.act_dim == 4) {             // KAMMA_medium.py:600
+      const float4 a = __ldcs(reinterpret_cast<const float4*>(io.actions) + i);
+      a4[0] = a.x; a4[1] = a.y; a4[2] = a.z; a4[3] = a.w;
+    } else if (p.act_dim == 2) {      // KA_DDPG_2D.py:624  [a0, a0, a1, a1]
+      const float2 a = __ldcs(reinterpret_cast<const float2*>(io.actions) + i);
+      a4[0] = a.x; a4[1] = a.x; a4[2] = a.y; a4[3] = a.y;
+    } else {                          // KA_DDPG_1D.py:600  repeat(1, 4)
+      const float a = __ldcs(io.actions + i);
+      a4[0] = a4[1] = a4[2] = a4[3] = a;
+    }
+    float prev_obs[6];
+    const bool replay = io.replay_states != nullptr;
+    if (replay) {
+      const float2* o = reinterpret_cast<const float2*>(io.obs + 6 * i);
+      const float2 o0 = o[0], o1 = o[1], o2 = o[2];
+      prev_obs[0] = o0.x; prev_obs[1] = o0.y; prev_obs[2] = o1.x; prev_obs[3] = o1.y; prev_obs[4] = o2.x; prev_obs[5] = o2.y;
+    }
+    uint4 ph = make_uint4(0, 0, 0, 0);
+    const bool need_philox = (p.blend == OIS_BLEND_SWITCH && io.rand_mask == nullptr) || io.reset_uniforms == nullptr;
+    if (need_philox) ph = Philox(io.philox_seed)((uint64_t)i, io.philox_offset * 4);
+
+    // ------------------------------------------------------------------ pre_physics_step :604-636
+    const float desired_v = cmd.x, desired_w = cmd.z;
+    const float current_v = pv.w, current_w = tp.y;
+    const float v_delta = sub(desired_v, current_v);
+    const float omega_delta = sub(desired_w, current_w);
+    const float lin = mul(p.kp, mul(p.vehicle_mass, dvd(v_delta, p.dt)));
+    const float ang = mul(p.kp_omega, mul(p.vehicle_inertia, dvd(omega_delta, p.dt)));
+    const float ac_left = sub(lin, ang), ac_right = add(lin, ang);
+    const float crit[4] = {ac_left, ac_left, ac_right, ac_right};
+    const float g1 = gamma_assist(p.gamma1_mode, p.gamma1_const, sim, p.max_sim_steps);
+    const float g2 = gamma_assist(p.gamma2_mode, p.gamma2_const, sim, p.max_sim_steps);
+    float tq[4], wt[4];
+    if (p.blend == OIS_BLEND_SWITCH) {          // :632-636
+      const float rm = io.rand_mask ? __ldcs(io.rand_mask + i) : u01(ph.x);
+      const float mask = rm < g1 ? 1.0f : 0.0f;
+      const float nmask = sub(1.0f, mask);
+#pragma unroll
+      for (int j = 0; j < 4; ++j) tq[j] = add(mul(mask, crit[j]), mul(nmask, mul(a4[j], p.action_scale)));
+    } else {                                    // KA_DDPG_1D.py:632-633
+      const float ng = sub(1.0f, g1);
+#pragma unroll
+      for (int j = 0; j < 4; ++j) tq[j] = add(mul(mul(ng, a4[j]), p.action_scale), mul(g1, crit[j]));
+    }
+    float guiding = 0.f;
+    if (!p.guiding_post_clip) {                 // KA_DDPG_1D.py:642
+      float acc2 = 0.f;
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const float d = sub(mul(a4[j], p.action_scale), crit[j]);
+        acc2 = j == 0 ? mul(d, d) : add(acc2, mul(d, d));
+      }
+      guiding = -sqrtf(acc2);
+    }
+#pragma unroll
+    for (int j = 0; j < 4; ++j) wt[j] = clipf(tq[j], -p.torque_clip, p.torque_clip);   // :649
+
+    // ------------------------------------------------------------------ physics :646-653 (replaces PhysX)
+    Skid s;
+    s.px = pv.x; s.py = pv.y; s.yaw = pv.z; s.vx = pv.w; s.vy = tp.x; s.r = tp.y;
+    s.w[0] = wv.x; s.w[1] = wv.y; s.w[2] = wv.z; s.w[3] = wv.w;
+    if (p.physics) skid_steps(s, wt, p);
+
+    if (p.guiding_post_clip) {                  // :656
+      float acc2 = 0.f;
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const float d = sub(wt[j], crit[j]);
+        acc2 = j == 0 ? mul(d, d) : add(acc2, mul(d, d));
+      }
+      guiding = -sqrtf(acc2);
+    }
+    if (eval) {                                 // KAMMA_eval.py:677-685
+      const float d0 = sub(ot.x, wt[0]), d1 = sub(ot.y, wt[1]), d2 = sub(ot.z, wt[2]), d3 = sub(ot.w, wt[3]);
+      const float ss = add(add(add(mul(d0, d0), mul(d1, d1)), mul(d2, d2)), mul(d3, d3));
+      se.x = add(se.x, dvd(ss, 10.0f));
+      se.z = add(se.z, dvd(desired_v, 10.0f));
+      ot = make_float4(wt[0], wt[1], wt[2], wt[3]);
+    }
+
+    // ------------------------------------------------------------------ post_physics_step :675-676
+    eb += 1;
+    sim += 1;
+    // is_done :736-760 (has_fallen is identically false for the planar model; env origins are zero :224)
+    const bool timeout = eb >= (int64_t)(p.max_episode_length - 1);
+    const bool oob = (s.px < -p.bound) | (s.px > p.bound) | (s.py < -p.bound) | (s.py > p.bound);
+    const bool reset = timeout | oob;
+
+    // calculate_metrics :767-810 (linear_acc lags a step: it uses the pre-physics projection)
+    const float lin_acc = dvd(sub(current_v, tp.z), p.dt);
+    const float ang_acc = dvd(sub(s.r, tp.w), p.dt);
+    const float prev_lin = current_v, prev_ang = s.r;
+    const float r1 = add(mul(v_delta, v_delta), mul(5.0f, mul(omega_delta, omega_delta)));
+    const float r2 = add(mul(lin_acc, lin_acc), mul(ang_acc, ang_acc));
+    const float r3 = add(add(add(mul(wt[0], wt[0]), mul(wt[1], wt[1])), mul(wt[2], wt[2])), mul(wt[3], wt[3]));
+    const float c1 = mul(-25.0f, r1), c2 = mul(-0.02f, r2), c3 = mul(-0.09f, r3);
+    const float rdense = add(add(c1, c2), c3);
+    const float sparse = (fabsf(v_delta) < 0.01f && fabsf(omega_delta) < 0.01f) ? 0.2f : 0.0f;
+    const float observed = add(rdense, sparse);
+    const float rew = add(mul(sub(1.0f, g2), observed), mul(g2, guiding));
+    sa.x = add(sa.x, c1); sa.y = add(sa.y, c2); sa.z = add(sa.z, c3); sa.w = add(sa.w, rdense);
+    sb.x = add(sb.x, sparse); sb.y = add(sb.y, guiding); sb.z = add(sb.z, observed); sb.w = add(sb.w, rew);
+    if (eval) se.y = add(se.y, dvd(fabsf(v_delta), 10.0f));   // KAMMA_eval.py:840
+
+    if (want_stats) { acc[19] += g1; acc[20] += g2; }
+
+    // ------------------------------------------------------------------ reset_idx :417-498
+    if (reset) {
+      any_reset_local = 1;
+      if (want_stats) {   // episode statistics (logging) :470-488
+        const float T = p.max_episode_length_s, fin = sb.w, om = sub(1.0f, g2);
+        acc[0] += sa.x; acc[1] += sa.y; acc[2] += sa.z; acc[3] += sa.w;
+        acc[4] += sb.x; acc[5] += sb.y; acc[6] += sb.z; acc[7] += sb.w;
+        acc[8] += se.x; acc[9] += se.y; acc[10] += se.z;
+        acc[11] += mul(T, dvd(mul(mul(100.0f, om), sa.x), fin));
+        acc[12] += mul(T, dvd(mul(mul(100.0f, om), sa.y), fin));
+        acc[13] += mul(T, dvd(mul(mul(100.0f, om), sa.z), fin));
+        acc[14] += mul(T, dvd(mul(mul(100.0f, om), sa.w), fin));
+        acc[15] += mul(T, dvd(mul(mul(100.0f, om), sb.x), fin));
+        acc[16] += mul(T, dvd(mul(mul(100.0f, g2), sb.y), fin));
+        acc[17] += mul(T, dvd(mul(mul(100.0f, om), sb.z), fin));
+        acc[18] += 1.0f;
+      }
+      ResetDraws d;
+      if (io.reset_uniforms) {
+        const float4 ua = __ldcs(reinterpret_cast<const float4*>(io.reset_uniforms + 8 * i));
+        const float4 ub = __ldcs(reinterpret_cast<const float4*>(io.reset_uniforms + 8 * i + 4));
+        d.u[0] = ua.x; d.u[1] = ua.y; d.u[2] = ua.z; d.u[3] = ua.w; d.u[4] = ub.x; d.u[5] = ub.y; d.u[6] = ub.z;
+      } else {
+        d = philox_reset_draws(io.philox_seed, io.philox_offset, i, ph);
+      }
+      apply_reset(p, d, sim, s, cmd);
+      eb = 0;                                                   // :462
+      st.episode_count[i] += 1;                                 // :463
+      sa = make_float4(0.f, 0.f, 0.f, 0.f);                     // :485
+      sb = sa;
+      se = sa;
+    }
+
+    // ------------------------------------------------------------------ get_observations :833 + stores
+    float ob[6] = {cmd.x, cmd.z, v_delta, omega_delta, lin_acc, ang_acc};
+    if (io.clip_obs > 0.f) {
+#pragma unroll
+      for (int k = 0; k < 6; ++k) ob[k] = clipf(ob[k], -io.clip_obs, io.clip_obs);
+    }
+    float2* o = reinterpret_cast<float2*>(io.obs + 6 * i);
+    o[0] = make_float2(ob[0], ob[1]);
+    o[1] = make_float2(ob[2], ob[3]);
+    o[2] = make_float2(ob[4], ob[5]);
+    __stcs(io.rew + i, rew);
+    io.reset[i] = reset ? 1 : 0;
+    st_stream4(io.wheel_torqs + 4 * i, make_float4(wt[0], wt[1], wt[2], wt[3]));
+    if (io.timeout) __stcs(io.timeout + i, (int64_t)(timeout ? 1 : 0));
+    if (io.torques) st_stream4(io.torques + 4 * i, make_float4(tq[0], tq[1], tq[2], tq[3]));
+    if (io.guiding) __stcs(io.guiding + i, guiding);
+
+    st_stream4(st.pose_vx + 4 * i, make_float4(s.px, s.py, s.yaw, s.vx));
+    st_stream4(st.twist_prev + 4 * i, make_float4(s.vy, s.r, prev_lin, prev_ang));
+    st_stream4(st.wheel_speed + 4 * i, make_float4(s.w[0], s.w[1], s.w[2], s.w[3]));
+    st_stream4(st.commands + 4 * i, cmd);
+    st_stream4(st.sums_a + 4 * i, sa);
+    st_stream4(st.sums_b + 4 * i, sb);
+    __stcs(st.sim_steps + i, sim);
+    __stcs(st.episode_buf + i, eb);
+    if (eval) {
+      st_stream4(st.sums_eval + 4 * i, se);
+      st_stream4(st.old_torques + 4 * i, ot);
+    }
+
+    if (replay) {   // DDPG.record_transition -> memory.add_samples (ddpg.py:313), row `memory_index`
+      float2* rs = reinterpret_cast<float2*>(io.replay_states + 6 * i);
+      rs[0] = make_float2(prev_obs[0], prev_obs[1]);
+      rs[1] = make_float2(prev_obs[2], prev_obs[3]);
+      rs[2] = make_float2(prev_obs[4], prev_obs[5]);
+      float2* rn = reinterpret_cast<float2*>(io.replay_next_states + 6 * i);
+      rn[0] = make_float2(ob[0], ob[1]);
+      rn[1] = make_float2(ob[2], ob[3]);
+      rn[2] = make_float2(ob[4], ob[5]);
+      if (io.relabel == OIS_RELABEL_EXECUTED) {   // actions = wheel_torqs / action_scale (base_KA_DDPG.py:212)
+        st_stream4(io.replay_actions + 4 * i, make_float4(dvd(wt[0], p.action_scale), dvd(wt[1], p.action_scale),
+                                                          dvd(wt[2], p.action_scale), dvd(wt[3], p.action_scale)));
+      } else if (p.act_dim == 4) {
+        st_stream4(io.replay_actions + 4 * i, make_float4(a4[0], a4[1], a4[2], a4[3]));
+      } else if (p.act_dim == 2) {
+        reinterpret_cast<float2*>(io.replay_actions)[i] = make_float2(a4[0], a4[2]);
+      } else {
+        io.replay_actions[i] = a4[0];
+      }
+      io.replay_rewards[i] = rew;
+      io.replay_terminated[i] = reset ? 1 : 0;
+      io.replay_truncated[i] = 0;
+    }
+
+    if (io.comp0 && i == 0) {   // env-0 scalars behind observed_components :840-867
+      float* c = io.comp0;
+      c[0] = desired_v; c[1] = current_v; c[2] = desired_w; c[3] = current_w; c[4] = v_delta; c[5] = omega_delta;
+      c[6] = lin_acc; c[7] = ang_acc; c[8] = (float)st.episode_count[0];
+      c[9] = tq[0]; c[10] = tq[1]; c[11] = tq[2]; c[12] = tq[3]; c[13] = ac_left; c[14] = ac_right;
+      c[15] = a4[0]; c[16] = a4[1]; c[17] = a4[2]; c[18] = a4[3];
+      c[19] = g2; c[20] = c1; c[21] = c2; c[22] = c3; c[23] = rdense; c[24] = sparse; c[25] = observed;
+      c[26] = guiding; c[27] = rew; c[28] = g1;
+    }
+  }
+
+  if (want_stats) {
+    const int lane = threadIdx.x & 31;
+#pragma unroll
+    for (int k = 0; k < OIS_EP_STATS_LEN; ++k) {
+      const float v = warp_sum(acc[k]);
+      if (lane == 0 && v != 0.f) atomicAdd(&s_stats[k], v);
+    }
+    __syncthreads();
+    if (threadIdx.x < OIS_EP_STATS_LEN && s_stats[threadIdx.x] != 0.f) atomicAdd(io.ep_stats + threadIdx.x, s_stats[threadIdx.x]);
+  }
+  if (eval && io.any_reset_flags != nullptr) {
+    if (__syncthreads_or(any_reset_local) && threadIdx.x == 0) atomicOr(io.any_reset_flags + (io.flag_slot + 1) % 3, 1);
+    if (blockIdx.x == 0 && threadIdx.x == 0) io.any_reset_flags[(io.flag_slot + 2) % 3] = 0;
+  }
+}
+
+__global__ void __launch_bounds__(kEnvThreads)
+dynamics_kernel(const __grid_constant__ OisEnvParams p, const __grid_constant__ OisEnvState st,
+                const float* __restrict__ torques, const int64_t n) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    const float4 pv = ld_stream4(st.pose_vx + 4 * i);
+    float4 tp = ld_stream4(st.twist_prev + 4 * i);
+    const float4 wv = ld_stream4(st.wheel_speed + 4 * i);
+    const float4 t = ld_stream4(torques + 4 * i);
+    Skid s;
+    s.px = pv.x; s.py = pv.y; s.yaw = pv.z; s.vx = pv.w; s.vy = tp.x; s.r = tp.y;
+    s.w[0] = wv.x; s.w[1] = wv.y; s.w[2] = wv.z; s.w[3] = wv.w;
+    const float tau[4] = {t.x, t.y, t.z, t.w};
+    skid_steps(s, tau, p);
+    tp.x = s.vy; tp.y = s.r;
+    st_stream4(st.pose_vx + 4 * i, make_float4(s.px, s.py, s.yaw, s.vx));
+    st_stream4(st.twist_prev + 4 * i, tp);
+    st_stream4(st.wheel_speed + 4 * i, make_float4(s.w[0], s.w[1], s.w[2], s.w[3]));
+  }
+}
+
+__global__ void __launch_bounds__(kEnvThreads)
+reset_idx_kernel(const __grid_constant__ OisEnvParams p, const __grid_constant__ OisEnvState st,
+                 const int64_t* __restrict__ ids, const int64_t n_ids, const float* __restrict__ uniforms,
+                 const uint64_t seed, const uint64_t offset) {
+  for (int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; t < n_ids; t += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t i = ids[t];
+    ResetDraws d;
+    if (uniforms) {
+      for (int k = 0; k < 7; ++k) d.u[k] = uniforms[8 * i + k];
+    } else {
+      d = philox_reset_draws(seed, offset, i, Philox(seed)((uint64_t)i, offset * 4));
+    }
+    Skid s;
+    float4 cmd = ld_stream4(st.commands + 4 * i);
+    float4 tp = ld_stream4(st.twist_prev + 4 * i);
+    apply_reset(p, d, st.sim_steps[i], s, cmd);
+    st_stream4(st.pose_vx + 4 * i, make_float4(s.px, s.py, s.yaw, 0.f));
+    tp.x = 0.f; tp.y = 0.f;     // previous_* velocities are NOT reset (KAMMA_medium.py:435-446)
+    st_stream4(st.twist_prev + 4 * i, tp);
+    st_stream4(st.wheel_speed + 4 * i, make_float4(0.f, 0.f, 0.f, 0.f));
+    st_stream4(st.commands + 4 * i, cmd);
+    const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
+    st_stream4(st.sums_a + 4 * i, z);
+    st_stream4(st.sums_b + 4 * i, z);
+    if (p.eval_sums) st_stream4(st.sums_eval + 4 * i, z);
+    st.episode_buf[i] = 0;
+    st.episode_count[i] += 1;
+  }
+}
+
+static int grid_for(int64_t n, int threads) {
+  int64_t blocks = (n + threads - 1) / threads;
+  const int64_t cap = (int64_t)num_sms() * 16;   // 16 resident CTAs of 128 threads per SM: one full wave
+  if (blocks > cap) blocks = cap;
+  if (blocks < 1) blocks = 1;
+  return (int)blocks;
+}
+
+static int check_state(const OisEnvParams* p, const OisEnvState* s) {
+  OIS_CHECK_ARG(p && s, "null params/state");
+  OIS_CHECK_ARG(p->act_dim == 1 || p->act_dim == 2 || p->act_dim == 4, "act_dim must be 1, 2 or 4");
+  OIS_CHECK_ARG(s->pose_vx && s->twist_prev && s->wheel_speed && s->commands && s->sums_a && s->sums_b,
+                "null state array");
+  OIS_CHECK_ARG(s->sim_steps && s->episode_buf && s->episode_count, "null counter array");
+  OIS_CHECK_ARG(!p->eval_sums || (s->sums_eval && s->old_torques), "eval_sums needs sums_eval and old_torques");
+  OIS_CHECK_ARG(p->decimation >= 0 && p->decimation <= 1000, "bad decimation");
+  return OIS_OK;
+}
+
+}  // namespace ois
+
+using namespace ois;
+
+extern "C" int ois_env_step(const OisEnvParams* params, const OisEnvState* state, const OisEnvIO* io, int64_t n_envs,
+                            void* stream) {
+  if (int e = check_state(params, state)) return e;
+  OIS_CHECK_ARG(io, "null io");
+  OIS_CHECK_ARG(n_envs >= 0, "negative n_envs");
+  OIS_CHECK_ARG(io->actions && io->obs && io->rew && io->reset && io->wheel_torqs, "null required io array");
+  const bool any_replay = io->replay_states || io->replay_actions || io->replay_rewards || io->replay_next_states ||
+                          io->replay_terminated || io->replay_truncated;
+  const bool all_replay = io->replay_states && io->replay_actions && io->replay_rewards && io->replay_next_states &&
+                          io->replay_terminated && io->replay_truncated;
+  OIS_CHECK_ARG(!any_replay || all_replay, "replay pointers must be all set or all null");
+  OIS_CHECK_ARG(io->flag_slot >= 0 && io->flag_slot < 3, "flag_slot must be 0..2");
+  if (n_envs == 0) return OIS_OK;
+  env_step_kernel<<<grid_for(n_envs, kEnvThreads), kEnvThreads, 0, (cudaStream_t)stream>>>(*params, *state, *io, n_envs);
+  OIS_CHECK_LAUNCH();
+  return OIS_OK;
+}
+
+extern "C" int ois_dynamics_step(const OisEnvParams* params, const OisEnvState* state, const float* wheel_torqs,
+                                 int64_t n_envs, void* stream) {
+  OIS_CHECK_ARG(params && state && wheel_torqs, "null argument");
+  OIS_CHECK_ARG(state->pose_vx && state->twist_prev && state->wheel_speed, "null state array");
+  OIS_CHECK_ARG(n_envs >= 0, "negative n_envs");
+  if (n_envs == 0) return OIS_OK;
+  dynamics_kernel<<<grid_for(n_envs, kEnvThreads), kEnvThreads, 0, (cudaStream_t)stream>>>(*params, *state, wheel_torqs, n_envs);
+  OIS_CHECK_LAUNCH();
+  return OIS_OK;
+}
+
+extern "C" int ois_env_reset_idx(const OisEnvParams* params, const OisEnvState* state, const int64_t* env_ids,
+                                 int64_t n_ids, const float* reset_uniforms, uint64_t philox_seed,
+                                 uint64_t philox_offset, int64_t n_envs, void* stream) {
+  if (int e = check_state(params, state)) return e;
+  OIS_CHECK_ARG(n_ids >= 0 && n_ids <= n_envs, "bad n_ids");
+  OIS_CHECK_ARG(env_ids || n_ids == 0, "null env_ids");
+  if (n_ids == 0) return OIS_OK;
+  reset_idx_kernel<<<grid_for(n_ids, kEnvThreads), kEnvThreads, 0, (cudaStream_t)stream>>>(
+      *params, *state, env_ids, n_ids, reset_uniforms, philox_seed, philox_offset);
+  OIS_CHECK_LAUNCH();
+  return OIS_OK;
+}

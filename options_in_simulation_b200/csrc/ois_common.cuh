@@ -1,0 +1,89 @@
+// Shared device/host helpers for libois_b200.so (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include "ois_b200.h"
+
+namespace ois {
+
+void set_error(const char* fmt, ...);
+
+#define OIS_CHECK_ARG(cond, msg)                         \
+  do {                                                   \
+    if (!(cond)) {                                       \
+      ::ois::set_error("%s: %s", __func__, msg);         \
+      return OIS_ERR_INVALID_ARG;                        \
+    }                                                    \
+  } while (0)
+
+#define OIS_CHECK_CUDA(expr)                                                              \
+  do {                                                                                    \
+    cudaError_t _e = (expr);                                                              \
+    if (_e != cudaSuccess) {                                                              \
+      ::ois::set_error("%s: %s -> %s", __func__, #expr, cudaGetErrorString(_e));          \
+      return OIS_ERR_CUDA;                                                                \
+    }                                                                                     \
+  } while (0)
+
+#define OIS_CHECK_LAUNCH() OIS_CHECK_CUDA(cudaGetLastError())
+
+inline int num_sms() {
+  static int sms = 0;
+  if (sms == 0) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || sms <= 0) sms = 148;
+  }
+  return sms;
+}
+
+// ---------------------------------------------------------------------------------------------
+// Philox4x32-10 (Salmon et al. 2011), counter-based: throughput-mode RNG for the Bernoulli switch,
+// resets, OU noise and replay sampling.  Parity tests bypass it by supplying the draws.
+// ---------------------------------------------------------------------------------------------
+struct Philox {
+  uint32_t k0, k1;
+  __host__ __device__ Philox(uint64_t seed) : k0((uint32_t)seed), k1((uint32_t)(seed >> 32)) {}
+  __host__ __device__ static inline void mulhilo(uint32_t a, uint32_t b, uint32_t& hi, uint32_t& lo) {
+    uint64_t p = (uint64_t)a * b;
+    hi = (uint32_t)(p >> 32);
+    lo = (uint32_t)p;
+  }
+  __host__ __device__ inline uint4 operator()(uint64_t ctr_lo, uint64_t ctr_hi) const {
+    uint32_t c0 = (uint32_t)ctr_lo, c1 = (uint32_t)(ctr_lo >> 32), c2 = (uint32_t)ctr_hi, c3 = (uint32_t)(ctr_hi >> 32);
+    uint32_t a = k0, b = k1;
+#pragma unroll
+    for (int r = 0; r < 10; ++r) {
+      uint32_t h0, l0, h1, l1;
+      mulhilo(0xD2511F53u, c0, h0, l0);
+      mulhilo(0xCD9E8D57u, c2, h1, l1);
+      c0 = h1 ^ c1 ^ a;
+      c1 = l1;
+      c2 = h0 ^ c3 ^ b;
+      c3 = l0;
+      a += 0x9E3779B9u;
+      b += 0xBB67AE85u;
+    }
+    return make_uint4(c0, c1, c2, c3);
+  }
+};
+
+// [0,1) with 24 random bits, the same mapping torch.rand uses for float32
+__host__ __device__ inline float u01(uint32_t x) { return (float)(x >> 8) * (1.0f / 16777216.0f); }
+
+// Box-Muller pair from two 32-bit words
+__device__ inline float2 normal2(uint32_t a, uint32_t b) {
+  float u1 = ((float)(a >> 8) + 1.0f) * (1.0f / 16777216.0f);  // (0,1]
+  float u2 = u01(b);
+  float r = sqrtf(-2.0f * logf(u1));
+  float s, c;
+  sincospif(2.0f * u2, &s, &c);
+  return make_float2(r * c, r * s);
+}
+
+// streaming 16-byte accesses: every state field is touched once per step
+__device__ inline float4 ld_stream4(const float* p) { return __ldcs(reinterpret_cast<const float4*>(p)); }
+__device__ inline void st_stream4(float* p, const float4& v) { __stcs(reinterpret_cast<float4*>(p), v); }
+
+}  // namespace ois

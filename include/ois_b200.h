@@ -178,6 +178,12 @@ typedef struct OisScaler {  /* skrl RunningStandardScaler state (fp64), restated
   double* current_count;    /* [1] */
 } OisScaler;
 
+/* RunningStandardScaler.forward(x, train) on [n_rows, dim] (dim <= 16): y = clamp((x - mean) / (sqrt(var) + 1e-8), +-5);
+ * train != 0 first merges the batch statistics into the fp64 running state (parallel variance), as skrl does
+ * inside DDPG._update (src/my_agents/ddpg.py:381-382).  Restated in oracle/ref_harness/skrl_shim.py. */
+int ois_scaler_forward(const OisScaler* scaler, const float* x, float* y, int64_t n_rows, int32_t dim, int32_t train,
+                       void* stream);
+
 typedef struct OisActIO {
   const float* states;       /* [N,obs_dim] */
   float* actions;            /* [N,act_dim] out */
@@ -197,6 +203,9 @@ typedef struct OisAgent OisAgent;   /* opaque: workspaces, bf16 weight copies, T
 int ois_agent_create(OisAgent** out, const OisMlpShape* actor, const OisMlpShape* critic, int64_t max_rows,
                      int32_t batch_size, int32_t precision, void* stream);
 int ois_agent_destroy(OisAgent* agent);
+/* The caller changed parameter buffers behind the handle's back (load_state_dict, checkpoint load):
+ * drop cached bf16 weight images.  ois_ddpg_update_phase invalidates by itself. */
+int ois_agent_invalidate(OisAgent* agent);
 
 /* DDPG.act (ddpg.py:215-268): scaler -> actor MLP -> OU noise -> clamp, N rows. */
 int ois_agent_act(OisAgent* agent, const float* actor_params, const OisScaler* scaler, const OisActIO* io,
@@ -235,6 +244,10 @@ int ois_ddpg_update_phase(OisAgent* agent, const OisScaler* scaler, const OisUpd
 /* ------------------------------------------------------------------------------------------------ */
 const char* ois_last_error_string(void);
 int ois_abi_version(void);
+/* sizeof() of the ABI structs as this library was compiled, so a foreign-language mirror (ctypes, cgo ...)
+ * can verify its layout: 0 OisEnvParams, 1 OisEnvState, 2 OisEnvIO, 3 OisMlpShape, 4 OisScaler, 5 OisActIO,
+ * 6 OisUpdateIO; -1 for an unknown index. */
+int ois_struct_size(int which);
 /* name of the SASS feature set compiled in, e.g. "sm_100a tcgen05+tma" */
 const char* ois_build_info(void);
 

@@ -92,12 +92,15 @@ SYMBOLS = {
     "ois_replay_sample_indices": (C.c_int, [_p, _i64, _i64, _u64, _u64, _p]),
     "ois_agent_create": (C.c_int, [_PP(_p), _PP(MlpShape), _PP(MlpShape), _i64, _i32, _i32, _p]),
     "ois_agent_destroy": (C.c_int, [_p]),
+    "ois_agent_invalidate": (C.c_int, [_p]),
     "ois_agent_act": (C.c_int, [_p, _p, _PP(Scaler), _PP(ActIO), _i64, _p]),
+    "ois_scaler_forward": (C.c_int, [_PP(Scaler), _p, _p, _i64, _i32, _i32, _p]),
     "ois_mlp_forward": (C.c_int, [_p, _PP(MlpShape), _p, _p, _p, _i64, _p]),
     "ois_ddpg_update_phase": (C.c_int, [_p, _PP(Scaler), _PP(UpdateIO), _i32, _f, _p]),
     "ois_last_error_string": (C.c_char_p, []),
     "ois_abi_version": (C.c_int, []),
     "ois_build_info": (C.c_char_p, []),
+    "ois_struct_size": (C.c_int, [C.c_int]),
 }
 
 _lib = None

@@ -128,3 +128,22 @@ def env_params(variant: EnvVariant, cfg: dict, *, physics: bool = True, gamma_co
     p.wheel_damping = float(ctl["damping"])
     p.wheel_speed_max = float(rob["wheel_speed_max"])
     return p
+
+
+def script_cfg(num_envs: int, *, stiffness: float = 0.035, damping: float = 0.005, static_friction: float = 0.85,
+               dynamic_friction: float = 0.85, yaw_constant: float = 0.5, linear_x=(1.0, 2.0), seed: int = 42,
+               sim_device: str = "cuda:0") -> dict:
+    """TASK_CFG after the mutations every train/eval script applies from its argparse defaults
+    (train/train_kamma_4d_nofifo_random_RLIL.py:63-91), with ``numEnvs`` as given."""
+    cfg = task_cfg()
+    cfg["seed"] = seed
+    cfg["sim_device"] = sim_device
+    env = cfg["task"]["env"]
+    env["numEnvs"] = int(num_envs)
+    env["control"]["stiffness"] = stiffness
+    env["control"]["damping"] = damping
+    mat = cfg["task"]["sim"]["default_physics_material"]
+    mat["static_friction"], mat["dynamic_friction"] = static_friction, dynamic_friction
+    env["randomCommandVelocityRanges"]["yaw_constant"] = yaw_constant
+    env["randomCommandVelocityRanges"]["linear_x"] = list(linear_x)
+    return cfg

@@ -403,6 +403,25 @@ extern "C" int ois_agent_destroy(OisAgent* a) {
   return OIS_OK;
 }
 
+extern "C" int ois_agent_invalidate(OisAgent* a) {
+  OIS_CHECK_ARG(a, "null agent");
+  if (a->precision == OIS_PRECISION_BF16) tc_invalidate_weights(a);
+  return OIS_OK;
+}
+
+extern "C" int ois_scaler_forward(const OisScaler* sc, const float* x, float* y, int64_t n_rows, int32_t dim,
+                                  int32_t train, void* stream) {
+  OIS_CHECK_ARG(sc && sc->running_mean && sc->running_variance && sc->current_count && x && y, "null argument");
+  OIS_CHECK_ARG(dim > 0 && dim <= 16 && n_rows >= 0, "bad sizes");
+  OIS_CHECK_ARG(!train || (n_rows >= 2 && n_rows <= (1 << 24)), "train needs 2 <= n_rows <= 2^24");
+  if (n_rows == 0) return OIS_OK;
+  cudaStream_t s = (cudaStream_t)stream;
+  if (train) scaler_train_kernel<<<1, 256, 0, s>>>(x, y, (int)n_rows, dim, sc->running_mean, sc->running_variance, sc->current_count, dim);
+  else scaler_apply_kernel<<<eg(n_rows * dim, 256), 256, 0, s>>>(x, y, n_rows, dim, sc->running_mean, sc->running_variance, dim);
+  OIS_CHECK_LAUNCH();
+  return OIS_OK;
+}
+
 extern "C" int ois_mlp_forward(OisAgent* a, const OisMlpShape* shape, const float* params, const float* x, float* y,
                                int64_t n_rows, void* stream) {
   OIS_CHECK_ARG(a && shape && params && x && y, "null argument");

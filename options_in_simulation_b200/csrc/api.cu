@@ -16,3 +16,15 @@ void set_error(const char* fmt, ...) {
 extern "C" const char* ois_last_error_string(void) { return ois::g_err; }
 extern "C" int ois_abi_version(void) { return OIS_ABI_VERSION; }
 extern "C" const char* ois_build_info(void) { return "sm_100a; env: fused fp32 SIMT; mlp: tcgen05+TMA bf16 / fp32 SIMT"; }
+extern "C" int ois_struct_size(int which) {
+  switch (which) {
+    case 0: return (int)sizeof(OisEnvParams);
+    case 1: return (int)sizeof(OisEnvState);
+    case 2: return (int)sizeof(OisEnvIO);
+    case 3: return (int)sizeof(OisMlpShape);
+    case 4: return (int)sizeof(OisScaler);
+    case 5: return (int)sizeof(OisActIO);
+    case 6: return (int)sizeof(OisUpdateIO);
+    default: return -1;
+  }
+}

@@ -362,6 +362,10 @@ env_step_kernel(const __grid_constant__ OisEnvParams p, const __grid_constant__ 
     }
 
     if (replay) {   // DDPG.record_transition -> memory.add_samples (ddpg.py:313), row `memory_index`
+      if (io.clip_obs > 0.f) {   // the trainer's `states` are the wrapper's clamped observations of the previous step
+#pragma unroll
+        for (int k = 0; k < 6; ++k) prev_obs[k] = clipf(prev_obs[k], -io.clip_obs, io.clip_obs);
+      }
       float2* rs = reinterpret_cast<float2*>(io.replay_states + 6 * i);
       rs[0] = make_float2(prev_obs[0], prev_obs[1]);
       rs[1] = make_float2(prev_obs[2], prev_obs[3]);

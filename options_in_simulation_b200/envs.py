@@ -283,8 +283,9 @@ class TorqueDistributionTask:
         """RLTask.reset (rl_task.py:251-253): flag every env for reset."""
         self.reset_buf = torch.ones_like(self.reset_buf)
 
-    def pre_physics_step(self, actions):
-        """KAMMA_medium.py:596-656 — and, fused behind it, everything post_physics_step computes."""
+    def pre_physics_step(self, actions, record: bool = True):
+        """KAMMA_medium.py:596-656 — and, fused behind it, everything post_physics_step computes.
+        ``record=False`` suppresses the fused replay append for this step (the wrapper's reset step)."""
         if self._env is not None and hasattr(self._env, "world") and not self._env.world.is_playing():
             return
         if actions.data_ptr() != self.actions.data_ptr():
@@ -306,7 +307,7 @@ class TorqueDistributionTask:
             io.any_reset_flags = self._any_reset_flags.data_ptr()
         io.flag_slot = self._launches % 3
         io.clip_obs = -1.0
-        if self._replay is not None:
+        if self._replay is not None and record:
             m = self._replay
             r = m.memory_index
             io.replay_states = m.tensors["states"][r].data_ptr()
@@ -330,8 +331,8 @@ class TorqueDistributionTask:
         self.progress_buf += 1
         return self.obs_buf, self.rew_buf, self.reset_buf, self.extras
 
-    def step(self, actions):
-        self.pre_physics_step(actions)
+    def step(self, actions, record: bool = True):
+        self.pre_physics_step(actions, record)
         return self.obs_buf, self.rew_buf, self.reset_buf, self.extras
 
     def get_observations(self):   # :825-869
@@ -418,7 +419,7 @@ class VecEnv:
                 self.task.post_reset()
             # VecEnvRLGames.reset steps once with zero actions to produce the first observation
             zero = torch.zeros(self.num_envs, self.task.num_actions, device=self.device)
-            obs, _, _, _ = self.task.step(zero)
+            obs, _, _, _ = self.task.step(zero, record=False)
             self._obs = torch.clamp(obs, -self.task.clip_obs, self.task.clip_obs)
             self._reset_once = False
         return self._obs, {}

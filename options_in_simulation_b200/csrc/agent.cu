@@ -5,6 +5,7 @@
 #include <new>
 #include "agent.cuh"
 #include "mlp_fp32.cuh"
+#include "explore.cuh"
 
 namespace ois {
 
@@ -215,16 +216,7 @@ __global__ void polyak_kernel(float* __restrict__ pt, const float* __restrict__ 
   pt[i] = __fadd_rn(__fmul_rn(pt[i], 1.0f - tau), __fmul_rn(tau, p[i]));
 }
 
-__device__ __forceinline__ void atomic_max_f(float* addr, float v) {
-  if (v >= 0.f) atomicMax(reinterpret_cast<int*>(addr), __float_as_int(v));
-  else atomicMin(reinterpret_cast<unsigned int*>(addr), __float_as_uint(v));
-}
-__device__ __forceinline__ void atomic_min_f(float* addr, float v) {
-  if (v >= 0.f) atomicMin(reinterpret_cast<int*>(addr), __float_as_int(v));
-  else atomicMax(reinterpret_cast<unsigned int*>(addr), __float_as_uint(v));
-}
-
-// OrnsteinUhlenbeckNoise.sample + ddpg.py:247-255 (scale, add, clamp) or the random_timesteps branch :229-230
+// the random_timesteps branch (ddpg.py:229-230) or OU exploration on top of the actor output (explore.cuh)
 __global__ void __launch_bounds__(256)
 explore_kernel(const __grid_constant__ OisActIO io, int64_t n, int A) {
   const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -237,38 +229,11 @@ explore_kernel(const __grid_constant__ OisActIO io, int64_t n, int A) {
       else { const uint4 r = Philox(io.philox_seed)((uint64_t)(i >> 2), io.philox_offset * 2 + 1); u = u01(((const uint32_t*)&r)[i & 3]); }
       io.actions[i] = __fadd_rn(__fmul_rn(u, __fsub_rn(io.clip_high, io.clip_low)), io.clip_low);
     } else if (io.ou_state) {
-      float z;
-      if (io.normals) z = io.normals[i];
-      else {
-        const uint4 r = Philox(io.philox_seed)((uint64_t)(i >> 2), io.philox_offset * 2);
-        const float2 n01 = normal2(r.x, r.y), n23 = normal2(r.z, r.w);
-        const float zz[4] = {n01.x, n01.y, n23.x, n23.y};
-        z = zz[i & 3];
-      }
-      const float st = io.ou_state[i];
-      const float ns = __fadd_rn(st, __fadd_rn(__fmul_rn(-st, io.theta), __fmul_rn(io.sigma, z)));   // state += -state*theta + sigma*N
-      io.ou_state[i] = ns;
-      if (io.noise_scale >= 0.f) {
-        nz = __fmul_rn(__fmul_rn(io.base_scale, ns), io.noise_scale);
-        have = true;
-        const float a = __fadd_rn(io.actions[i], nz);
-        io.actions[i] = fminf(fmaxf(a, io.clip_low), io.clip_high);
-      }
+      io.actions[i] = explore_elem(io, i, io.actions[i], nz, have);
     }
   }
-  if (io.noise_stats && !io.random_phase && io.ou_state && io.noise_scale >= 0.f) {
-    float mx = have ? nz : -INFINITY, mn = have ? nz : INFINITY, sm = have ? nz : 0.f;
-    for (int o = 16; o > 0; o >>= 1) {
-      mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
-      mn = fminf(mn, __shfl_xor_sync(0xffffffffu, mn, o));
-      sm += __shfl_xor_sync(0xffffffffu, sm, o);
-    }
-    if ((threadIdx.x & 31) == 0 && mx != -INFINITY) {
-      atomic_max_f(io.noise_stats + 0, mx);
-      atomic_min_f(io.noise_stats + 1, mn);
-      atomicAdd(io.noise_stats + 2, sm);
-    }
-  }
+  if (io.noise_stats && !io.random_phase && io.ou_state && io.noise_scale >= 0.f)
+    noise_stats_warp(io, have ? nz : -INFINITY, have ? nz : INFINITY, have ? nz : 0.f);
 }
 
 // ------------------------------------------------------------------------------------------- host helpers
@@ -442,7 +407,7 @@ extern "C" int ois_agent_act(OisAgent* a, const float* actor_params, const OisSc
   const int A = a->actor.out_dim, D = a->actor.in_dim;
   if (!io->random_phase) {
     if (a->precision == OIS_PRECISION_BF16) {
-      if (int e = tc_actor_forward(a, actor_params, scaler, io->states, io->actions, n_rows, s)) return e;
+      return tc_actor_forward(a, actor_params, scaler, io, n_rows, s);   // exploration fused into its epilogue
     } else {
       const float* x = io->states;
       if (scaler && scaler->running_mean) {

@@ -1,0 +1,53 @@
+// OrnsteinUhlenbeckNoise.sample + ddpg.py:247-255 (scale, add, clamp) for ONE action element, shared by the
+// standalone explore kernel (fp32 path) and the epilogue of the tcgen05 actor kernel, so both paths draw
+// identical noise.  `i` = row * act_dim + column.
+#pragma once
+#include "ois_common.cuh"
+
+namespace ois {
+
+__device__ __forceinline__ float explore_elem(const OisActIO& io, int64_t i, float action, float& nz, bool& have) {
+  float z;
+  if (io.normals) {
+    z = io.normals[i];
+  } else {
+    const uint4 r = Philox(io.philox_seed)((uint64_t)(i >> 2), io.philox_offset * 2);
+    const float2 n01 = normal2(r.x, r.y), n23 = normal2(r.z, r.w);
+    const int k = (int)(i & 3);
+    z = k == 0 ? n01.x : k == 1 ? n01.y : k == 2 ? n23.x : n23.y;
+  }
+  const float st = io.ou_state[i];
+  const float ns = __fadd_rn(st, __fadd_rn(__fmul_rn(-st, io.theta), __fmul_rn(io.sigma, z)));   // state += -state*theta + sigma*N
+  io.ou_state[i] = ns;
+  if (io.noise_scale >= 0.f) {
+    nz = __fmul_rn(__fmul_rn(io.base_scale, ns), io.noise_scale);
+    have = true;
+    return fminf(fmaxf(__fadd_rn(action, nz), io.clip_low), io.clip_high);
+  }
+  return action;
+}
+
+__device__ __forceinline__ void atomic_max_f(float* addr, float v) {
+  if (v >= 0.f) atomicMax(reinterpret_cast<int*>(addr), __float_as_int(v));
+  else atomicMin(reinterpret_cast<unsigned int*>(addr), __float_as_uint(v));
+}
+__device__ __forceinline__ void atomic_min_f(float* addr, float v) {
+  if (v >= 0.f) atomicMin(reinterpret_cast<int*>(addr), __float_as_int(v));
+  else atomicMax(reinterpret_cast<unsigned int*>(addr), __float_as_uint(v));
+}
+
+// warp-reduce (max, min, sum) of the applied noises and fold into io.noise_stats (ddpg.py:258-260)
+__device__ __forceinline__ void noise_stats_warp(const OisActIO& io, float mx, float mn, float sm) {
+  for (int o = 16; o > 0; o >>= 1) {
+    mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+    mn = fminf(mn, __shfl_xor_sync(0xffffffffu, mn, o));
+    sm += __shfl_xor_sync(0xffffffffu, sm, o);
+  }
+  if ((threadIdx.x & 31) == 0 && mx != -INFINITY) {
+    atomic_max_f(io.noise_stats + 0, mx);
+    atomic_min_f(io.noise_stats + 1, mn);
+    atomicAdd(io.noise_stats + 2, sm);
+  }
+}
+
+}  // namespace ois

@@ -5,6 +5,9 @@ skrl-Agent mirror (options_in_simulation_b200/agent.py):
   * bf16 tcgen05 actor inference vs the fp32 oracle under the stated bf16 tolerance.
 Tolerances (fp32 path): actions / Q statistics / updated weights <= 1e-5 relative to max(1, |ref|) —
 GEMM summation order differs from CPU torch, so results are not bit-identical; scaler state (fp64) <= 1e-9.
+Scaler statistics: the reference feeds float32 torch.mean / torch.var results into its fp64 running state, so
+its state carries fp32 reduction-order noise (~1e-7 relative); the kernel reduces in fp64 and rounds once ->
+compared at 1e-6 relative.
 bf16 path: |action - fp32 oracle| <= 2e-2 absolute on the sigmoid/tanh output (bf16 has 8 mantissa bits:
 three 512/128-wide bf16 layers give ~3e-3 typical, 2e-2 worst case; fp32 accumulation)."""
 import numpy as np
@@ -99,8 +102,8 @@ def test_ddpg_fp32_matches_reference_golden(fname):
             assert rel(d[f"r{k}_{net}_sub"], sub) <= 1e-5, f"{net} round {k}"
             assert flat.double().sum().item() == pytest.approx(float(d[f"r{k}_{net}_sum"]), abs=2e-3)
         sc = agent._state_preprocessor
-        assert np.abs(sc.running_mean.cpu().numpy() - d[f"r{k}_scaler_mean"]).max() <= 1e-9
-        assert np.abs(sc.running_variance.cpu().numpy() - d[f"r{k}_scaler_var"]).max() <= 1e-9
+        assert rel(d[f"r{k}_scaler_mean"], sc.running_mean.cpu().numpy()) <= 1e-6
+        assert rel(d[f"r{k}_scaler_var"], sc.running_variance.cpu().numpy()) <= 1e-6
         assert float(sc.current_count) == float(d[f"r{k}_scaler_count"])
         assert rel(d[f"r{k}_policy_m_sub"], agent.policy_optimizer.m[:: meta["stride"]].cpu().numpy()) <= 1e-5
         assert rel(d[f"r{k}_policy_v_sub"], agent.policy_optimizer.v[:: meta["stride"]].cpu().numpy()) <= 1e-5
@@ -135,10 +138,11 @@ def test_scaler_forward_train_matches_skrl_restatement():
         x = torch.randn(512, 6, generator=g) * (k + 1) + k
         y, yr = mine(x.cuda(), train=True), ref(x, train=True)
         assert rel(yr.numpy(), y.cpu().numpy()) <= 1e-6
-        assert torch.allclose(mine.running_mean.cpu(), ref.running_mean, rtol=0, atol=1e-9)
-        assert torch.allclose(mine.running_variance.cpu(), ref.running_variance, rtol=1e-9, atol=1e-9)
+        assert rel(ref.running_mean.numpy(), mine.running_mean.cpu().numpy()) <= 1e-6
+        assert rel(ref.running_variance.numpy(), mine.running_variance.cpu().numpy()) <= 1e-6
         assert float(mine.current_count) == float(ref.current_count)
     x = torch.randn(1000, 6, generator=g) * 50
+    mine.load_state_dict(ref.state_dict())                 # identical fp64 state ->
     assert torch.equal(mine(x.cuda()).cpu(), ref(x))      # inference form: same fp32 expression, bit-exact
 
 

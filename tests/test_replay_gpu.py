@@ -132,7 +132,8 @@ def test_fused_append_equals_record_transition_path():
         a = torch.rand(n, 4, device="cuda", generator=g)
         o0, r0, d0, tr0, _ = envs[0].step(a)
         o1, r1, d1, tr1, _ = envs[1].step(a)
-        relabeled = tasks[1].wheel_torqs / tasks[1].action_scale
+        # true fp32 division like CPU torch (CUDA torch multiplies by the reciprocal: 1 ulp apart)
+        relabeled = (tasks[1].wheel_torqs.cpu() / tasks[1].action_scale).cuda()
         plain.add_samples(states=obs[1], actions=relabeled, rewards=r1, next_states=o1, terminated=d1, truncated=tr1)
         obs = [o0.clone(), o1.clone()]
         assert fused.memory_index == plain.memory_index and fused.filled == plain.filled

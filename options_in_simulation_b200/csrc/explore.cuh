@@ -27,6 +27,32 @@ __device__ __forceinline__ float explore_elem(const OisActIO& io, int64_t i, flo
   return action;
 }
 
+// The same for one whole row when act_dim == 4 (one Philox call serves the row: counter = row, lanes 0..3 —
+// exactly the draws explore_elem makes for i = 4*row + k).  Accumulates the applied noises into (mx, mn, sm).
+__device__ __forceinline__ void explore_row4(const OisActIO& io, int64_t row, float (&a)[4], float& mx, float& mn, float& sm) {
+  float z[4];
+  if (io.normals) {
+    const float4 n4 = *reinterpret_cast<const float4*>(io.normals + 4 * row);
+    z[0] = n4.x; z[1] = n4.y; z[2] = n4.z; z[3] = n4.w;
+  } else {
+    const uint4 r = Philox(io.philox_seed)((uint64_t)row, io.philox_offset * 2);
+    const float2 n01 = normal2(r.x, r.y), n23 = normal2(r.z, r.w);
+    z[0] = n01.x; z[1] = n01.y; z[2] = n23.x; z[3] = n23.y;
+  }
+  float4 st4 = *reinterpret_cast<const float4*>(io.ou_state + 4 * row);
+  float st[4] = {st4.x, st4.y, st4.z, st4.w};
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    st[k] = __fadd_rn(st[k], __fadd_rn(__fmul_rn(-st[k], io.theta), __fmul_rn(io.sigma, z[k])));
+    if (io.noise_scale >= 0.f) {
+      const float nz = __fmul_rn(__fmul_rn(io.base_scale, st[k]), io.noise_scale);
+      mx = fmaxf(mx, nz); mn = fminf(mn, nz); sm += nz;
+      a[k] = fminf(fmaxf(__fadd_rn(a[k], nz), io.clip_low), io.clip_high);
+    }
+  }
+  *reinterpret_cast<float4*>(io.ou_state + 4 * row) = make_float4(st[0], st[1], st[2], st[3]);
+}
+
 __device__ __forceinline__ void atomic_max_f(float* addr, float v) {
   if (v >= 0.f) atomicMax(reinterpret_cast<int*>(addr), __float_as_int(v));
   else atomicMin(reinterpret_cast<unsigned int*>(addr), __float_as_uint(v));

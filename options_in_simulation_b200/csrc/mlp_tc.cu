@@ -2,17 +2,19 @@
 // in ONE persistent, warp-specialised kernel (reference: src/my_agents/ddpg.py:215-268 with the
 // model of train/train_kamma_4d_nofifo_random_RLIL.py:21-36).
 //
-// One CTA owns a 128-row tile of envs at a time; all four layers run back to back with the activations never
-// leaving the SM:
+// One CTA owns a 128-row tile of envs at a time; all four layers run back to back and the activations never
+// leave the SM:
 //   * weights: packed once per parameter change into a bf16 "stream image" (canonical UMMA no-swizzle K-major
 //     core-matrix layout, in exactly the order the MMA warp consumes it: 42 stages of 16 KB), streamed from L2
-//     through a 3-deep shared-memory ring by 1-D bulk async copies (UBLKCP) completing on mbarriers;
-//   * MMA: one elected thread issues tcgen05.mma.cta_group::1.kind::f16 (M=128, N=128/16, K=16), A = activations
-//     in shared memory, B = weight stage, D = fp32 accumulators in TMEM (2 x 128 ping-pong columns + L3 + L4);
+//     through a 10-deep shared-memory ring (160 KB in flight) by 1-D bulk async copies (UBLKCP) on mbarriers;
+//   * layer-1 / layer-3 outputs (act1 128x512, act3 128x128, bf16) live in TENSOR MEMORY and feed the next
+//     layer as the A operand of tcgen05.mma (A-from-TMEM form): no shared-memory traffic for A, and shared
+//     memory is left to the weight ring;
+//   * MMA: one elected thread issues tcgen05.mma.cta_group::1.kind::f16, M=128, N=64 pieces with fp32
+//     accumulators ping-ponging between two 64-column TMEM buffers; layer-3 partial products (A = the 64-column
+//     slice of act2 just activated, in shared memory) are issued one piece behind layer 2;
 //   * epilogue: 8 warps (two per TMEM lane quadrant) tcgen05.ld the accumulators, add bias, ELU, convert to
-//     bf16 and write the next layer's A operand straight into shared memory; layer-3 partial products are
-//     issued as soon as each 128-column slice of layer 2 has been activated, so act2 only ever exists as one
-//     32 KB slice;
+//     bf16 and tcgen05.st / st.shared the next operand;
 //   * the last epilogue applies Sigmoid/Tanh, the OU exploration noise (explore.cuh) and the clamp.
 // fp32 master weights are untouched; accumulation is fp32; tolerance vs the fp32 oracle: tests/test_agent_gpu.py.
 #include "agent.cuh"
@@ -27,34 +29,34 @@ constexpr int kThreads = 320;             // warp 0: bulk-copy producer, warp 1:
 constexpr int kEpiWarps = 8;
 constexpr int kH0 = 512, kH1 = 512, kH2 = 128, kInPad = 16, kOutPad = 16;
 constexpr int kStageBytes = 16384;
-constexpr int kStages = 3;
+constexpr int kStages = 10;
+constexpr int kRingSlots = 3;             // act2 slices: [8 kc][128 rows][8] bf16 = 16 KB each
 constexpr int kStreamStages = 42;         // 1 (W1) + 32 (W2) + 8 (W3) + 1 (W4)
 constexpr int kLastStageBytes = kOutPad * kH2 * 2;                       // 4096
 constexpr size_t kImageBytes = (size_t)(kStreamStages - 1) * kStageBytes + kLastStageBytes;
 // shared memory map (bytes)
-constexpr int kOffAct1 = 0;                                // [64 kc][128 rows][8] bf16 = 128 KB
-constexpr int kOffRing = kOffAct1 + kTileM * kH0 * 2;      // act2 slice / act3: [16 kc][128][8] = 32 KB
-constexpr int kOffX = kOffRing + kTileM * 128 * 2;         // [2 kc][128][8] = 4 KB
-constexpr int kOffW = kOffX + kTileM * kInPad * 2;         // 3 x 16 KB
-constexpr int kOffBias = kOffW + kStages * kStageBytes;    // b1 512, b2 512, b3 128, b4 16 fp32
+constexpr int kOffW = 0;                                    // 10 x 16 KB weight ring
+constexpr int kOffRing = kOffW + kStages * kStageBytes;     // 3 x 16 KB act2 slices
+constexpr int kOffX = kOffRing + kRingSlots * 16384;        // [2 kc][128][8] = 4 KB
+constexpr int kOffBias = kOffX + kTileM * kInPad * 2;       // b1 512, b2 512, b3 128, b4 16 fp32
 constexpr int kOffBar = kOffBias + (kH0 + kH1 + kH2 + kOutPad) * 4;
-constexpr int kSmemBytes = kOffBar + 256;
+constexpr int kSmemBytes = kOffBar + 512;
 // TMEM columns
-constexpr int kColD = 0;        // two ping-pong 128-column accumulators (layers 1 and 2)
-constexpr int kColD3 = 256;     // layer 3, 128 columns
-constexpr int kColD4 = 384;     // layer 4, 16 columns
+constexpr int kColAct = 0;      // act1 as bf16 pairs: 256 columns (act3 later reuses columns 0..63)
+constexpr int kColD = 256;      // two ping-pong 64-column fp32 accumulators (layers 1, 2; layer 4 uses buffer 0)
+constexpr int kColD3 = 384;     // layer 3, 128 columns
 constexpr int kTmemCols = 512;
 
-// stream order: W1 | W2 q0 (8 k-blocks) | W2 q1 | W3 p0 (2 halves) | W2 q2 | W3 p1 | W2 q3 | W3 p2 | W3 p3 | W4
+// stream order: W1 | W2 q0 (4 k-blocks of 128) | W2 q1 | W3 p0 | W2 q2 | W3 p1 | ... | W2 q7 | W3 p6 | W3 p7 | W4
 __host__ __device__ inline void stage_info(int s, int& layer, int& piece, int& kb) {
   if (s == 0) { layer = 1; piece = 0; kb = 0; }
-  else if (s < 17) { layer = 2; piece = (s - 1) >> 3; kb = (s - 1) & 7; }
-  else if (s < 19) { layer = 3; piece = 0; kb = s - 17; }
-  else if (s < 27) { layer = 2; piece = 2; kb = s - 19; }
-  else if (s < 29) { layer = 3; piece = 1; kb = s - 27; }
-  else if (s < 37) { layer = 2; piece = 3; kb = s - 29; }
-  else if (s < 39) { layer = 3; piece = 2; kb = s - 37; }
-  else if (s < 41) { layer = 3; piece = 3; kb = s - 39; }
+  else if (s < 9) { layer = 2; piece = (s - 1) >> 2; kb = (s - 1) & 3; }
+  else if (s < 39) {
+    const int g = (s - 9) / 5, r = (s - 9) % 5;
+    if (r == 0) { layer = 3; piece = g; kb = 0; }
+    else { layer = 2; piece = g + 2; kb = r - 1; }
+  }
+  else if (s < 41) { layer = 3; piece = s - 33; kb = 0; }
   else { layer = 4; piece = 0; kb = 0; }
 }
 }  // namespace tc
@@ -87,8 +89,8 @@ tc_pack_kernel(const float* __restrict__ P, uint4* __restrict__ image, int in_di
   const float* W;
   int n, k0, N, K;
   if (layer == 1) { W = P + w0; n = cc & 511; k0 = (cc >> 9) * 8; N = kH0; K = in_dim; }
-  else if (layer == 2) { W = P + w1; n = piece * 128 + (cc & 127); k0 = kb * 64 + (cc >> 7) * 8; N = kH1; K = kH0; }
-  else if (layer == 3) { W = P + w2; n = cc & 127; k0 = piece * 128 + kb * 64 + (cc >> 7) * 8; N = kH2; K = kH1; }
+  else if (layer == 2) { W = P + w1; n = piece * 64 + (cc & 63); k0 = kb * 128 + (cc >> 6) * 8; N = kH1; K = kH0; }
+  else if (layer == 3) { W = P + w2; n = cc & 127; k0 = piece * 64 + (cc >> 7) * 8; N = kH2; K = kH1; }
   else { W = P + w3; n = cc & 15; k0 = (cc >> 4) * 8; N = out_dim; K = kH2; }
   float v[8];
 #pragma unroll
@@ -98,33 +100,36 @@ tc_pack_kernel(const float* __restrict__ P, uint4* __restrict__ image, int in_di
 }
 
 
+
+
 // ----------------------------------------------------------------------------------------------------------
-// epilogue helpers (8 warps; warp quadrant = warp_id % 4 is the TMEM lane group the hardware lets it read)
+// epilogue helpers (8 warps; warp quadrant = warp_id % 4 is the TMEM lane group the hardware lets it access)
 // ----------------------------------------------------------------------------------------------------------
 __device__ __forceinline__ float elu_fast(float x) {   // bf16 output: ex2.approx is far inside the tolerance
   return x > 0.f ? x : __expf(x) - 1.0f;
 }
 
-// 32 accumulator columns [col0, col0+32) of this thread's row -> +bias -> ELU -> bf16 -> 4 x 16-byte chunks of
-// the next layer's A operand ([kc][row][8] layout, kc = k / 8).
-__device__ __forceinline__ void epi_chunk_to_smem(uint32_t taddr, const float* __restrict__ bias, uint8_t* dst_kc0,
-                                                  int row) {
+// 32 fp32 accumulator columns of this thread's row -> +bias -> ELU -> 16 bf16 pairs
+__device__ __forceinline__ void epi_load_act(uint32_t taddr, const float* __restrict__ bias, uint32_t (&w)[16]) {
   uint32_t v[32];
   ptx::tmem_ld32(taddr, v);
   ptx::tmem_ld_wait();
 #pragma unroll
-  for (int j = 0; j < 4; ++j) {
-    uint32_t w[4];
-#pragma unroll
-    for (int e = 0; e < 4; ++e) {
-      const int c = j * 8 + e * 2;
-      const float a = elu_fast(__uint_as_float(v[c]) + bias[c]);
-      const float b = elu_fast(__uint_as_float(v[c + 1]) + bias[c + 1]);
-      w[e] = ptx::pack_bf16(a, b);
-    }
-    *reinterpret_cast<uint4*>(dst_kc0 + j * 2048 + row * 16) = make_uint4(w[0], w[1], w[2], w[3]);
+  for (int e = 0; e < 16; ++e) {
+    const float a = elu_fast(__uint_as_float(v[2 * e]) + bias[2 * e]);
+    const float b = elu_fast(__uint_as_float(v[2 * e + 1]) + bias[2 * e + 1]);
+    w[e] = ptx::pack_bf16(a, b);
   }
 }
+
+// Diagnostics (not part of the public ABI): per-phase %globaltimer stamps of CTA 0, read by profiles/tc_trace.py.
+__device__ unsigned long long g_tc_trace[64];
+__device__ __forceinline__ void tc_stamp(int slot) {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  g_tc_trace[slot] = t;
+}
+#define TC_STAMP(cond, slot) do { if (cond) tc_stamp(slot); } while (0)
 
 struct TcActArgs {
   const float* params;        // fp32 master (biases are read from it)
@@ -140,56 +145,57 @@ __global__ void __launch_bounds__(tc::kThreads, 1)
 tc_actor_kernel(const __grid_constant__ TcActArgs args) {
   using namespace tc;
   extern __shared__ __align__(1024) uint8_t smem[];
-  uint8_t* s_act1 = smem + kOffAct1;
+  uint8_t* s_w = smem + kOffW;
   uint8_t* s_ring = smem + kOffRing;
   uint8_t* s_x = smem + kOffX;
-  uint8_t* s_w = smem + kOffW;
   float* s_bias = reinterpret_cast<float*>(smem + kOffBias);
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + kOffBar);
-  uint64_t* w_full = bars;            // [3]
-  uint64_t* w_empty = bars + 3;       // [3]
-  uint64_t* x_ready = bars + 6;
-  uint64_t* d_full = bars + 7;        // [2]
-  uint64_t* d_empty = bars + 9;       // [2]
-  uint64_t* act1_ready = bars + 11;   // [4]
-  uint64_t* act2_ready = bars + 15;
-  uint64_t* act2_free = bars + 16;
-  uint64_t* d3_full = bars + 17;
-  uint64_t* act3_ready = bars + 18;
-  uint64_t* d4_full = bars + 19;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 20);
+  uint64_t* w_full = bars;                    // [10]
+  uint64_t* w_empty = bars + kStages;         // [10]
+  uint64_t* x_ready = bars + 2 * kStages;
+  uint64_t* d_full = x_ready + 1;             // [2]
+  uint64_t* d_empty = d_full + 2;             // [2]
+  uint64_t* act1_ready = d_empty + 2;
+  uint64_t* slot_ready = act1_ready + 1;      // [3]
+  uint64_t* slot_free = slot_ready + kRingSlots;   // [3]
+  uint64_t* d3_full = slot_free + kRingSlots;
+  uint64_t* act3_ready = d3_full + 1;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(act3_ready + 1);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int num_tiles = (int)((args.rows + kTileM - 1) / kTileM);
+  const bool tr = blockIdx.x == 0 && lane == 0;      // trace CTA 0
+  TC_STAMP(tr && warp == 2, 0);
 
   // ---- one-time setup
-  for (int i = threadIdx.x; i < kH0 + kH1 + kH2 + kOutPad; i += kThreads) {
-    const int64_t b0 = (int64_t)kH0 * args.in_dim, w1 = b0 + kH0, b1 = w1 + (int64_t)kH1 * kH0, w2 = b1 + kH1;
-    const int64_t b2 = w2 + (int64_t)kH2 * kH1, w3 = b2 + kH2, b3 = w3 + (int64_t)args.out_dim * kH2;
-    float v;
-    if (i < kH0) v = args.params[b0 + i];
-    else if (i < kH0 + kH1) v = args.params[b1 + i - kH0];
-    else if (i < kH0 + kH1 + kH2) v = args.params[b2 + i - kH0 - kH1];
-    else v = (i - kH0 - kH1 - kH2) < args.out_dim ? args.params[b3 + i - kH0 - kH1 - kH2] : 0.f;
-    s_bias[i] = v;
-  }
   if (threadIdx.x == 0) {
     for (int i = 0; i < kStages; ++i) { ptx::mbar_init(&w_full[i], 1); ptx::mbar_init(&w_empty[i], 1); }
     ptx::mbar_init(x_ready, kEpiWarps);
     for (int i = 0; i < 2; ++i) { ptx::mbar_init(&d_full[i], 1); ptx::mbar_init(&d_empty[i], kEpiWarps); }
-    for (int i = 0; i < 4; ++i) ptx::mbar_init(&act1_ready[i], kEpiWarps);
-    ptx::mbar_init(act2_ready, kEpiWarps);
-    ptx::mbar_init(act2_free, 1);
+    ptx::mbar_init(act1_ready, kEpiWarps * 8);
+    for (int i = 0; i < kRingSlots; ++i) { ptx::mbar_init(&slot_ready[i], kEpiWarps); ptx::mbar_init(&slot_free[i], 1); }
     ptx::mbar_init(d3_full, 1);
     ptx::mbar_init(act3_ready, kEpiWarps);
-    ptx::mbar_init(d4_full, 1);
     ptx::fence_barrier_init();
   }
   if (warp == 1) ptx::tmem_alloc<kTmemCols>(tmem_slot);
+  if (warp >= 2) {   // biases: fp32, straight from the master parameters
+    const int64_t b0 = (int64_t)kH0 * args.in_dim, w1 = b0 + kH0, b1 = w1 + (int64_t)kH1 * kH0, w2 = b1 + kH1;
+    const int64_t b2 = w2 + (int64_t)kH2 * kH1, w3 = b2 + kH2, b3 = w3 + (int64_t)args.out_dim * kH2;
+    for (int i = threadIdx.x - 64; i < kH0 + kH1 + kH2 + kOutPad; i += kThreads - 64) {
+      float v;
+      if (i < kH0) v = args.params[b0 + i];
+      else if (i < kH0 + kH1) v = args.params[b1 + i - kH0];
+      else if (i < kH0 + kH1 + kH2) v = args.params[b2 + i - kH0 - kH1];
+      else v = (i - kH0 - kH1 - kH2) < args.out_dim ? args.params[b3 + i - kH0 - kH1 - kH2] : 0.f;
+      s_bias[i] = v;
+    }
+  }
   ptx::tc_fence_before();
   __syncthreads();
   ptx::tc_fence_after();
   const uint32_t tmem = *tmem_slot;
+  TC_STAMP(tr && warp == 2, 1);
 
   if (warp == 0) {
     // ===================================================== producer: stream the weight image, tile after tile
@@ -206,20 +212,28 @@ tc_actor_kernel(const __grid_constant__ TcActArgs args) {
       }
     }
   } else if (warp == 1) {
-    // ===================================================== MMA issuer (one thread)
-    if (lane == 0) {
-      const uint32_t id128 = ptx::idesc_bf16(128, 128), id16 = ptx::idesc_bf16(128, 16);
-      const uint32_t a1 = ptx::smem_u32(s_act1), ring = ptx::smem_u32(s_ring), xs = ptx::smem_u32(s_x), ws = ptx::smem_u32(s_w);
+    // ===================================================== MMA issuer: the whole warp runs the (warp-uniform) control
+    // flow and the mbarrier waits; one elected lane issues tcgen05.mma / tcgen05.commit, so every operand is a
+    // uniform register and no per-instruction election loop is generated
+    {
+      const bool leader = ptx::elect_one();
+      const uint32_t id64 = ptx::idesc_bf16(128, 64), id128 = ptx::idesc_bf16(128, 128), id16 = ptx::idesc_bf16(128, 16);
+      constexpr uint32_t hi = ptx::smem_desc_hi(128);
+      const uint32_t ring = ptx::smem_u32(s_ring), xs = ptx::smem_u32(s_x), ws = ptx::smem_u32(s_w);
+      const uint32_t x_lo = ptx::smem_desc_lo(xs, 2048);
       uint32_t n = 0;            // weight stages consumed
-      uint32_t d_uses[2] = {0, 0};
-      uint32_t tiles_done = 0, a2_cnt = 0;
+      uint32_t d_uses[2] = {0, 0}, slot_uses[kRingSlots] = {0, 0, 0};
+      uint32_t tiles_done = 0;
       auto wait_stage = [&]() -> uint32_t {
         const int slot = n % kStages;
         ptx::mbar_wait(&w_full[slot], (n / kStages) & 1);
         ptx::tc_fence_after();
         return ws + slot * kStageBytes;
       };
-      auto release_stage = [&]() { ptx::mma_commit(&w_empty[n % kStages]); ++n; };
+      auto release_stage = [&]() {
+        if (leader) ptx::mma_commit(&w_empty[n % kStages]);
+        ++n;
+      };
       auto acquire_d = [&](int b) {
         ptx::mbar_wait(&d_empty[b], (d_uses[b] & 1) ^ 1);
         ptx::tc_fence_after();
@@ -227,69 +241,95 @@ tc_actor_kernel(const __grid_constant__ TcActArgs args) {
       };
       for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++tiles_done) {
         const uint32_t tpar = tiles_done & 1;
-        // ---- layer 1: X[128,16] x W1^T, four 128-column pieces
+        // ---- layer 1: X[128,16] (smem) x W1^T, eight 64-column pieces
         ptx::mbar_wait(x_ready, tpar);
         ptx::tc_fence_after();
+        TC_STAMP(tr && tiles_done == 0, 32);
         {
-          const uint32_t w = wait_stage();
-          for (int q = 0; q < 4; ++q) {
+          const uint32_t w_lo = ptx::smem_desc_lo(wait_stage(), 8192);
+          TC_STAMP(tr && tiles_done == 0, 33);
+#pragma unroll
+          for (int q = 0; q < 8; ++q) {
             acquire_d(q & 1);
-            ptx::mma_ss(tmem + kColD + (q & 1) * 128, ptx::smem_desc(xs, 2048, 128),
-                        ptx::smem_desc(w + q * 2048, 8192, 128), id128, false);
-            ptx::mma_commit(&d_full[q & 1]);
+            if (leader) {
+              ptx::mma_ss(tmem + kColD + (q & 1) * 64, ptx::make_desc(x_lo, hi), ptx::make_desc(w_lo + q * (1024 >> 4), hi), id64, false);
+              ptx::mma_commit(&d_full[q & 1]);
+            }
+            __syncwarp();
           }
           release_stage();
         }
-        auto l2_piece = [&](int q) {
+        auto l2_piece = [&](int q) {     // act1 (TMEM) x W2[64q .. 64q+64, :]^T
           acquire_d(q & 1);
-          const uint32_t d = tmem + kColD + (q & 1) * 128;
-          for (int kb = 0; kb < 8; ++kb) {
-            const uint32_t w = wait_stage();
+          const uint32_t d = tmem + kColD + (q & 1) * 64;
 #pragma unroll
-            for (int ks = 0; ks < 4; ++ks)
-              ptx::mma_ss(d, ptx::smem_desc(a1 + (kb * 4 + ks) * 4096, 2048, 128), ptx::smem_desc(w + ks * 4096, 2048, 128),
-                          id128, (kb | ks) != 0);
+          for (int kb = 0; kb < 4; ++kb) {
+            const uint32_t w_lo = ptx::smem_desc_lo(wait_stage(), 1024);
+            if (leader) {
+#pragma unroll
+              for (int j = 0; j < 8; ++j)
+                ptx::mma_ts(d, tmem + kColAct + (kb * 8 + j) * 8, ptx::make_desc(w_lo + j * (2048 >> 4), hi), id64, (kb | j) != 0);
+            }
+            __syncwarp();
             release_stage();
           }
-          ptx::mma_commit(&d_full[q & 1]);
+          if (leader) ptx::mma_commit(&d_full[q & 1]);
+          __syncwarp();
         };
-        auto l3_partial = [&](int p) {
-          ptx::mbar_wait(act2_ready, a2_cnt & 1);
-          ++a2_cnt;
+        auto l3_partial = [&](int p) {   // act2[:, 64p .. 64p+64] (smem slice) x W3[:, 64p .. 64p+64]^T
+          const int slot = p % kRingSlots;
+          ptx::mbar_wait(&slot_ready[slot], slot_uses[slot] & 1);
+          ++slot_uses[slot];
           ptx::tc_fence_after();
-          for (int h = 0; h < 2; ++h) {
-            const uint32_t w = wait_stage();
+          const uint32_t w_lo = ptx::smem_desc_lo(wait_stage(), 2048);
+          const uint32_t a_lo = ptx::smem_desc_lo(ring + slot * 16384, 2048);
+          if (leader) {
 #pragma unroll
-            for (int ks = 0; ks < 4; ++ks)
-              ptx::mma_ss(tmem + kColD3, ptx::smem_desc(ring + (h * 4 + ks) * 4096, 2048, 128),
-                          ptx::smem_desc(w + ks * 4096, 2048, 128), id128, (p | h | ks) != 0);
-            release_stage();
+            for (int j = 0; j < 4; ++j)
+              ptx::mma_ss(tmem + kColD3, ptx::make_desc(a_lo + j * (4096 >> 4), hi), ptx::make_desc(w_lo + j * (4096 >> 4), hi), id128,
+                          (p | j) != 0);
           }
-          ptx::mma_commit(act2_free);
-          if (p == 3) ptx::mma_commit(d3_full);
+          __syncwarp();
+          release_stage();
+          if (leader) {
+            ptx::mma_commit(&slot_free[slot]);
+            if (p == 7) ptx::mma_commit(d3_full);
+          }
+          __syncwarp();
         };
-        // ---- layer 2 (+ layer-3 partial products one slice behind)
-        for (int q = 0; q < 4; ++q) { ptx::mbar_wait(&act1_ready[q], tpar); }
+        // ---- layer 2 (+ layer-3 partial products one piece behind)
+        TC_STAMP(tr && tiles_done == 0, 34);
+        ptx::mbar_wait(act1_ready, tpar);
         ptx::tc_fence_after();
+        TC_STAMP(tr && tiles_done == 0, 35);
         l2_piece(0);
+        TC_STAMP(tr && tiles_done == 0, 36);
         l2_piece(1);
-        l3_partial(0);
-        l2_piece(2);
-        l3_partial(1);
-        l2_piece(3);
-        l3_partial(2);
-        l3_partial(3);
-        // ---- layer 4: act3[128,128] x W4^T (N padded to 16)
+#pragma unroll
+        for (int q = 2; q < 8; ++q) {
+          l3_partial(q - 2);
+          l2_piece(q);
+        }
+        TC_STAMP(tr && tiles_done == 0, 37);
+        l3_partial(6);
+        l3_partial(7);
+        TC_STAMP(tr && tiles_done == 0, 38);
+        // ---- layer 4: act3 (TMEM) x W4^T (N padded to 16) into accumulator buffer 0
         ptx::mbar_wait(act3_ready, tpar);
         ptx::tc_fence_after();
         {
-          const uint32_t w = wait_stage();
+          acquire_d(0);
+          const uint32_t w_lo = ptx::smem_desc_lo(wait_stage(), 256);
+          if (leader) {
 #pragma unroll
-          for (int ks = 0; ks < 8; ++ks)
-            ptx::mma_ss(tmem + kColD4, ptx::smem_desc(ring + ks * 4096, 2048, 128), ptx::smem_desc(w + ks * 512, 256, 128),
-                        id16, ks != 0);
+            for (int j = 0; j < 8; ++j)
+              ptx::mma_ts(tmem + kColD, tmem + kColAct + j * 8, ptx::make_desc(w_lo + j * (512 >> 4), hi), id16, j != 0);
+          }
+          __syncwarp();
           release_stage();
-          ptx::mma_commit(d4_full);
+          if (leader) ptx::mma_commit(&d_full[0]);
+          __syncwarp();
+          TC_STAMP(tr && tiles_done == 0, 39);
         }
       }
     }
@@ -297,24 +337,24 @@ tc_actor_kernel(const __grid_constant__ TcActArgs args) {
     // ===================================================== epilogue warps
     const int e = warp - 2;                 // 0..7
     const int quad = warp & 3;              // TMEM lane quadrant this warp may access
-    const int half = e >> 2;                // which 64 of the piece's 128 columns
+    const int half = e >> 2;                // which 32 of a piece's 64 columns
     const int row = quad * 32 + lane;       // row of the tile == TMEM lane
     const uint32_t t_lane = tmem + ((uint32_t)(quad * 32) << 16);
-    float mu[16], inv[16];
     const bool has_scaler = args.mean != nullptr;
-    for (int c = 0; c < args.in_dim && c < 16; ++c) {
-      mu[c] = has_scaler ? (float)args.mean[c] : 0.f;
-      inv[c] = has_scaler ? __fadd_rn(sqrtf((float)args.var[c]), 1e-8f) : 1.f;
-    }
-    uint32_t d_cnt[2] = {0, 0}, tiles_done = 0, free_cnt = 0;
+    uint32_t d_cnt[2] = {0, 0}, slot_cnt[kRingSlots] = {0, 0, 0}, tiles_done = 0;
     auto warp_arrive = [&](uint64_t* bar) {
       __syncwarp();
       if (lane == 0) ptx::mbar_arrive(bar);
     };
+    auto wait_d = [&](int b) {
+      ptx::mbar_wait(&d_full[b], d_cnt[b] & 1);
+      ++d_cnt[b];
+      ptx::tc_fence_after();
+    };
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++tiles_done) {
       const uint32_t tpar = tiles_done & 1;
       const int64_t grow = (int64_t)tile * kTileM + row;
-      // ---- X: scaler + bf16, K padded to 16 (half 0 warps write kc 0, half 1 warps kc 1)
+      // ---- X: scaler + bf16, K padded to 16 (half-0 warps write k 0..7, half-1 warps k 8..15)
       {
         float x[8];
 #pragma unroll
@@ -323,7 +363,8 @@ tc_actor_kernel(const __grid_constant__ TcActArgs args) {
           float v = 0.f;
           if (c < args.in_dim && grow < args.rows) {
             v = args.io.states[grow * args.in_dim + c];
-            if (has_scaler) v = fminf(fmaxf(__fdiv_rn(__fsub_rn(v, mu[c]), inv[c]), -5.0f), 5.0f);
+            if (has_scaler)
+              v = fminf(fmaxf(__fdiv_rn(__fsub_rn(v, (float)args.mean[c]), __fadd_rn(sqrtf((float)args.var[c]), 1e-8f)), -5.0f), 5.0f);
           }
           x[j] = v;
         }
@@ -331,62 +372,59 @@ tc_actor_kernel(const __grid_constant__ TcActArgs args) {
             make_uint4(ptx::pack_bf16(x[0], x[1]), ptx::pack_bf16(x[2], x[3]), ptx::pack_bf16(x[4], x[5]), ptx::pack_bf16(x[6], x[7]));
         ptx::fence_async_smem();
         warp_arrive(x_ready);
+        TC_STAMP(tr && warp == 2 && tiles_done == 0, 2);
       }
-      // ---- layer 1 pieces -> act1
-      for (int q = 0; q < 4; ++q) {
+      // ---- layer 1 pieces -> act1 (TMEM, bf16 pairs)
+      for (int q = 0; q < 8; ++q) {
         const int b = q & 1;
-        ptx::mbar_wait(&d_full[b], d_cnt[b] & 1);
-        ++d_cnt[b];
-        ptx::tc_fence_after();
-#pragma unroll
-        for (int c = 0; c < 2; ++c) {
-          const int col = half * 64 + c * 32;                 // column inside the piece
-          epi_chunk_to_smem(t_lane + kColD + b * 128 + col, s_bias + q * 128 + col, s_act1 + ((q * 128 + col) >> 3) * 2048, row);
-        }
+        wait_d(b);
+        uint32_t w[16];
+        epi_load_act(t_lane + kColD + b * 64 + half * 32, s_bias + q * 64 + half * 32, w);
+        ptx::tmem_st16(t_lane + kColAct + q * 32 + half * 16, w);
+        ptx::tmem_st_wait();
         ptx::tc_fence_before();
-        ptx::fence_async_smem();
         warp_arrive(&d_empty[b]);
-        warp_arrive(&act1_ready[q]);
+        warp_arrive(act1_ready);
+        TC_STAMP(tr && warp == 2 && tiles_done == 0, 3 + q);
       }
-      // ---- layer 2 pieces -> ring (one 128-column slice of act2 at a time)
-      for (int q = 0; q < 4; ++q) {
-        const int b = q & 1;
-        ptx::mbar_wait(&d_full[b], d_cnt[b] & 1);
-        ++d_cnt[b];
-        ptx::tc_fence_after();
-        if (q > 0) {   // the previous slice has been consumed by its layer-3 partial product
-          ptx::mbar_wait(act2_free, free_cnt & 1);
-          ++free_cnt;
-        }
-#pragma unroll
-        for (int c = 0; c < 2; ++c) {
-          const int col = half * 64 + c * 32;
-          epi_chunk_to_smem(t_lane + kColD + b * 128 + col, s_bias + kH0 + q * 128 + col, s_ring + (col >> 3) * 2048, row);
-        }
+      // ---- layer 2 pieces -> one 64-column slice of act2 each, in the shared-memory ring
+      for (int q = 0; q < 8; ++q) {
+        const int b = q & 1, slot = q % kRingSlots;
+        wait_d(b);
+        uint32_t w[16];
+        epi_load_act(t_lane + kColD + b * 64 + half * 32, s_bias + kH0 + q * 64 + half * 32, w);
         ptx::tc_fence_before();
+        warp_arrive(&d_empty[b]);                                           // accumulator drained
+        ptx::mbar_wait(&slot_free[slot], (slot_cnt[slot] & 1) ^ 1);         // previous user of the slot consumed
+        ++slot_cnt[slot];
+        uint8_t* dst = s_ring + slot * 16384 + (half * 4) * 2048 + row * 16;
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+          *reinterpret_cast<uint4*>(dst + j * 2048) = make_uint4(w[4 * j], w[4 * j + 1], w[4 * j + 2], w[4 * j + 3]);
         ptx::fence_async_smem();
-        warp_arrive(&d_empty[b]);
-        warp_arrive(act2_ready);
+        warp_arrive(&slot_ready[slot]);
+        TC_STAMP(tr && warp == 2 && tiles_done == 0, 11 + q);
       }
-      // ---- layer 3 -> ring (act3)
-      ptx::mbar_wait(act2_free, free_cnt & 1);   // completion of the 4th partial product (keeps the phase count in step)
-      ++free_cnt;
+      // ---- layer 3 -> act3 (TMEM columns 0..63; act1 is dead: every layer-2 MMA has completed)
       ptx::mbar_wait(d3_full, tpar);
       ptx::tc_fence_after();
+      TC_STAMP(tr && warp == 2 && tiles_done == 0, 19);
 #pragma unroll
       for (int c = 0; c < 2; ++c) {
-        const int col = half * 64 + c * 32;
-        epi_chunk_to_smem(t_lane + kColD3 + col, s_bias + kH0 + kH1 + col, s_ring + (col >> 3) * 2048, row);
+        uint32_t w[16];
+        epi_load_act(t_lane + kColD3 + half * 64 + c * 32, s_bias + kH0 + kH1 + half * 64 + c * 32, w);
+        ptx::tmem_st16(t_lane + kColAct + half * 32 + c * 16, w);
       }
+      ptx::tmem_st_wait();
       ptx::tc_fence_before();
-      ptx::fence_async_smem();
       warp_arrive(act3_ready);
+      TC_STAMP(tr && warp == 2 && tiles_done == 0, 20);
       // ---- layer 4 -> output activation -> exploration -> actions
-      ptx::mbar_wait(d4_full, tpar);
-      ptx::tc_fence_after();
+      wait_d(0);
+      TC_STAMP(tr && warp == 2 && tiles_done == 0, 21);
       if (half == 0) {
         uint32_t v[16];
-        ptx::tmem_ld16(t_lane + kColD4, v);
+        ptx::tmem_ld16(t_lane + kColD, v);
         ptx::tmem_ld_wait();
         float mx = -INFINITY, mn = INFINITY, sm = 0.f;
         if (grow < args.rows) {
@@ -410,6 +448,8 @@ tc_actor_kernel(const __grid_constant__ TcActArgs args) {
         if (args.io.noise_stats && args.io.ou_state && args.io.noise_scale >= 0.f) noise_stats_warp(args.io, mx, mn, sm);
       }
       ptx::tc_fence_before();
+      warp_arrive(&d_empty[0]);
+      TC_STAMP(tr && warp == 2 && tiles_done == 0, 22);
     }
   }
   // ---- teardown
@@ -486,3 +526,9 @@ int tc_actor_forward(OisAgent* a, const float* actor_params, const OisScaler* sc
 }
 
 }  // namespace ois
+
+// diagnostics hook for profiles/tc_trace.py (deliberately not declared in include/ois_b200.h)
+extern "C" int ois_debug_tc_trace(unsigned long long* out_host, int n) {
+  if (n > 64) n = 64;
+  return cudaMemcpyFromSymbol(out_host, ois::g_tc_trace, sizeof(unsigned long long) * n) == cudaSuccess ? 0 : -2;
+}

@@ -1,0 +1,42 @@
+"""Summarise an `ncu --set full` report: python profiles/ncu_raw_extract.py <file.ncu-rep> [more.ncu-rep ...]
+Prints, per profiled launch, the counters DESIGN.md / bench.py quote (duration, DRAM bytes, pipe activity)."""
+import csv
+import io
+import subprocess
+import sys
+
+WANT = [
+    ("gpu__time_duration.sum", "duration"),
+    ("launch__grid_size", "grid"),
+    ("launch__block_size", "block"),
+    ("launch__registers_per_thread", "regs/thread"),
+    ("dram__bytes_read.sum", "dram read"),
+    ("dram__bytes_write.sum", "dram write"),
+    ("gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed", "dram % of peak"),
+    ("lts__t_bytes.sum", "L2 bytes"),
+    ("sm__throughput.avg.pct_of_peak_sustained_elapsed", "sm throughput %"),
+    ("sm__warps_active.avg.pct_of_peak_sustained_active", "warps active %"),
+    ("smsp__inst_executed.sum", "warp instructions"),
+    ("sm__pipe_tensor_subpipe_hmma_cycles_active.avg.pct_of_peak_sustained_active", "tensor (hmma) pipe active %"),
+    ("sm__inst_executed_pipe_xu.avg.pct_of_peak_sustained_active", "xu (MUFU) pipe %"),
+    ("sm__inst_executed_pipe_fma.avg.pct_of_peak_sustained_active", "fma pipe %"),
+    ("smsp__issue_active.avg.pct_of_peak_sustained_active", "issue slots busy %"),
+]
+
+
+def main():
+    for path in sys.argv[1:]:
+        out = subprocess.run(["ncu", "-i", path, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
+        rows = list(csv.reader(io.StringIO(out)))
+        head, units = rows[0], rows[1]
+        print(f"## {path}")
+        for r in rows[2:]:
+            print(f"- {r[head.index('Kernel Name')][:60]}")
+            for key, label in WANT:
+                if key in head:
+                    i = head.index(key)
+                    print(f"    {label:32s} {r[i]:>16s} {units[i]}")
+
+
+if __name__ == "__main__":
+    main()

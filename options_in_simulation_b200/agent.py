@@ -28,6 +28,7 @@ import numpy as np
 import torch
 
 from . import _lib as L
+from . import parallel as P
 
 DDPG_DEFAULT_CONFIG = {   # src/my_agents/ddpg.py:19-61
     "gradient_steps": 1,
@@ -66,8 +67,8 @@ def _space_size(space) -> int:
 
 def distributed_info():
     """skrl.config.torch.{is_distributed, rank, local_rank, world_size} (read from the torchrun env)."""
-    ws = int(os.environ.get("WORLD_SIZE", "1"))
-    return ws > 1, int(os.environ.get("RANK", "0")), int(os.environ.get("LOCAL_RANK", "0")), ws
+    d = P.distributed_info()
+    return d.is_distributed, d.rank, d.local_rank, d.world_size
 
 
 # ------------------------------------------------------------------------------------------- models
@@ -141,7 +142,11 @@ class DeterministicMLP:
             self.flat.mul_(1 - polyak).add_(model.flat, alpha=polyak)
 
     def broadcast_parameters(self, rank=0):
-        torch.distributed.broadcast(self.flat, rank)
+        P.broadcast_flat(self.flat, rank)
+
+    def reduce_parameters(self, flat_grad):
+        """skrl Model.reduce_parameters on the flat gradient buffer; returns the 1/world_size factor to apply."""
+        return P.all_reduce_gradients(flat_grad)
 
     def random_act(self, inputs, role=""):
         raise L.OisError("random_act is served by DDPG.act (fused explore kernel)")
@@ -301,8 +306,7 @@ class DDPG:
                                    "target_critic": self.target_critic}
         self.is_distributed, self.rank, self.local_rank, self.world_size = distributed_info()
         if self.is_distributed:   # ddpg.py:122-127 / base.py:88-92
-            if not torch.distributed.is_initialized():
-                torch.distributed.init_process_group("nccl")
+            P.ensure_process_group("nccl")
             self.policy.broadcast_parameters()
             self.critic.broadcast_parameters()
         self.target_policy.freeze_parameters(True)       # ddpg.py:129-136
@@ -571,6 +575,11 @@ class DDPG:
             self.set_mode("train")
             self._update(timestep, timesteps)
             self.set_mode("eval")
+        self.base_post_interaction(timestep, timesteps)
+
+    def base_post_interaction(self, timestep, timesteps):
+        """skrl Agent.post_interaction (base.py:645-669), which single_agent_eval calls directly
+        (base_KA_DDPG.py:334) to skip ``_update``."""
         timestep += 1
         if self.checkpoint_interval > 0 and not timestep % self.checkpoint_interval:
             self.write_checkpoint(timestep, timesteps)
@@ -608,10 +617,10 @@ class DDPG:
             stream = L.current_stream()
             L.check(lib.ois_ddpg_update_phase(self._handle, self._scaler_ref(), C.byref(io), 0, scale, stream))
             if self.is_distributed:   # critic.reduce_parameters(), ddpg.py:409-410
-                torch.distributed.all_reduce(self._grad_critic, op=torch.distributed.ReduceOp.SUM)
+                self.critic.reduce_parameters(self._grad_critic)
             L.check(lib.ois_ddpg_update_phase(self._handle, self._scaler_ref(), C.byref(io), 1, scale, stream))
             if self.is_distributed:   # policy.reduce_parameters(), ddpg.py:431-432
-                torch.distributed.all_reduce(self._grad_actor, op=torch.distributed.ReduceOp.SUM)
+                self.policy.reduce_parameters(self._grad_actor)
             L.check(lib.ois_ddpg_update_phase(self._handle, self._scaler_ref(), C.byref(io), 2, scale, stream))
             self._updates += 1
             self.kernel_launches += UPDATE_LAUNCHES + (0 if self._state_preprocessor is not None else 0)

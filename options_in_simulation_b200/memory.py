@@ -8,6 +8,8 @@ Tensors are ``(memory_size, num_envs, dim)`` in HBM; append and gather are CUDA 
 """
 from __future__ import annotations
 
+import collections
+
 import torch
 
 from . import _lib as L
@@ -36,6 +38,7 @@ class Memory:
         self._draws = 0
         self.kernel_launches = 0
         self._out = None
+        self._supplied_indexes = collections.deque()
 
     def __len__(self) -> int:   # skrl Memory.__len__
         return self.memory_size * self.num_envs if self.filled else self.memory_index * self.num_envs + self.env_index
@@ -99,9 +102,18 @@ class Memory:
         by_name = dict(zip(_NAMES, out))
         return [[by_name[n] for n in names]]
 
+    def supply_indexes(self, index_sets) -> None:
+        """Parity mode: the next ``sample`` calls use these index vectors (what the reference's host
+        ``torch.randperm(len)[:B]`` produced) instead of drawing their own."""
+        self._supplied_indexes.extend(torch.as_tensor(i, dtype=torch.int64) for i in index_sets)
+
     def sample(self, names, batch_size: int, mini_batches: int = 1, sequence_length: int = 1):
         size = len(self)
-        if self.sampler == "device":
+        if self._supplied_indexes:
+            idx = self._supplied_indexes.popleft()
+            if idx.numel() != batch_size or int(idx.max()) >= size:
+                raise L.OisError("supplied sampling indexes do not fit this memory / batch size")
+        elif self.sampler == "device":
             idx = torch.empty(batch_size, dtype=torch.int64, device=self.device)
             L.check(L.lib().ois_replay_sample_indices(L.ptr(idx), batch_size, size, self._seed, self._draws,
                                                       L.current_stream()))

@@ -33,7 +33,8 @@ def subsample(flat: torch.Tensor) -> np.ndarray:
     return flat[::STRIDE].numpy().copy()
 
 
-def build_reference_agent(obs_dim, act_dim, out_act, batch, base_scale, clip_low, T_e, lr_a, lr_c, discount, polyak, rows):
+def build_reference_agent(obs_dim, act_dim, out_act, batch, base_scale, clip_low, T_e, lr_a, lr_c, discount, polyak, rows,
+                          *, n_envs=64, random_timesteps=10, learning_starts=10, timesteps=1000):
     from oracle.ref_harness import stubs
 
     stubs.install()
@@ -68,7 +69,6 @@ def build_reference_agent(obs_dim, act_dim, out_act, batch, base_scale, clip_low
     models = {"policy": DeterministicActor(obs_space, act_space, "cpu"),
               "target_policy": DeterministicActor(obs_space, act_space, "cpu"),
               "critic": Critic(obs_space, act_space, "cpu"), "target_critic": Critic(obs_space, act_space, "cpu")}
-    n_envs = 64
     memory = sk.RandomMemory(memory_size=rows // n_envs, num_envs=n_envs, device="cpu", replacement=False)
     from my_agents.ddpg import DDPG_DEFAULT_CONFIG
     import copy
@@ -78,13 +78,13 @@ def build_reference_agent(obs_dim, act_dim, out_act, batch, base_scale, clip_low
     cfg["exploration"]["final_scale"] = 1e-4
     cfg["exploration"]["timesteps"] = T_e
     cfg.update(gradient_steps=1, batch_size=batch, discount_factor=discount, polyak=polyak, actor_learning_rate=lr_a,
-               critic_learning_rate=lr_c, random_timesteps=10, learning_starts=10,
+               critic_learning_rate=lr_c, random_timesteps=random_timesteps, learning_starts=learning_starts,
                state_preprocessor=sk.RunningStandardScaler,
                state_preprocessor_kwargs={"size": obs_space, "device": "cpu"})
     cfg["experiment"]["write_interval"] = 0
     cfg["experiment"]["checkpoint_interval"] = 0
     agent = DDPG(models=models, memory=memory, cfg=cfg, observation_space=obs_space, action_space=act_space, device="cpu")
-    agent.init({"timesteps": 1000})
+    agent.init({"timesteps": timesteps})
     return agent, memory, n_envs
 
 

@@ -92,7 +92,7 @@ typedef struct OisEnvIO {
   const float* reset_uniforms;  /* [N,8] draws of reset_idx in reference order, or NULL -> Philox */
   uint64_t philox_seed, philox_offset;
   /* outputs */
-  float* obs;                   /* [N,6] in/out: read as the previous observation when replay_states != NULL */
+  float* obs;                   /* [N,6] in/out (raw obs_buf): read as the previous observation when replay_states != NULL */
   float* rew;                   /* [N]   rew_buf */
   uint8_t* reset;               /* [N]   reset_buf (bool) */
   float* wheel_torqs;           /* [N,4] clipped torques */
@@ -113,8 +113,12 @@ typedef struct OisEnvIO {
   uint8_t* replay_terminated;   /* [N] */
   uint8_t* replay_truncated;    /* [N] (always 0: the wrapper finds no time_outs) */
   int32_t relabel;              /* OIS_RELABEL_* */
-  float clip_obs;               /* > 0: clamp the stored observations to +-clip_obs, as the env wrapper does
-                                   (clipObservations, KAMMA_medium.py:42, rl_task.py:99); <= 0: raw obs_buf */
+  float clip_obs;               /* > 0: +-clamp applied to obs_clipped and to the replay rows, as the env wrapper does
+                                   (clipObservations, KAMMA_medium.py:42, rl_task.py:99); <= 0: no clamp */
+  float clip_actions;           /* > 0: actions are clamped to +-clip_actions before use, as VecEnvRLGames.step does
+                                   (clipActions, rl_task.py:100); <= 0: no clamp */
+  float* obs_clipped;           /* [N,6] nullable: clamp(obs, +-clip_obs) — what the env wrapper hands to the agent;
+                                   `obs` itself stays the raw obs_buf */
 } OisEnvIO;
 
 /* One policy step for all envs: pre_physics_step + decimation physics sub-steps + post_physics_step

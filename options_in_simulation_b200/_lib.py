@@ -52,6 +52,7 @@ class EnvIO(C.Structure):
         ("guiding", _p), ("ep_stats", _p), ("comp0", _p), ("any_reset_flags", _p), ("flag_slot", _i32),
         ("replay_states", _p), ("replay_actions", _p), ("replay_rewards", _p), ("replay_next_states", _p),
         ("replay_terminated", _p), ("replay_truncated", _p), ("relabel", _i32), ("clip_obs", _f),
+        ("clip_actions", _f), ("obs_clipped", _p),
     ]
 
 

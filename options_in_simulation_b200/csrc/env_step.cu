@@ -35,60 +35,93 @@ struct Skid {
 // `decimation` linearly-implicit sub-steps of the planar skid-steer model under constant torques.
 // Equations: oracle/dynamics_twin.py (increment form).  Wheel order fl, rl, fr, rr:
 // x = (+a, -a, +a, -a), y = (+b, +b, -b, -b).
+//
+// The kernel is issue-bound, not HBM-bound (profiles/r01_ncu_full_summary.txt), so the sub-step is written
+// for instruction count: the two wheels of an axle travel as one packed float2 (lane x = left, y = right)
+// through Blackwell's FFMA2 / FMUL2 / FADD2; reciprocals are MUFU.RCP + one Newton step (2 FMA, no IEEE
+// slow path); the slip norm uses MUFU.RSQ directly.
 // ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ float2 fma2(float2 a, float2 b, float2 c) { return __ffma2_rn(a, b, c); }
+__device__ __forceinline__ float2 mul2(float2 a, float2 b) { return __fmul2_rn(a, b); }
+__device__ __forceinline__ float2 add2(float2 a, float2 b) { return __fadd2_rn(a, b); }
+__device__ __forceinline__ float2 bc(float s) { return make_float2(s, s); }
+__device__ __forceinline__ float2 neg2(float2 a) { return make_float2(-a.x, -a.y); }
+__device__ __forceinline__ float mufu_rcp(float x) { float r; asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
+__device__ __forceinline__ float mufu_rsq(float x) { float r; asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
+// 1/x for two lanes: MUFU seed + one Newton step, r <- r + r (1 - x r)
+__device__ __forceinline__ float2 rcp2(float2 x) {
+  const float2 r = make_float2(mufu_rcp(x.x), mufu_rcp(x.y));
+  return fma2(r, fma2(neg2(x), r, bc(1.0f)), r);
+}
+__device__ __forceinline__ float rcp1(float x) {
+  const float r = mufu_rcp(x);
+  return fmaf(r, fmaf(-x, r, 1.0f), r);
+}
+
+struct AxleOut { float2 al, be, k, g, phi, kl; };
+
+// one axle (x position xi, lateral contact speed l): the left (y=+b) and right (y=-b) wheels in the two lanes
+__device__ __forceinline__ AxleOut axle(float2 w, float2 tau, float2 nu /* -(uL, uR) */, float l, float2 R2, float2 RR2,
+                                        float2 Iwh2, float2 nc2, float2 mu2, float eps2) {
+  AxleOut o;
+  const float2 sx = fma2(R2, w, nu);                       // R w - u
+  const float2 n2 = fma2(sx, sx, bc(fmaf(l, l, eps2)));
+  const float2 k = mul2(make_float2(mufu_rsq(n2.x), mufu_rsq(n2.y)), mu2);
+  const float2 inv = rcp2(fma2(RR2, k, Iwh2));             // 1 / (Iw/h + c + R^2 k)
+  const float2 Rk = mul2(R2, k);
+  o.al = mul2(fma2(neg2(Rk), sx, fma2(nc2, w, tau)), inv);  // (tau - c w - R k sx) / E
+  o.be = mul2(Rk, inv);
+  o.g = mul2(mul2(k, Iwh2), inv);
+  o.phi = mul2(k, fma2(R2, o.al, sx));
+  o.kl = mul2(k, bc(l));
+  o.k = k;
+  return o;
+}
+
 __device__ __forceinline__ void skid_steps(Skid& s, const float tau[4], const OisEnvParams& p) {
   const float h = p.sim_dt, R = p.wheel_radius, c = p.wheel_damping;
   const float a = p.half_wheelbase, b = p.half_track;
   const float m = p.mass;
   const float m_h = m / h, J_h = p.yaw_inertia / h, Iw_h = p.wheel_inertia / h + c;
-  const float eps2 = p.slip_eps * p.slip_eps, R2 = R * R, aa = a * a, bb = b * b;
+  const float eps2 = p.slip_eps * p.slip_eps, aa = a * a, bb = b * b;
   const float wmax = p.wheel_speed_max;
+  const float2 R2 = bc(R), RR2 = bc(R * R), Iwh2 = bc(Iw_h), nc2 = bc(-c), mu2 = bc(p.mu_n);
+  const float2 side = make_float2(-b, b);                  // u' - u = dvx -+ dr b  (left, right)
+  float2 wF = make_float2(s.w[0], s.w[2]), wB = make_float2(s.w[1], s.w[3]);   // front / rear axle, (left, right)
+  const float2 tF = make_float2(tau[0], tau[2]), tB = make_float2(tau[1], tau[3]);
   float sn, cs;
   sincosf(s.yaw, &sn, &cs);
 #pragma unroll 1
   for (int it = 0; it < p.decimation; ++it) {
     const float vx = s.vx, vy = s.vy, r = s.r;
-    const float uL = vx - r * b, uR = vx + r * b;   // contact longitudinal speed, left (y=+b) / right (y=-b)
-    const float lF = vy + r * a, lB = vy - r * a;   // contact lateral speed, front (x=+a) / rear (x=-a)
-    float A00 = m_h, A11 = m_h, A22 = J_h, A02 = 0.f, A12 = 0.f;
-    float b0 = m * (r * vy), b1 = -(m * (r * vx)), b2 = 0.f;
-    float al[4], be[4];
-#pragma unroll
-    for (int i = 0; i < 4; ++i) {
-      const float xi = (i & 1) ? -a : a;
-      const float yi = (i & 2) ? -b : b;
-      const float u = (i & 2) ? uR : uL;
-      const float l = (i & 1) ? lB : lF;
-      const float sx = R * s.w[i] - u;
-      const float k = p.mu_n * rsqrtf(sx * sx + l * l + eps2);
-      const float invE = __frcp_rn(Iw_h + R2 * k);
-      const float Rk = R * k;
-      al[i] = (tau[i] - c * s.w[i] - Rk * sx) * invE;
-      be[i] = Rk * invE;
-      const float g = k * Iw_h * invE;
-      const float phi = k * (sx + R * al[i]);
-      const float kl = k * l;
-      A00 += g;
-      A11 += k;
-      A22 += aa * k + bb * g;
-      A02 -= yi * g;
-      A12 += xi * k;
-      b0 += phi;
-      b1 -= kl;
-      b2 -= xi * kl + yi * phi;
-    }
-    const float i00 = __frcp_rn(A00), i11 = __frcp_rn(A11);
-    const float s22 = A22 - A02 * A02 * i00 - A12 * A12 * i11;
-    const float dr = (b2 - A02 * b0 * i00 - A12 * b1 * i11) * __frcp_rn(s22);
-    const float dvx = (b0 - A02 * dr) * i00;
-    const float dvy = (b1 - A12 * dr) * i11;
+    const float2 nu = fma2(bc(r), make_float2(b, -b), bc(-vx));   // -(vx - r b), -(vx + r b)
+    const AxleOut F = axle(wF, tF, nu, fmaf(r, a, vy), R2, RR2, Iwh2, nc2, mu2, eps2);
+    const AxleOut B = axle(wB, tB, nu, fmaf(-r, a, vy), R2, RR2, Iwh2, nc2, mu2, eps2);
+    const float2 G = add2(F.g, B.g), K = add2(F.k, B.k), KD = add2(F.k, neg2(B.k));
+    const float2 PH = add2(F.phi, B.phi), KL = add2(F.kl, B.kl), KLD = add2(F.kl, neg2(B.kl));
+    const float gs = G.x + G.y, ks = K.x + K.y;
+    const float A00 = m_h + gs, A11 = m_h + ks;
+    const float A22 = fmaf(bb, gs, fmaf(aa, ks, J_h));
+    const float A02 = -b * (G.x - G.y);                      // -sum y_i g_i
+    const float A12 = a * (KD.x + KD.y);                     //  sum x_i k_i
+    const float b0 = fmaf(m * r, vy, PH.x + PH.y);
+    const float b1 = -fmaf(m * r, vx, KL.x + KL.y);
+    const float b2 = -fmaf(a, KLD.x + KLD.y, b * (PH.x - PH.y));
+    const float2 iA = rcp2(make_float2(A00, A11));
+    const float e0 = A02 * iA.x, e1 = A12 * iA.y;
+    const float s22 = fmaf(-A12, e1, fmaf(-A02, e0, A22));
+    const float dr = fmaf(-e1, b1, fmaf(-e0, b0, b2)) * rcp1(s22);
+    const float dvx = fmaf(-A02, dr, b0) * iA.x;
+    const float dvy = fmaf(-A12, dr, b1) * iA.y;
     s.vx = vx + dvx;
     s.vy = vy + dvy;
     s.r = r + dr;
-    const float duL = dvx - dr * b, duR = dvx + dr * b;
-#pragma unroll
-    for (int i = 0; i < 4; ++i) s.w[i] = clipf(s.w[i] + (al[i] + be[i] * ((i & 2) ? duR : duL)), -wmax, wmax);
-    // heading: rotate (cos, sin) by d = h*r' with a Taylor pair (|d| < 0.7 always: |r'| <= wheel slip limits)
+    const float2 du = fma2(bc(dr), side, bc(dvx));
+    wF = add2(wF, fma2(F.be, du, F.al));
+    wB = add2(wB, fma2(B.be, du, B.al));
+    wF = make_float2(clipf(wF.x, -wmax, wmax), clipf(wF.y, -wmax, wmax));
+    wB = make_float2(clipf(wB.x, -wmax, wmax), clipf(wB.y, -wmax, wmax));
+    // heading: rotate (cos, sin) by d = h*r' with a Taylor pair (|d| <= 0.01 * R wmax / b = 0.3)
     const float d = h * s.r, d2 = d * d;
     const float sd = d * (1.f + d2 * (-1.f / 6.f + d2 * (1.f / 120.f + d2 * (-1.f / 5040.f + d2 * (1.f / 362880.f)))));
     const float cd = 1.f + d2 * (-0.5f + d2 * (1.f / 24.f + d2 * (-1.f / 720.f + d2 * (1.f / 40320.f))));
@@ -99,6 +132,7 @@ __device__ __forceinline__ void skid_steps(Skid& s, const float tau[4], const Oi
     s.px += h * (s.vx * cs - s.vy * sn);
     s.py += h * (s.vx * sn + s.vy * cs);
   }
+  s.w[0] = wF.x; s.w[2] = wF.y; s.w[1] = wB.x; s.w[3] = wB.y;
 }
 
 // warp-level sum
@@ -156,41 +190,36 @@ __device__ __forceinline__ ResetDraws philox_reset_draws(uint64_t seed, uint64_t
 }
 
 constexpr int kEnvThreads = 128;
+constexpr int kEnvMinBlocks = 5;   // <= 102 registers: 20 resident warps per SM (the kernel is issue/latency-bound)
 
-__global__ void __launch_bounds__(kEnvThreads)
+// kStats / kEval are compile-time so that the common launch carries neither the 24 logging accumulators nor the
+// eval-only state in registers.  Only what the sub-steps need is loaded before them; episode sums, the episode
+// counter and the previous observation (replay append) are loaded after the physics.
+template <bool kStats, bool kEval>
+__global__ void __launch_bounds__(kEnvThreads, kEnvMinBlocks)
 env_step_kernel(const __grid_constant__ OisEnvParams p, const __grid_constant__ OisEnvState st,
                 const __grid_constant__ OisEnvIO io, const int64_t n) {
   __shared__ float s_stats[OIS_EP_STATS_LEN];
-  const bool want_stats = io.ep_stats != nullptr;
-  if (want_stats) {
+  if (kStats) {
     if (threadIdx.x < OIS_EP_STATS_LEN) s_stats[threadIdx.x] = 0.f;
     __syncthreads();
   }
-  float acc[OIS_EP_STATS_LEN];
-  if (want_stats) {
+  float acc[kStats ? OIS_EP_STATS_LEN : 1];
+  if (kStats) {
 #pragma unroll
     for (int k = 0; k < OIS_EP_STATS_LEN; ++k) acc[k] = 0.f;
   }
   int any_reset_local = 0;
-  const bool eval = p.eval_sums != 0;
-  const bool zero_old = eval && io.any_reset_flags != nullptr && io.any_reset_flags[io.flag_slot] != 0;
+  const bool zero_old = kEval && io.any_reset_flags != nullptr && io.any_reset_flags[io.flag_slot] != 0;
+  const bool replay = io.replay_states != nullptr;
 
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
-    // ------------------------------------------------------------------ loads (all independent, issued up front)
+    // ------------------------------------------------------------------ loads the sub-steps depend on
     const float4 pv = ld_stream4(st.pose_vx + 4 * i);
     const float4 tp = ld_stream4(st.twist_prev + 4 * i);
     const float4 wv = ld_stream4(st.wheel_speed + 4 * i);
     float4 cmd = ld_stream4(st.commands + 4 * i);
-    float4 sa = ld_stream4(st.sums_a + 4 * i);
-    float4 sb = ld_stream4(st.sums_b + 4 * i);
     int64_t sim = __ldcs(st.sim_steps + i);
-    int64_t eb = __ldcs(st.episode_buf + i);
-    float4 se = make_float4(0.f, 0.f, 0.f, 0.f), ot = make_float4(0.f, 0.f, 0.f, 0.f);
-    if (eval) {
-      se = ld_stream4(st.sums_eval + 4 * i);
-      ot = ld_stream4(st.old_torques + 4 * i);
-      if (zero_old) ot = make_float4(0.f, 0.f, 0.f, 0.f);
-    }
     float a4[4];
     if (p.act_dim == 4) {             // KAMMA_medium.py:600
       const float4 a = __ldcs(reinterpret_cast<const float4*>(io.actions) + i);
@@ -202,16 +231,11 @@ env_step_kernel(const __grid_constant__ OisEnvParams p, const __grid_constant__ 
       const float a = __ldcs(io.actions + i);
       a4[0] = a4[1] = a4[2] = a4[3] = a;
     }
-    float prev_obs[6];
-    const bool replay = io.replay_states != nullptr;
-    if (replay) {
-      const float2* o = reinterpret_cast<const float2*>(io.obs + 6 * i);
-      const float2 o0 = o[0], o1 = o[1], o2 = o[2];
-      prev_obs[0] = o0.x; prev_obs[1] = o0.y; prev_obs[2] = o1.x; prev_obs[3] = o1.y; prev_obs[4] = o2.x; prev_obs[5] = o2.y;
+    if (io.clip_actions > 0.f) {      // VecEnvRLGames.step clamps the actions before pre_physics_step (clipActions)
+#pragma unroll
+      for (int j = 0; j < 4; ++j) a4[j] = clipf(a4[j], -io.clip_actions, io.clip_actions);
     }
-    uint4 ph = make_uint4(0, 0, 0, 0);
-    const bool need_philox = (p.blend == OIS_BLEND_SWITCH && io.rand_mask == nullptr) || io.reset_uniforms == nullptr;
-    if (need_philox) ph = Philox(io.philox_seed)((uint64_t)i, io.philox_offset * 4);
+    const bool need_mask_draw = p.blend == OIS_BLEND_SWITCH && io.rand_mask == nullptr;
 
     // ------------------------------------------------------------------ pre_physics_step :604-636
     const float desired_v = cmd.x, desired_w = cmd.z;
@@ -226,7 +250,7 @@ env_step_kernel(const __grid_constant__ OisEnvParams p, const __grid_constant__ 
     const float g2 = gamma_assist(p.gamma2_mode, p.gamma2_const, sim, p.max_sim_steps);
     float tq[4], wt[4];
     if (p.blend == OIS_BLEND_SWITCH) {          // :632-636
-      const float rm = io.rand_mask ? __ldcs(io.rand_mask + i) : u01(ph.x);
+      const float rm = need_mask_draw ? u01(Philox(io.philox_seed)((uint64_t)i, io.philox_offset * 4).x) : __ldcs(io.rand_mask + i);
       const float mask = rm < g1 ? 1.0f : 0.0f;
       const float nmask = sub(1.0f, mask);
 #pragma unroll
@@ -236,18 +260,50 @@ env_step_kernel(const __grid_constant__ OisEnvParams p, const __grid_constant__ 
 #pragma unroll
       for (int j = 0; j < 4; ++j) tq[j] = add(mul(mul(ng, a4[j]), p.action_scale), mul(g1, crit[j]));
     }
-    float guiding = 0.f;
-    if (!p.guiding_post_clip) {                 // KA_DDPG_1D.py:642
+#pragma unroll
+    for (int j = 0; j < 4; ++j) wt[j] = clipf(tq[j], -p.torque_clip, p.torque_clip);   // :649
+    float guiding;
+    {
       float acc2 = 0.f;
 #pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        const float d = sub(mul(a4[j], p.action_scale), crit[j]);
+      for (int j = 0; j < 4; ++j) {             // KA_DDPG_1D.py:642 (pre-clip) | KAMMA_medium.py:656 (post-clip)
+        const float d = p.guiding_post_clip ? sub(wt[j], crit[j]) : sub(mul(a4[j], p.action_scale), crit[j]);
         acc2 = j == 0 ? mul(d, d) : add(acc2, mul(d, d));
       }
       guiding = -sqrtf(acc2);
     }
-#pragma unroll
-    for (int j = 0; j < 4; ++j) wt[j] = clipf(tq[j], -p.torque_clip, p.torque_clip);   // :649
+    // everything about the torques is final before the physics: store it now and drop the registers
+    st_stream4(io.wheel_torqs + 4 * i, make_float4(wt[0], wt[1], wt[2], wt[3]));
+    if (io.torques) st_stream4(io.torques + 4 * i, make_float4(tq[0], tq[1], tq[2], tq[3]));
+    if (io.guiding) __stcs(io.guiding + i, guiding);
+    if (io.comp0 && i == 0) {   // env-0 scalars behind observed_components :840-867 (pre-physics part)
+      float* c = io.comp0;
+      c[0] = desired_v; c[1] = current_v; c[2] = desired_w; c[3] = current_w; c[4] = v_delta; c[5] = omega_delta;
+      c[9] = tq[0]; c[10] = tq[1]; c[11] = tq[2]; c[12] = tq[3]; c[13] = ac_left; c[14] = ac_right;
+      c[15] = a4[0]; c[16] = a4[1]; c[17] = a4[2]; c[18] = a4[3];
+      c[19] = g2; c[26] = guiding; c[28] = g1;
+    }
+    const float r3 = add(add(add(mul(wt[0], wt[0]), mul(wt[1], wt[1])), mul(wt[2], wt[2])), mul(wt[3], wt[3]));
+    // calculate_metrics :770 — linear_acc lags a step: it uses the pre-physics projection
+    const float lin_acc = dvd(sub(current_v, tp.z), p.dt);
+    float smooth = 0.f;
+    if (kEval) {                                // KAMMA_eval.py:677-685
+      float4 ot = ld_stream4(st.old_torques + 4 * i);
+      if (zero_old) ot = make_float4(0.f, 0.f, 0.f, 0.f);
+      const float d0 = sub(ot.x, wt[0]), d1 = sub(ot.y, wt[1]), d2 = sub(ot.z, wt[2]), d3 = sub(ot.w, wt[3]);
+      smooth = dvd(add(add(add(mul(d0, d0), mul(d1, d1)), mul(d2, d2)), mul(d3, d3)), 10.0f);
+      st_stream4(st.old_torques + 4 * i, make_float4(wt[0], wt[1], wt[2], wt[3]));
+    }
+    float4 replay_act = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (replay) {   // what record_transition stores as the action (base_KA_DDPG.py:212 relabel, or the policy's)
+      if (io.relabel == OIS_RELABEL_EXECUTED)
+        replay_act = make_float4(dvd(wt[0], p.action_scale), dvd(wt[1], p.action_scale), dvd(wt[2], p.action_scale),
+                                 dvd(wt[3], p.action_scale));
+      else replay_act = make_float4(a4[0], a4[1], a4[2], a4[3]);
+      if (io.relabel == OIS_RELABEL_EXECUTED || p.act_dim == 4) st_stream4(io.replay_actions + 4 * i, replay_act);
+      else if (p.act_dim == 2) reinterpret_cast<float2*>(io.replay_actions)[i] = make_float2(a4[0], a4[2]);
+      else io.replay_actions[i] = a4[0];
+    }
 
     // ------------------------------------------------------------------ physics :646-653 (replaces PhysX)
     Skid s;
@@ -255,21 +311,21 @@ env_step_kernel(const __grid_constant__ OisEnvParams p, const __grid_constant__ 
     s.w[0] = wv.x; s.w[1] = wv.y; s.w[2] = wv.z; s.w[3] = wv.w;
     if (p.physics) skid_steps(s, wt, p);
 
-    if (p.guiding_post_clip) {                  // :656
-      float acc2 = 0.f;
-#pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        const float d = sub(wt[j], crit[j]);
-        acc2 = j == 0 ? mul(d, d) : add(acc2, mul(d, d));
-      }
-      guiding = -sqrtf(acc2);
+    // ------------------------------------------------------------------ loads of the post-physics part
+    float4 sa = ld_stream4(st.sums_a + 4 * i);
+    float4 sb = ld_stream4(st.sums_b + 4 * i);
+    int64_t eb = __ldcs(st.episode_buf + i);
+    float4 se = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (kEval) se = ld_stream4(st.sums_eval + 4 * i);
+    float prev_obs[6];
+    if (replay) {
+      const float2* o = reinterpret_cast<const float2*>(io.obs + 6 * i);
+      const float2 o0 = o[0], o1 = o[1], o2 = o[2];
+      prev_obs[0] = o0.x; prev_obs[1] = o0.y; prev_obs[2] = o1.x; prev_obs[3] = o1.y; prev_obs[4] = o2.x; prev_obs[5] = o2.y;
     }
-    if (eval) {                                 // KAMMA_eval.py:677-685
-      const float d0 = sub(ot.x, wt[0]), d1 = sub(ot.y, wt[1]), d2 = sub(ot.z, wt[2]), d3 = sub(ot.w, wt[3]);
-      const float ss = add(add(add(mul(d0, d0), mul(d1, d1)), mul(d2, d2)), mul(d3, d3));
-      se.x = add(se.x, dvd(ss, 10.0f));
+    if (kEval) {
+      se.x = add(se.x, smooth);
       se.z = add(se.z, dvd(desired_v, 10.0f));
-      ot = make_float4(wt[0], wt[1], wt[2], wt[3]);
     }
 
     // ------------------------------------------------------------------ post_physics_step :675-676
@@ -280,13 +336,11 @@ env_step_kernel(const __grid_constant__ OisEnvParams p, const __grid_constant__ 
     const bool oob = (s.px < -p.bound) | (s.px > p.bound) | (s.py < -p.bound) | (s.py > p.bound);
     const bool reset = timeout | oob;
 
-    // calculate_metrics :767-810 (linear_acc lags a step: it uses the pre-physics projection)
-    const float lin_acc = dvd(sub(current_v, tp.z), p.dt);
+    // calculate_metrics :767-810
     const float ang_acc = dvd(sub(s.r, tp.w), p.dt);
     const float prev_lin = current_v, prev_ang = s.r;
     const float r1 = add(mul(v_delta, v_delta), mul(5.0f, mul(omega_delta, omega_delta)));
     const float r2 = add(mul(lin_acc, lin_acc), mul(ang_acc, ang_acc));
-    const float r3 = add(add(add(mul(wt[0], wt[0]), mul(wt[1], wt[1])), mul(wt[2], wt[2])), mul(wt[3], wt[3]));
     const float c1 = mul(-25.0f, r1), c2 = mul(-0.02f, r2), c3 = mul(-0.09f, r3);
     const float rdense = add(add(c1, c2), c3);
     const float sparse = (fabsf(v_delta) < 0.01f && fabsf(omega_delta) < 0.01f) ? 0.2f : 0.0f;
@@ -294,14 +348,19 @@ env_step_kernel(const __grid_constant__ OisEnvParams p, const __grid_constant__ 
     const float rew = add(mul(sub(1.0f, g2), observed), mul(g2, guiding));
     sa.x = add(sa.x, c1); sa.y = add(sa.y, c2); sa.z = add(sa.z, c3); sa.w = add(sa.w, rdense);
     sb.x = add(sb.x, sparse); sb.y = add(sb.y, guiding); sb.z = add(sb.z, observed); sb.w = add(sb.w, rew);
-    if (eval) se.y = add(se.y, dvd(fabsf(v_delta), 10.0f));   // KAMMA_eval.py:840
+    if (kEval) se.y = add(se.y, dvd(fabsf(v_delta), 10.0f));   // KAMMA_eval.py:840
 
-    if (want_stats) { acc[19] += g1; acc[20] += g2; }
+    if (kStats) { acc[19] += g1; acc[20] += g2; }
+    if (io.comp0 && i == 0) {   // env-0 scalars, post-physics part
+      float* c = io.comp0;
+      c[6] = lin_acc; c[7] = ang_acc; c[20] = c1; c[21] = c2; c[22] = c3; c[23] = rdense; c[24] = sparse; c[25] = observed;
+      c[27] = rew;
+    }
 
     // ------------------------------------------------------------------ reset_idx :417-498
     if (reset) {
       any_reset_local = 1;
-      if (want_stats) {   // episode statistics (logging) :470-488
+      if (kStats) {   // episode statistics (logging) :470-488
         const float T = p.max_episode_length_s, fin = sb.w, om = sub(1.0f, g2);
         acc[0] += sa.x; acc[1] += sa.y; acc[2] += sa.z; acc[3] += sa.w;
         acc[4] += sb.x; acc[5] += sb.y; acc[6] += sb.z; acc[7] += sb.w;
@@ -320,8 +379,8 @@ env_step_kernel(const __grid_constant__ OisEnvParams p, const __grid_constant__ 
         const float4 ua = __ldcs(reinterpret_cast<const float4*>(io.reset_uniforms + 8 * i));
         const float4 ub = __ldcs(reinterpret_cast<const float4*>(io.reset_uniforms + 8 * i + 4));
         d.u[0] = ua.x; d.u[1] = ua.y; d.u[2] = ua.z; d.u[3] = ua.w; d.u[4] = ub.x; d.u[5] = ub.y; d.u[6] = ub.z;
-      } else {
-        d = philox_reset_draws(io.philox_seed, io.philox_offset, i, ph);
+      } else {   // resets are rare: the first Philox block is recomputed here rather than held across the physics
+        d = philox_reset_draws(io.philox_seed, io.philox_offset, i, Philox(io.philox_seed)((uint64_t)i, io.philox_offset * 4));
       }
       apply_reset(p, d, sim, s, cmd);
       eb = 0;                                                   // :462
@@ -330,23 +389,26 @@ env_step_kernel(const __grid_constant__ OisEnvParams p, const __grid_constant__ 
       sb = sa;
       se = sa;
     }
+    if (io.comp0 && i == 0) io.comp0[8] = (float)st.episode_count[0];
 
     // ------------------------------------------------------------------ get_observations :833 + stores
-    float ob[6] = {cmd.x, cmd.z, v_delta, omega_delta, lin_acc, ang_acc};
-    if (io.clip_obs > 0.f) {
-#pragma unroll
-      for (int k = 0; k < 6; ++k) ob[k] = clipf(ob[k], -io.clip_obs, io.clip_obs);
-    }
+    const float ob[6] = {cmd.x, cmd.z, v_delta, omega_delta, lin_acc, ang_acc};
     float2* o = reinterpret_cast<float2*>(io.obs + 6 * i);
     o[0] = make_float2(ob[0], ob[1]);
     o[1] = make_float2(ob[2], ob[3]);
     o[2] = make_float2(ob[4], ob[5]);
+    float oc[6];
+#pragma unroll
+    for (int k = 0; k < 6; ++k) oc[k] = io.clip_obs > 0.f ? clipf(ob[k], -io.clip_obs, io.clip_obs) : ob[k];
+    if (io.obs_clipped) {   // what the env wrapper returns: clamp(obs_buf, +-clipObservations)  (rl_task.py:99)
+      float2* q = reinterpret_cast<float2*>(io.obs_clipped + 6 * i);
+      q[0] = make_float2(oc[0], oc[1]);
+      q[1] = make_float2(oc[2], oc[3]);
+      q[2] = make_float2(oc[4], oc[5]);
+    }
     __stcs(io.rew + i, rew);
     io.reset[i] = reset ? 1 : 0;
-    st_stream4(io.wheel_torqs + 4 * i, make_float4(wt[0], wt[1], wt[2], wt[3]));
     if (io.timeout) __stcs(io.timeout + i, (int64_t)(timeout ? 1 : 0));
-    if (io.torques) st_stream4(io.torques + 4 * i, make_float4(tq[0], tq[1], tq[2], tq[3]));
-    if (io.guiding) __stcs(io.guiding + i, guiding);
 
     st_stream4(st.pose_vx + 4 * i, make_float4(s.px, s.py, s.yaw, s.vx));
     st_stream4(st.twist_prev + 4 * i, make_float4(s.vy, s.r, prev_lin, prev_ang));
@@ -356,10 +418,7 @@ env_step_kernel(const __grid_constant__ OisEnvParams p, const __grid_constant__ 
     st_stream4(st.sums_b + 4 * i, sb);
     __stcs(st.sim_steps + i, sim);
     __stcs(st.episode_buf + i, eb);
-    if (eval) {
-      st_stream4(st.sums_eval + 4 * i, se);
-      st_stream4(st.old_torques + 4 * i, ot);
-    }
+    if (kEval) st_stream4(st.sums_eval + 4 * i, se);
 
     if (replay) {   // DDPG.record_transition -> memory.add_samples (ddpg.py:313), row `memory_index`
       if (io.clip_obs > 0.f) {   // the trainer's `states` are the wrapper's clamped observations of the previous step
@@ -371,36 +430,16 @@ env_step_kernel(const __grid_constant__ OisEnvParams p, const __grid_constant__ 
       rs[1] = make_float2(prev_obs[2], prev_obs[3]);
       rs[2] = make_float2(prev_obs[4], prev_obs[5]);
       float2* rn = reinterpret_cast<float2*>(io.replay_next_states + 6 * i);
-      rn[0] = make_float2(ob[0], ob[1]);
-      rn[1] = make_float2(ob[2], ob[3]);
-      rn[2] = make_float2(ob[4], ob[5]);
-      if (io.relabel == OIS_RELABEL_EXECUTED) {   // actions = wheel_torqs / action_scale (base_KA_DDPG.py:212)
-        st_stream4(io.replay_actions + 4 * i, make_float4(dvd(wt[0], p.action_scale), dvd(wt[1], p.action_scale),
-                                                          dvd(wt[2], p.action_scale), dvd(wt[3], p.action_scale)));
-      } else if (p.act_dim == 4) {
-        st_stream4(io.replay_actions + 4 * i, make_float4(a4[0], a4[1], a4[2], a4[3]));
-      } else if (p.act_dim == 2) {
-        reinterpret_cast<float2*>(io.replay_actions)[i] = make_float2(a4[0], a4[2]);
-      } else {
-        io.replay_actions[i] = a4[0];
-      }
+      rn[0] = make_float2(oc[0], oc[1]);
+      rn[1] = make_float2(oc[2], oc[3]);
+      rn[2] = make_float2(oc[4], oc[5]);
       io.replay_rewards[i] = rew;
       io.replay_terminated[i] = reset ? 1 : 0;
       io.replay_truncated[i] = 0;
     }
-
-    if (io.comp0 && i == 0) {   // env-0 scalars behind observed_components :840-867
-      float* c = io.comp0;
-      c[0] = desired_v; c[1] = current_v; c[2] = desired_w; c[3] = current_w; c[4] = v_delta; c[5] = omega_delta;
-      c[6] = lin_acc; c[7] = ang_acc; c[8] = (float)st.episode_count[0];
-      c[9] = tq[0]; c[10] = tq[1]; c[11] = tq[2]; c[12] = tq[3]; c[13] = ac_left; c[14] = ac_right;
-      c[15] = a4[0]; c[16] = a4[1]; c[17] = a4[2]; c[18] = a4[3];
-      c[19] = g2; c[20] = c1; c[21] = c2; c[22] = c3; c[23] = rdense; c[24] = sparse; c[25] = observed;
-      c[26] = guiding; c[27] = rew; c[28] = g1;
-    }
   }
 
-  if (want_stats) {
+  if (kStats) {
     const int lane = threadIdx.x & 31;
 #pragma unroll
     for (int k = 0; k < OIS_EP_STATS_LEN; ++k) {
@@ -410,7 +449,7 @@ env_step_kernel(const __grid_constant__ OisEnvParams p, const __grid_constant__ 
     __syncthreads();
     if (threadIdx.x < OIS_EP_STATS_LEN && s_stats[threadIdx.x] != 0.f) atomicAdd(io.ep_stats + threadIdx.x, s_stats[threadIdx.x]);
   }
-  if (eval && io.any_reset_flags != nullptr) {
+  if (kEval && io.any_reset_flags != nullptr) {
     if (__syncthreads_or(any_reset_local) && threadIdx.x == 0) atomicOr(io.any_reset_flags + (io.flag_slot + 1) % 3, 1);
     if (blockIdx.x == 0 && threadIdx.x == 0) io.any_reset_flags[(io.flag_slot + 2) % 3] = 0;
   }
@@ -468,7 +507,7 @@ reset_idx_kernel(const __grid_constant__ OisEnvParams p, const __grid_constant__
 
 static int grid_for(int64_t n, int threads) {
   int64_t blocks = (n + threads - 1) / threads;
-  const int64_t cap = (int64_t)num_sms() * 16;   // 16 resident CTAs of 128 threads per SM: one full wave
+  const int64_t cap = (int64_t)num_sms() * kEnvMinBlocks * 2;   // two waves of resident CTAs; grid-stride beyond
   if (blocks > cap) blocks = cap;
   if (blocks < 1) blocks = 1;
   return (int)blocks;
@@ -502,7 +541,13 @@ extern "C" int ois_env_step(const OisEnvParams* params, const OisEnvState* state
   OIS_CHECK_ARG(!any_replay || all_replay, "replay pointers must be all set or all null");
   OIS_CHECK_ARG(io->flag_slot >= 0 && io->flag_slot < 3, "flag_slot must be 0..2");
   if (n_envs == 0) return OIS_OK;
-  env_step_kernel<<<grid_for(n_envs, kEnvThreads), kEnvThreads, 0, (cudaStream_t)stream>>>(*params, *state, *io, n_envs);
+  const int grid = grid_for(n_envs, kEnvThreads);
+  cudaStream_t s = (cudaStream_t)stream;
+  const bool stats = io->ep_stats != nullptr, ev = params->eval_sums != 0;
+  if (stats && ev) env_step_kernel<true, true><<<grid, kEnvThreads, 0, s>>>(*params, *state, *io, n_envs);
+  else if (stats) env_step_kernel<true, false><<<grid, kEnvThreads, 0, s>>>(*params, *state, *io, n_envs);
+  else if (ev) env_step_kernel<false, true><<<grid, kEnvThreads, 0, s>>>(*params, *state, *io, n_envs);
+  else env_step_kernel<false, false><<<grid, kEnvThreads, 0, s>>>(*params, *state, *io, n_envs);
   OIS_CHECK_LAUNCH();
   return OIS_OK;
 }

@@ -138,6 +138,10 @@ class TorqueDistributionTask:
         self._any_reset_flags = torch.zeros(3, dtype=torch.int32, device=dev) if ev else None
         self.sim_steps, self.episode_buf, self.episode_count = zl(), zl(), zl()
         self.obs_buf = torch.zeros(n, 6, dtype=torch.float32, device=dev)
+        # clamp(obs_buf, +-clipObservations) as the env wrapper returns it; two buffers alternate so the previous
+        # step's observations (the trainer's `states`) stay intact while the next step is written
+        self._obs_clipped = [torch.zeros(n, 6, dtype=torch.float32, device=dev) for _ in range(2)]
+        self.obs_clipped = self._obs_clipped[0]
         self.rew_buf = torch.zeros(n, dtype=torch.float32, device=dev)
         self.reset_buf = torch.ones(n, dtype=torch.bool, device=dev)
         self.timeout_buf = zl()
@@ -288,10 +292,13 @@ class TorqueDistributionTask:
         ``record=False`` suppresses the fused replay append for this step (the wrapper's reset step)."""
         if self._env is not None and hasattr(self._env, "world") and not self._env.world.is_playing():
             return
-        if actions.data_ptr() != self.actions.data_ptr():
-            self.actions.copy_(actions.reshape(self._num_envs, self._num_actions))   # actions.clone() :600
+        if not (actions.is_cuda and actions.dtype == torch.float32 and actions.is_contiguous()
+                and actions.numel() == self._num_envs * self._num_actions):
+            actions = actions.to(device=self._device, dtype=torch.float32).reshape(self._num_envs, self._num_actions).contiguous()
+        self.actions = actions      # :600 keeps a clone; the kernel only reads it, so a reference is enough
         io = L.EnvIO()
-        io.actions = self.actions.data_ptr()
+        io.actions = actions.data_ptr()
+        io.clip_actions = self.clip_actions if math.isfinite(self.clip_actions) else -1.0
         io.rand_mask = L.ptr(self._supplied_mask)
         io.reset_uniforms = L.ptr(self._supplied_reset)
         io.philox_seed, io.philox_offset = self._seed, self._launches
@@ -306,7 +313,9 @@ class TorqueDistributionTask:
         if self.variant.eval_sums:
             io.any_reset_flags = self._any_reset_flags.data_ptr()
         io.flag_slot = self._launches % 3
-        io.clip_obs = -1.0
+        io.clip_obs = self.clip_obs if math.isfinite(self.clip_obs) else -1.0
+        self.obs_clipped = self._obs_clipped[self._launches & 1]
+        io.obs_clipped = self.obs_clipped.data_ptr()
         if self._replay is not None and record:
             m = self._replay
             r = m.memory_index
@@ -317,7 +326,6 @@ class TorqueDistributionTask:
             io.replay_terminated = m.tensors["terminated"][r].data_ptr()
             io.replay_truncated = m.tensors["truncated"][r].data_ptr()
             io.relabel = self._relabel
-            io.clip_obs = self.clip_obs if math.isfinite(self.clip_obs) else -1.0
             m.advance()
         L.check(L.lib().ois_env_step(C.byref(self._params), C.byref(self._state), C.byref(io), self._num_envs,
                                      L.current_stream()))
@@ -419,15 +427,16 @@ class VecEnv:
                 self.task.post_reset()
             # VecEnvRLGames.reset steps once with zero actions to produce the first observation
             zero = torch.zeros(self.num_envs, self.task.num_actions, device=self.device)
-            obs, _, _, _ = self.task.step(zero, record=False)
-            self._obs = torch.clamp(obs, -self.task.clip_obs, self.task.clip_obs)
+            self.task.step(zero, record=False)
+            self._obs = self.task.obs_clipped
             self._reset_once = False
         return self._obs, {}
 
     def step(self, actions):
-        a = torch.clamp(actions, -self.task.clip_actions, self.task.clip_actions)
-        obs, rew, reset, extras = self.task.step(a)
-        self._obs = torch.clamp(obs, -self.task.clip_obs, self.task.clip_obs)
+        """Both clamps of VecEnvRLGames.step (actions to +-clipActions, observations to +-clipObservations) are
+        done inside the fused kernel; the returned observation tensor alternates between two buffers."""
+        _, rew, reset, extras = self.task.step(actions)
+        self._obs = self.task.obs_clipped
         return self._obs, rew.view(-1, 1), reset.view(-1, 1), self._truncated, extras
 
     def render(self, *a, **k):

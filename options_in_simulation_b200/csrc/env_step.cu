@@ -190,7 +190,10 @@ __device__ __forceinline__ ResetDraws philox_reset_draws(uint64_t seed, uint64_t
 }
 
 constexpr int kEnvThreads = 128;
-constexpr int kEnvMinBlocks = 5;   // <= 102 registers: 20 resident warps per SM (the kernel is issue/latency-bound)
+#ifndef OIS_ENV_MIN_BLOCKS
+#define OIS_ENV_MIN_BLOCKS 5
+#endif
+constexpr int kEnvMinBlocks = OIS_ENV_MIN_BLOCKS;   // 5: <= 102 registers, 20 resident warps per SM (issue/latency-bound kernel)
 
 // kStats / kEval are compile-time so that the common launch carries neither the 24 logging accumulators nor the
 // eval-only state in registers.  Only what the sub-steps need is loaded before them; episode sums, the episode

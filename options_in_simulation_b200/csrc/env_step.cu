@@ -198,6 +198,34 @@ constexpr int kEnvMinBlocks = OIS_ENV_MIN_BLOCKS;   // 5: <= 102 registers, 20 r
 // kStats / kEval are compile-time so that the common launch carries neither the 24 logging accumulators nor the
 // eval-only state in registers.  Only what the sub-steps need is loaded before them; episode sums, the episode
 // counter and the previous observation (replay append) are loaded after the physics.
+// cp.async (LDGSTS) staging: global -> shared without passing through registers.  Each thread only ever reads the
+// slots it filled itself, so cp.async.wait_group is the only synchronisation needed.
+__device__ __forceinline__ void cp_async16(void* smem, const void* gmem) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((uint32_t)__cvta_generic_to_shared(smem)), "l"(gmem) : "memory");
+}
+__device__ __forceinline__ void cp_async8(void* smem, const void* gmem) {
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"((uint32_t)__cvta_generic_to_shared(smem)), "l"(gmem) : "memory");
+}
+__device__ __forceinline__ void cp_async4(void* smem, const void* gmem) {
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"((uint32_t)__cvta_generic_to_shared(smem)), "l"(gmem) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int kPending>
+__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(kPending) : "memory"); }
+
+// Inputs of one env, staged per thread.  Group A = what the sub-steps depend on (double-buffered: the next
+// grid-stride iteration's group A lands while this iteration computes); group B = what is only needed after the
+// physics (issued a whole iteration ahead as well, single buffer, re-issued as soon as it has been consumed).
+struct StageA {
+  float4 pv[kEnvThreads], tp[kEnvThreads], wv[kEnvThreads], cmd[kEnvThreads], act[kEnvThreads];
+  int64_t sim[kEnvThreads];
+};
+struct StageB {
+  float4 sa[kEnvThreads], sb[kEnvThreads], se[kEnvThreads];
+  int64_t eb[kEnvThreads];
+  float2 obs[3][kEnvThreads];
+};
+
 template <bool kStats, bool kEval>
 __global__ void __launch_bounds__(kEnvThreads, kEnvMinBlocks)
 env_step_kernel(const __grid_constant__ OisEnvParams p, const __grid_constant__ OisEnvState st,
@@ -216,23 +244,59 @@ env_step_kernel(const __grid_constant__ OisEnvParams p, const __grid_constant__ 
   const bool zero_old = kEval && io.any_reset_flags != nullptr && io.any_reset_flags[io.flag_slot] != 0;
   const bool replay = io.replay_states != nullptr;
 
-  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
-    // ------------------------------------------------------------------ loads the sub-steps depend on
-    const float4 pv = ld_stream4(st.pose_vx + 4 * i);
-    const float4 tp = ld_stream4(st.twist_prev + 4 * i);
-    const float4 wv = ld_stream4(st.wheel_speed + 4 * i);
-    float4 cmd = ld_stream4(st.commands + 4 * i);
-    int64_t sim = __ldcs(st.sim_steps + i);
+  __shared__ __align__(16) StageA s_a[2];
+  __shared__ __align__(16) StageB s_b;
+  const int tid = threadIdx.x;
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  auto issue_a = [&](int buf, int64_t j) {
+    if (j < n) {
+      StageA& a = s_a[buf];
+      cp_async16(&a.pv[tid], st.pose_vx + 4 * j);
+      cp_async16(&a.tp[tid], st.twist_prev + 4 * j);
+      cp_async16(&a.wv[tid], st.wheel_speed + 4 * j);
+      cp_async16(&a.cmd[tid], st.commands + 4 * j);
+      cp_async8(&a.sim[tid], st.sim_steps + j);
+      if (p.act_dim == 4) cp_async16(&a.act[tid], io.actions + 4 * j);
+      else if (p.act_dim == 2) cp_async8(&a.act[tid], io.actions + 2 * j);
+      else cp_async4(&a.act[tid], io.actions + j);
+    }
+    cp_async_commit();
+  };
+  auto issue_b = [&](int64_t j) {
+    if (j < n) {
+      cp_async16(&s_b.sa[tid], st.sums_a + 4 * j);
+      cp_async16(&s_b.sb[tid], st.sums_b + 4 * j);
+      cp_async8(&s_b.eb[tid], st.episode_buf + j);
+      if (kEval) cp_async16(&s_b.se[tid], st.sums_eval + 4 * j);
+      if (replay) {
+        const float* o = io.obs + 6 * j;
+        cp_async8(&s_b.obs[0][tid], o);
+        cp_async8(&s_b.obs[1][tid], o + 2);
+        cp_async8(&s_b.obs[2][tid], o + 4);
+      }
+    }
+    cp_async_commit();
+  };
+  const int64_t i0 = (int64_t)blockIdx.x * blockDim.x + tid;
+  issue_a(0, i0);
+  issue_b(i0);
+  int buf = 0;
+
+  for (int64_t i = i0; i < n; i += stride, buf ^= 1) {
+    // ------------------------------------------------------------------ group A: this env's now, the next one's in flight
+    issue_a(buf ^ 1, i + stride);
+    cp_async_wait<2>();               // pending at most: B(i), A(i + stride)
+    const float4 pv = s_a[buf].pv[tid];
+    const float4 tp = s_a[buf].tp[tid];
+    const float4 wv = s_a[buf].wv[tid];
+    float4 cmd = s_a[buf].cmd[tid];
+    int64_t sim = s_a[buf].sim[tid];
     float a4[4];
-    if (p.act_dim == 4) {             // KAMMA_medium.py:600
-      const float4 a = __ldcs(reinterpret_cast<const float4*>(io.actions) + i);
-      a4[0] = a.x; a4[1] = a.y; a4[2] = a.z; a4[3] = a.w;
-    } else if (p.act_dim == 2) {      // KA_DDPG_2D.py:624  [a0, a0, a1, a1]
-      const float2 a = __ldcs(reinterpret_cast<const float2*>(io.actions) + i);
-      a4[0] = a.x; a4[1] = a.x; a4[2] = a.y; a4[3] = a.y;
-    } else {                          // KA_DDPG_1D.py:600  repeat(1, 4)
-      const float a = __ldcs(io.actions + i);
-      a4[0] = a4[1] = a4[2] = a4[3] = a;
+    {
+      const float4 a = s_a[buf].act[tid];
+      if (p.act_dim == 4) { a4[0] = a.x; a4[1] = a.y; a4[2] = a.z; a4[3] = a.w; }            // KAMMA_medium.py:600
+      else if (p.act_dim == 2) { a4[0] = a.x; a4[1] = a.x; a4[2] = a.y; a4[3] = a.y; }       // KA_DDPG_2D.py:624
+      else { a4[0] = a4[1] = a4[2] = a4[3] = a.x; }                                          // KA_DDPG_1D.py:600
     }
     if (io.clip_actions > 0.f) {      // VecEnvRLGames.step clamps the actions before pre_physics_step (clipActions)
 #pragma unroll
@@ -314,18 +378,19 @@ env_step_kernel(const __grid_constant__ OisEnvParams p, const __grid_constant__ 
     s.w[0] = wv.x; s.w[1] = wv.y; s.w[2] = wv.z; s.w[3] = wv.w;
     if (p.physics) skid_steps(s, wt, p);
 
-    // ------------------------------------------------------------------ loads of the post-physics part
-    float4 sa = ld_stream4(st.sums_a + 4 * i);
-    float4 sb = ld_stream4(st.sums_b + 4 * i);
-    int64_t eb = __ldcs(st.episode_buf + i);
+    // ------------------------------------------------------------------ group B: issued one iteration ago
+    cp_async_wait<1>();               // pending at most: A(i + stride)
+    float4 sa = s_b.sa[tid];
+    float4 sb = s_b.sb[tid];
+    int64_t eb = s_b.eb[tid];
     float4 se = make_float4(0.f, 0.f, 0.f, 0.f);
-    if (kEval) se = ld_stream4(st.sums_eval + 4 * i);
+    if (kEval) se = s_b.se[tid];
     float prev_obs[6];
     if (replay) {
-      const float2* o = reinterpret_cast<const float2*>(io.obs + 6 * i);
-      const float2 o0 = o[0], o1 = o[1], o2 = o[2];
+      const float2 o0 = s_b.obs[0][tid], o1 = s_b.obs[1][tid], o2 = s_b.obs[2][tid];
       prev_obs[0] = o0.x; prev_obs[1] = o0.y; prev_obs[2] = o1.x; prev_obs[3] = o1.y; prev_obs[4] = o2.x; prev_obs[5] = o2.y;
     }
+    issue_b(i + stride);              // lands during the rest of this iteration and the next env's physics
     if (kEval) {
       se.x = add(se.x, smooth);
       se.z = add(se.z, dvd(desired_v, 10.0f));
@@ -546,6 +611,14 @@ extern "C" int ois_env_step(const OisEnvParams* params, const OisEnvState* state
   if (n_envs == 0) return OIS_OK;
   const int grid = grid_for(n_envs, kEnvThreads);
   cudaStream_t s = (cudaStream_t)stream;
+  static bool carveout_set = false;   // 32 KB of staging per CTA x kEnvMinBlocks CTAs: ask for the large shared-memory split
+  if (!carveout_set) {
+    cudaFuncSetAttribute(env_step_kernel<false, false>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+    cudaFuncSetAttribute(env_step_kernel<false, true>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+    cudaFuncSetAttribute(env_step_kernel<true, false>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+    cudaFuncSetAttribute(env_step_kernel<true, true>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+    carveout_set = true;
+  }
   const bool stats = io->ep_stats != nullptr, ev = params->eval_sums != 0;
   if (stats && ev) env_step_kernel<true, true><<<grid, kEnvThreads, 0, s>>>(*params, *state, *io, n_envs);
   else if (stats) env_step_kernel<true, false><<<grid, kEnvThreads, 0, s>>>(*params, *state, *io, n_envs);

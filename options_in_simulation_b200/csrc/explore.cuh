@@ -53,6 +53,41 @@ __device__ __forceinline__ void explore_row4(const OisActIO& io, int64_t row, fl
   *reinterpret_cast<float4*>(io.ou_state + 4 * row) = make_float4(st[0], st[1], st[2], st[3]);
 }
 
+// OU update of one whole row for act_dim in {1, 2, 4}, WITHOUT touching the action: advances io.ou_state and returns the
+// scaled noises nz[k] to add (applied == false: timestep past the exploration horizon, nothing is added).  Bit-identical
+// to explore_elem for i = act_dim*row + k (the row's elements share one Philox counter block because act_dim divides 4).
+// Lets the tensor-core actor prepare the noise while the MLP is still in flight.
+__device__ __forceinline__ void explore_row_prepare(const OisActIO& io, int64_t row, int A, float (&nz)[4], bool& applied) {
+  const int64_t i0 = row * A;
+  float z[4] = {0.f, 0.f, 0.f, 0.f};
+  if (io.normals) {
+#pragma unroll
+    for (int k = 0; k < 4; ++k) if (k < A) z[k] = io.normals[i0 + k];
+  } else {
+    const uint4 r = Philox(io.philox_seed)((uint64_t)(i0 >> 2), io.philox_offset * 2);
+    const int l0 = (int)(i0 & 3);
+    if (A == 4) {
+      const float2 n01 = normal2(r.x, r.y), n23 = normal2(r.z, r.w);
+      z[0] = n01.x; z[1] = n01.y; z[2] = n23.x; z[3] = n23.y;
+    } else {   // one Box-Muller pair covers the row: lanes (l0, l0+1) for A == 2, lane l0 for A == 1
+      const float2 nn = (l0 & 2) ? normal2(r.z, r.w) : normal2(r.x, r.y);
+      if (A == 2) { z[0] = nn.x; z[1] = nn.y; }
+      else z[0] = (l0 & 1) ? nn.y : nn.x;
+    }
+  }
+  applied = io.noise_scale >= 0.f;
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    nz[k] = 0.f;
+    if (k < A) {
+      const float st = io.ou_state[i0 + k];
+      const float ns = __fadd_rn(st, __fadd_rn(__fmul_rn(-st, io.theta), __fmul_rn(io.sigma, z[k])));
+      io.ou_state[i0 + k] = ns;
+      if (applied) nz[k] = __fmul_rn(__fmul_rn(io.base_scale, ns), io.noise_scale);
+    }
+  }
+}
+
 __device__ __forceinline__ void atomic_max_f(float* addr, float v) {
   if (v >= 0.f) atomicMax(reinterpret_cast<int*>(addr), __float_as_int(v));
   else atomicMin(reinterpret_cast<unsigned int*>(addr), __float_as_uint(v));

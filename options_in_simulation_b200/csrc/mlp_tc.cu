@@ -13,8 +13,10 @@
 //   * MMA: one elected thread issues tcgen05.mma.cta_group::1.kind::f16, M=128, N=64 pieces with fp32
 //     accumulators ping-ponging between two 64-column TMEM buffers; layer-3 partial products (A = the 64-column
 //     slice of act2 just activated, in shared memory) are issued one piece behind layer 2;
-//   * epilogue: 8 warps (two per TMEM lane quadrant) tcgen05.ld the accumulators, add bias, ELU, convert to
-//     bf16 and tcgen05.st / st.shared the next operand;
+//   * epilogue: two groups of 4 warps (one warp per TMEM lane quadrant in each group) take ALTERNATE 64-column
+//     pieces, so one group's tcgen05.ld / mbarrier latencies hide behind the other group's arithmetic; layer 1
+//     runs on four accumulator buffers (the layer-3 region is free then), layers 2 on two; each warp
+//     tcgen05.ld's the accumulators, adds bias, ELU, converts to bf16 and tcgen05.st / st.shared's the operand;
 //   * the last epilogue applies Sigmoid/Tanh, the OU exploration noise (explore.cuh) and the clamp.
 // fp32 master weights are untouched; accumulation is fp32; tolerance vs the fp32 oracle: tests/test_agent_gpu.py.
 #include "agent.cuh"
@@ -39,12 +41,14 @@ constexpr int kOffW = 0;                                    // 10 x 16 KB weight
 constexpr int kOffRing = kOffW + kStages * kStageBytes;     // 3 x 16 KB act2 slices
 constexpr int kOffX = kOffRing + kRingSlots * 16384;        // [2 kc][128][8] = 4 KB
 constexpr int kOffBias = kOffX + kTileM * kInPad * 2;       // b1 512, b2 512, b3 128, b4 16 fp32
-constexpr int kOffBar = kOffBias + (kH0 + kH1 + kH2 + kOutPad) * 4;
+constexpr int kOffScale = kOffBias + (kH0 + kH1 + kH2 + kOutPad) * 4;   // scaler: mean[16], sqrt(var)+eps[16] fp32
+constexpr int kOffBar = kOffScale + 2 * kInPad * 4;
 constexpr int kSmemBytes = kOffBar + 512;
 // TMEM columns
 constexpr int kColAct = 0;      // act1 as bf16 pairs: 256 columns (act3 later reuses columns 0..63)
-constexpr int kColD = 256;      // two ping-pong 64-column fp32 accumulators (layers 1, 2; layer 4 uses buffer 0)
-constexpr int kColD3 = 384;     // layer 3, 128 columns
+constexpr int kColD = 256;      // 64-column fp32 accumulator buffers: 0, 1 (layers 1, 2; layer 4 uses buffer 0) ...
+constexpr int kColD3 = 384;     // ... 2, 3 during layer 1 only; then the 128 columns of layer 3
+constexpr int kDBufs = 4;
 constexpr int kTmemCols = 512;
 
 // stream order: W1 | W2 q0 (4 k-blocks of 128) | W2 q1 | W3 p0 | W2 q2 | W3 p1 | ... | W2 q7 | W3 p6 | W3 p7 | W4
@@ -105,8 +109,19 @@ tc_pack_kernel(const float* __restrict__ P, uint4* __restrict__ image, int in_di
 // ----------------------------------------------------------------------------------------------------------
 // epilogue helpers (8 warps; warp quadrant = warp_id % 4 is the TMEM lane group the hardware lets it access)
 // ----------------------------------------------------------------------------------------------------------
-__device__ __forceinline__ float elu_fast(float x) {   // bf16 output: ex2.approx is far inside the tolerance
-  return x > 0.f ? x : __expf(x) - 1.0f;
+// ELU on a pair of pre-activations.  exp(x) = ex2(x log2 e) is ONE MUFU.EX2 (ex2.approx.ftz: no range fix-up — the result
+// is rounded to bf16, and for x < -126/log2(e) it flushes to 0, i.e. ELU = -1, which is the bf16 answer anyway); the
+// bias add, the log2(e) scale and the "- 1" run as packed FADD2 / FMUL2 (two elements per instruction on sm_100).
+__device__ __forceinline__ float ex2_approx(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+__device__ __forceinline__ uint32_t bias_elu_pack(float2 acc, float2 bias) {
+  const float2 x = __fadd2_rn(acc, bias);
+  const float2 t = __fmul2_rn(x, make_float2(1.4426950408889634f, 1.4426950408889634f));
+  const float2 em1 = __fadd2_rn(make_float2(ex2_approx(t.x), ex2_approx(t.y)), make_float2(-1.0f, -1.0f));
+  return ptx::pack_bf16(x.x > 0.f ? x.x : em1.x, x.y > 0.f ? x.y : em1.y);
 }
 
 // 32 fp32 accumulator columns of this thread's row -> +bias -> ELU -> 16 bf16 pairs
@@ -114,12 +129,10 @@ __device__ __forceinline__ void epi_load_act(uint32_t taddr, const float* __rest
   uint32_t v[32];
   ptx::tmem_ld32(taddr, v);
   ptx::tmem_ld_wait();
+  const float2* b2 = reinterpret_cast<const float2*>(bias);
 #pragma unroll
-  for (int e = 0; e < 16; ++e) {
-    const float a = elu_fast(__uint_as_float(v[2 * e]) + bias[2 * e]);
-    const float b = elu_fast(__uint_as_float(v[2 * e + 1]) + bias[2 * e + 1]);
-    w[e] = ptx::pack_bf16(a, b);
-  }
+  for (int e = 0; e < 16; ++e)
+    w[e] = bias_elu_pack(make_float2(__uint_as_float(v[2 * e]), __uint_as_float(v[2 * e + 1])), b2[e]);
 }
 
 // Diagnostics (not part of the public ABI): per-phase %globaltimer stamps of CTA 0, read by profiles/tc_trace.py.
@@ -149,13 +162,14 @@ tc_actor_kernel(const __grid_constant__ TcActArgs args) {
   uint8_t* s_ring = smem + kOffRing;
   uint8_t* s_x = smem + kOffX;
   float* s_bias = reinterpret_cast<float*>(smem + kOffBias);
+  float* s_scale = reinterpret_cast<float*>(smem + kOffScale);
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + kOffBar);
   uint64_t* w_full = bars;                    // [10]
   uint64_t* w_empty = bars + kStages;         // [10]
   uint64_t* x_ready = bars + 2 * kStages;
-  uint64_t* d_full = x_ready + 1;             // [2]
-  uint64_t* d_empty = d_full + 2;             // [2]
-  uint64_t* act1_ready = d_empty + 2;
+  uint64_t* d_full = x_ready + 1;             // [4]
+  uint64_t* d_empty = d_full + kDBufs;        // [4]
+  uint64_t* act1_ready = d_empty + kDBufs;
   uint64_t* slot_ready = act1_ready + 1;      // [3]
   uint64_t* slot_free = slot_ready + kRingSlots;   // [3]
   uint64_t* d3_full = slot_free + kRingSlots;
@@ -171,9 +185,9 @@ tc_actor_kernel(const __grid_constant__ TcActArgs args) {
   if (threadIdx.x == 0) {
     for (int i = 0; i < kStages; ++i) { ptx::mbar_init(&w_full[i], 1); ptx::mbar_init(&w_empty[i], 1); }
     ptx::mbar_init(x_ready, kEpiWarps);
-    for (int i = 0; i < 2; ++i) { ptx::mbar_init(&d_full[i], 1); ptx::mbar_init(&d_empty[i], kEpiWarps); }
-    ptx::mbar_init(act1_ready, kEpiWarps * 8);
-    for (int i = 0; i < kRingSlots; ++i) { ptx::mbar_init(&slot_ready[i], kEpiWarps); ptx::mbar_init(&slot_free[i], 1); }
+    for (int i = 0; i < kDBufs; ++i) { ptx::mbar_init(&d_full[i], 1); ptx::mbar_init(&d_empty[i], kEpiWarps / 2); }
+    ptx::mbar_init(act1_ready, (kEpiWarps / 2) * 8);       // 8 pieces, each finished by the 4 warps of one group
+    for (int i = 0; i < kRingSlots; ++i) { ptx::mbar_init(&slot_ready[i], kEpiWarps / 2); ptx::mbar_init(&slot_free[i], 1); }
     ptx::mbar_init(d3_full, 1);
     ptx::mbar_init(act3_ready, kEpiWarps);
     ptx::fence_barrier_init();
@@ -189,6 +203,13 @@ tc_actor_kernel(const __grid_constant__ TcActArgs args) {
       else if (i < kH0 + kH1 + kH2) v = args.params[b2 + i - kH0 - kH1];
       else v = (i - kH0 - kH1 - kH2) < args.out_dim ? args.params[b3 + i - kH0 - kH1 - kH2] : 0.f;
       s_bias[i] = v;
+    }
+    if (threadIdx.x - 64 < 2 * kInPad) {   // RunningStandardScaler constants: mean.float(), sqrt(var.float()) + eps
+      const int c = (threadIdx.x - 64) & (kInPad - 1);
+      const bool is_mean = threadIdx.x - 64 < kInPad;
+      float v = is_mean ? 0.f : 1.f;
+      if (args.mean != nullptr && c < args.in_dim) v = is_mean ? (float)args.mean[c] : __fadd_rn(sqrtf((float)args.var[c]), 1e-8f);
+      s_scale[threadIdx.x - 64] = v;
     }
   }
   ptx::tc_fence_before();
@@ -222,7 +243,7 @@ tc_actor_kernel(const __grid_constant__ TcActArgs args) {
       const uint32_t ring = ptx::smem_u32(s_ring), xs = ptx::smem_u32(s_x), ws = ptx::smem_u32(s_w);
       const uint32_t x_lo = ptx::smem_desc_lo(xs, 2048);
       uint32_t n = 0;            // weight stages consumed
-      uint32_t d_uses[2] = {0, 0}, slot_uses[kRingSlots] = {0, 0, 0};
+      uint32_t d_uses[kDBufs] = {0, 0, 0, 0}, slot_uses[kRingSlots] = {0, 0, 0};
       uint32_t tiles_done = 0;
       auto wait_stage = [&]() -> uint32_t {
         const int slot = n % kStages;
@@ -249,11 +270,11 @@ tc_actor_kernel(const __grid_constant__ TcActArgs args) {
           const uint32_t w_lo = ptx::smem_desc_lo(wait_stage(), 8192);
           TC_STAMP(tr && tiles_done == 0, 33);
 #pragma unroll
-          for (int q = 0; q < 8; ++q) {
-            acquire_d(q & 1);
+          for (int q = 0; q < 8; ++q) {    // four accumulator buffers: the layer-3 columns are free during layer 1
+            acquire_d(q & 3);
             if (leader) {
-              ptx::mma_ss(tmem + kColD + (q & 1) * 64, ptx::make_desc(x_lo, hi), ptx::make_desc(w_lo + q * (1024 >> 4), hi), id64, false);
-              ptx::mma_commit(&d_full[q & 1]);
+              ptx::mma_ss(tmem + kColD + (q & 3) * 64, ptx::make_desc(x_lo, hi), ptx::make_desc(w_lo + q * (1024 >> 4), hi), id64, false);
+              ptx::mma_commit(&d_full[q & 3]);
             }
             __syncwarp();
           }
@@ -334,14 +355,13 @@ tc_actor_kernel(const __grid_constant__ TcActArgs args) {
       }
     }
   } else {
-    // ===================================================== epilogue warps
+    // ===================================================== epilogue warps: two groups of four (one per TMEM lane quadrant)
     const int e = warp - 2;                 // 0..7
     const int quad = warp & 3;              // TMEM lane quadrant this warp may access
-    const int half = e >> 2;                // which 32 of a piece's 64 columns
+    const int g = e >> 2;                   // group: takes the pieces q with (q & 1) == g
     const int row = quad * 32 + lane;       // row of the tile == TMEM lane
     const uint32_t t_lane = tmem + ((uint32_t)(quad * 32) << 16);
-    const bool has_scaler = args.mean != nullptr;
-    uint32_t d_cnt[2] = {0, 0}, slot_cnt[kRingSlots] = {0, 0, 0}, tiles_done = 0;
+    uint32_t d_cnt[kDBufs] = {0, 0, 0, 0}, tiles_done = 0;
     auto warp_arrive = [&](uint64_t* bar) {
       __syncwarp();
       if (lane == 0) ptx::mbar_arrive(bar);
@@ -351,60 +371,75 @@ tc_actor_kernel(const __grid_constant__ TcActArgs args) {
       ++d_cnt[b];
       ptx::tc_fence_after();
     };
+    const int A = args.out_dim;
+    const bool row_noise = args.io.ou_state != nullptr && (A == 1 || A == 2 || A == 4);
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++tiles_done) {
       const uint32_t tpar = tiles_done & 1;
       const int64_t grow = (int64_t)tile * kTileM + row;
-      // ---- X: scaler + bf16, K padded to 16 (half-0 warps write k 0..7, half-1 warps k 8..15)
+      // ---- X: scaler + bf16, K padded to 16 (group 0 writes k 0..7, group 1 k 8..15)
       {
         float x[8];
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
-          const int c = half * 8 + j;
-          float v = 0.f;
-          if (c < args.in_dim && grow < args.rows) {
-            v = args.io.states[grow * args.in_dim + c];
-            if (has_scaler)
-              v = fminf(fmaxf(__fdiv_rn(__fsub_rn(v, (float)args.mean[c]), __fadd_rn(sqrtf((float)args.var[c]), 1e-8f)), -5.0f), 5.0f);
-          }
-          x[j] = v;
+          const int c = g * 8 + j;
+          x[j] = (c < args.in_dim && grow < args.rows) ? args.io.states[grow * args.in_dim + c] : 0.f;
         }
-        *reinterpret_cast<uint4*>(s_x + half * 2048 + row * 16) =
+        if (args.mean != nullptr) {
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            const int c = g * 8 + j;
+            if (c < args.in_dim)
+              x[j] = fminf(fmaxf(__fdiv_rn(__fsub_rn(x[j], s_scale[c]), s_scale[kInPad + c]), -5.0f), 5.0f);
+          }
+        }
+        *reinterpret_cast<uint4*>(s_x + g * 2048 + row * 16) =
             make_uint4(ptx::pack_bf16(x[0], x[1]), ptx::pack_bf16(x[2], x[3]), ptx::pack_bf16(x[4], x[5]), ptx::pack_bf16(x[6], x[7]));
         ptx::fence_async_smem();
         warp_arrive(x_ready);
         TC_STAMP(tr && warp == 2 && tiles_done == 0, 2);
       }
-      // ---- layer 1 pieces -> act1 (TMEM, bf16 pairs)
-      for (int q = 0; q < 8; ++q) {
-        const int b = q & 1;
+      // ---- layer 1: this group's pieces (64 columns each) -> act1 (TMEM, bf16 pairs)
+      for (int q = g; q < 8; q += 2) {
+        const int b = q & 3;
         wait_d(b);
-        uint32_t w[16];
-        epi_load_act(t_lane + kColD + b * 64 + half * 32, s_bias + q * 64 + half * 32, w);
-        ptx::tmem_st16(t_lane + kColAct + q * 32 + half * 16, w);
+#pragma unroll
+        for (int c = 0; c < 2; ++c) {
+          uint32_t w[16];
+          epi_load_act(t_lane + kColD + b * 64 + c * 32, s_bias + q * 64 + c * 32, w);
+          ptx::tmem_st16(t_lane + kColAct + q * 32 + c * 16, w);
+        }
         ptx::tmem_st_wait();
         ptx::tc_fence_before();
         warp_arrive(&d_empty[b]);
         warp_arrive(act1_ready);
-        TC_STAMP(tr && warp == 2 && tiles_done == 0, 3 + q);
+        TC_STAMP(tr && (warp == 2 || warp == 6) && tiles_done == 0, 3 + q);
       }
-      // ---- layer 2 pieces -> one 64-column slice of act2 each, in the shared-memory ring
-      for (int q = 0; q < 8; ++q) {
-        const int b = q & 1, slot = q % kRingSlots;
-        wait_d(b);
-        uint32_t w[16];
-        epi_load_act(t_lane + kColD + b * 64 + half * 32, s_bias + kH0 + q * 64 + half * 32, w);
+      // ---- layer 2: this group's pieces -> one 64-column slice of act2 each, in the shared-memory ring
+      for (int q = g; q < 8; q += 2) {
+        const int slot = q % kRingSlots;
+        wait_d(g);
+        uint32_t w0[16], w1[16];
+        epi_load_act(t_lane + kColD + g * 64, s_bias + kH0 + q * 64, w0);
+        epi_load_act(t_lane + kColD + g * 64 + 32, s_bias + kH0 + q * 64 + 32, w1);
         ptx::tc_fence_before();
-        warp_arrive(&d_empty[b]);                                           // accumulator drained
-        ptx::mbar_wait(&slot_free[slot], (slot_cnt[slot] & 1) ^ 1);         // previous user of the slot consumed
-        ++slot_cnt[slot];
-        uint8_t* dst = s_ring + slot * 16384 + (half * 4) * 2048 + row * 16;
+        warp_arrive(&d_empty[g]);                                           // accumulator drained
+        // slot `slot` is used by the pieces q = slot, slot + 3, (slot + 6): use number = tiles * uses-per-tile + q / 3
+        const uint32_t use = tiles_done * (slot == 2 ? 2u : 3u) + (uint32_t)(q / kRingSlots);
+        ptx::mbar_wait(&slot_free[slot], (use & 1) ^ 1);                    // previous user of the slot consumed
+        uint8_t* dst = s_ring + slot * 16384 + row * 16;
 #pragma unroll
-        for (int j = 0; j < 4; ++j)
-          *reinterpret_cast<uint4*>(dst + j * 2048) = make_uint4(w[4 * j], w[4 * j + 1], w[4 * j + 2], w[4 * j + 3]);
+        for (int j = 0; j < 4; ++j) {
+          *reinterpret_cast<uint4*>(dst + j * 2048) = make_uint4(w0[4 * j], w0[4 * j + 1], w0[4 * j + 2], w0[4 * j + 3]);
+          *reinterpret_cast<uint4*>(dst + (4 + j) * 2048) = make_uint4(w1[4 * j], w1[4 * j + 1], w1[4 * j + 2], w1[4 * j + 3]);
+        }
         ptx::fence_async_smem();
         warp_arrive(&slot_ready[slot]);
-        TC_STAMP(tr && warp == 2 && tiles_done == 0, 11 + q);
+        TC_STAMP(tr && (warp == 2 || warp == 6) && tiles_done == 0, 11 + q);
       }
+      // ---- exploration noise of this row, prepared while the last layer-2 / layer-3 MMAs run (group 0 owns the output)
+      float nz[4] = {0.f, 0.f, 0.f, 0.f};
+      bool applied = false;
+      if (g == 0 && row_noise && grow < args.rows) explore_row_prepare(args.io, grow, A, nz, applied);
       // ---- layer 3 -> act3 (TMEM columns 0..63; act1 is dead: every layer-2 MMA has completed)
       ptx::mbar_wait(d3_full, tpar);
       ptx::tc_fence_after();
@@ -412,44 +447,63 @@ tc_actor_kernel(const __grid_constant__ TcActArgs args) {
 #pragma unroll
       for (int c = 0; c < 2; ++c) {
         uint32_t w[16];
-        epi_load_act(t_lane + kColD3 + half * 64 + c * 32, s_bias + kH0 + kH1 + half * 64 + c * 32, w);
-        ptx::tmem_st16(t_lane + kColAct + half * 32 + c * 16, w);
+        epi_load_act(t_lane + kColD3 + g * 64 + c * 32, s_bias + kH0 + kH1 + g * 64 + c * 32, w);
+        ptx::tmem_st16(t_lane + kColAct + g * 32 + c * 16, w);
       }
       ptx::tmem_st_wait();
       ptx::tc_fence_before();
       warp_arrive(act3_ready);
       TC_STAMP(tr && warp == 2 && tiles_done == 0, 20);
-      // ---- layer 4 -> output activation -> exploration -> actions
-      wait_d(0);
-      TC_STAMP(tr && warp == 2 && tiles_done == 0, 21);
-      if (half == 0) {
+      // ---- layer 4 -> output activation -> exploration -> actions (group 0; accumulator buffer 0)
+      if (g == 0) {
+        wait_d(0);
+        TC_STAMP(tr && warp == 2 && tiles_done == 0, 21);
         uint32_t v[16];
         ptx::tmem_ld16(t_lane + kColD, v);
         ptx::tmem_ld_wait();
+        ptx::tc_fence_before();
+        warp_arrive(&d_empty[0]);
         float mx = -INFINITY, mn = INFINITY, sm = 0.f;
         if (grow < args.rows) {
           const float* b4 = s_bias + kH0 + kH1 + kH2;
+          float a[8];
 #pragma unroll
           for (int j = 0; j < 8; ++j) {
-            if (j < args.out_dim) {
-              const float z = __uint_as_float(v[j]) + b4[j];
-              float a = args.out_act == OIS_ACT_SIGMOID ? 1.0f / (1.0f + __expf(-z)) : args.out_act == OIS_ACT_TANH ? tanhf(z) : z;
-              const int64_t i = grow * args.out_dim + j;
-              if (args.io.ou_state) {
-                float nz = 0.f;
-                bool have = false;
-                a = explore_elem(args.io, i, a, nz, have);
-                if (have) { mx = fmaxf(mx, nz); mn = fminf(mn, nz); sm += nz; }
+            const float z = __uint_as_float(v[j]) + b4[j];
+            a[j] = args.out_act == OIS_ACT_SIGMOID ? 1.0f / (1.0f + __expf(-z)) : args.out_act == OIS_ACT_TANH ? tanhf(z) : z;
+          }
+          if (row_noise) {
+            if (applied) {
+#pragma unroll
+              for (int j = 0; j < 4; ++j) {
+                if (j < A) {
+                  a[j] = fminf(fmaxf(__fadd_rn(a[j], nz[j]), args.io.clip_low), args.io.clip_high);
+                  mx = fmaxf(mx, nz[j]); mn = fminf(mn, nz[j]); sm += nz[j];
+                }
               }
-              args.io.actions[i] = a;
             }
+          } else if (args.io.ou_state) {   // act_dim not in {1, 2, 4}: element-wise path
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+              if (j < A) {
+                float n1 = 0.f;
+                bool have = false;
+                a[j] = explore_elem(args.io, grow * A + j, a[j], n1, have);
+                if (have) { mx = fmaxf(mx, n1); mn = fminf(mn, n1); sm += n1; }
+              }
+            }
+          }
+          float* out = args.io.actions + grow * A;
+          if (A == 4) *reinterpret_cast<float4*>(out) = make_float4(a[0], a[1], a[2], a[3]);
+          else if (A == 2) *reinterpret_cast<float2*>(out) = make_float2(a[0], a[1]);
+          else {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) if (j < A) out[j] = a[j];
           }
         }
         if (args.io.noise_stats && args.io.ou_state && args.io.noise_scale >= 0.f) noise_stats_warp(args.io, mx, mn, sm);
+        TC_STAMP(tr && warp == 2 && tiles_done == 0, 22);
       }
-      ptx::tc_fence_before();
-      warp_arrive(&d_empty[0]);
-      TC_STAMP(tr && warp == 2 && tiles_done == 0, 22);
     }
   }
   // ---- teardown

@@ -27,7 +27,9 @@ namespace ois {
 
 namespace tc {
 constexpr int kTileM = 128;
-constexpr int kThreads = 320;             // warp 0: bulk-copy producer, warp 1: MMA issuer, warps 2-9: epilogue
+constexpr int kThreads = 416;             // warp 0 and warps 10-12: bulk-copy producers, warp 1: MMA issuer, warps 2-9: epilogue
+constexpr int kProducers = 4;             // one issuing thread sustains one bulk copy per ~520 cycles whatever its size
+                                          // (profiles/mma_rate.cu: 62 GB/s at 16 KB); four reach ~220 GB/s per SM
 constexpr int kEpiWarps = 8;
 constexpr int kH0 = 512, kH1 = 512, kH2 = 128, kInPad = 16, kOutPad = 16;
 constexpr int kStageBytes = 16384;
@@ -124,15 +126,25 @@ __device__ __forceinline__ uint32_t bias_elu_pack(float2 acc, float2 bias) {
   return ptx::pack_bf16(x.x > 0.f ? x.x : em1.x, x.y > 0.f ? x.y : em1.y);
 }
 
-// 32 fp32 accumulator columns of this thread's row -> +bias -> ELU -> 16 bf16 pairs
-__device__ __forceinline__ void epi_load_act(uint32_t taddr, const float* __restrict__ bias, uint32_t (&w)[16]) {
-  uint32_t v[32];
-  ptx::tmem_ld32(taddr, v);
-  ptx::tmem_ld_wait();
+// 32 fp32 accumulator columns of this thread's row -> +bias -> ELU -> 16 bf16 pairs.  The TMEM load and the arithmetic
+// are separate so that the accumulator buffer can be handed back to the MMA warp as soon as the load has landed.
+__device__ __forceinline__ void epi_act(const uint32_t (&v)[32], const float* __restrict__ bias, uint32_t (&w)[16]) {
   const float2* b2 = reinterpret_cast<const float2*>(bias);
 #pragma unroll
   for (int e = 0; e < 16; ++e)
     w[e] = bias_elu_pack(make_float2(__uint_as_float(v[2 * e]), __uint_as_float(v[2 * e + 1])), b2[e]);
+}
+__device__ __forceinline__ void epi_load_act(uint32_t taddr, const float* __restrict__ bias, uint32_t (&w)[16]) {
+  uint32_t v[32];
+  ptx::tmem_ld32(taddr, v);
+  ptx::tmem_ld_wait();
+  epi_act(v, bias, w);
+}
+__device__ __forceinline__ float sigmoid_fast(float z) { return __fdividef(1.0f, 1.0f + ex2_approx(-1.4426950408889634f * z)); }
+__device__ __forceinline__ float tanh_fast(float z) {
+  float y;
+  asm("tanh.approx.f32 %0, %1;" : "=f"(y) : "f"(z));
+  return y;
 }
 
 // Diagnostics (not part of the public ABI): per-phase %globaltimer stamps of CTA 0, read by profiles/tc_trace.py.
@@ -143,6 +155,11 @@ __device__ __forceinline__ void tc_stamp(int slot) {
   g_tc_trace[slot] = t;
 }
 #define TC_STAMP(cond, slot) do { if (cond) tc_stamp(slot); } while (0)
+#ifdef OIS_TC_DIAG      // per-wait cycle counters of the MMA warp (profiles/tc_trace.py); off in the product build
+#define TC_CLOCK() clock64()
+#else
+#define TC_CLOCK() 0ll
+#endif
 
 struct TcActArgs {
   const float* params;        // fp32 master (biases are read from it)
@@ -193,10 +210,10 @@ tc_actor_kernel(const __grid_constant__ TcActArgs args) {
     ptx::fence_barrier_init();
   }
   if (warp == 1) ptx::tmem_alloc<kTmemCols>(tmem_slot);
-  if (warp >= 2) {   // biases: fp32, straight from the master parameters
+  if (warp >= 2 && warp < 2 + kEpiWarps) {   // biases: fp32, straight from the master parameters
     const int64_t b0 = (int64_t)kH0 * args.in_dim, w1 = b0 + kH0, b1 = w1 + (int64_t)kH1 * kH0, w2 = b1 + kH1;
     const int64_t b2 = w2 + (int64_t)kH2 * kH1, w3 = b2 + kH2, b3 = w3 + (int64_t)args.out_dim * kH2;
-    for (int i = threadIdx.x - 64; i < kH0 + kH1 + kH2 + kOutPad; i += kThreads - 64) {
+    for (int i = threadIdx.x - 64; i < kH0 + kH1 + kH2 + kOutPad; i += kEpiWarps * 32) {
       float v;
       if (i < kH0) v = args.params[b0 + i];
       else if (i < kH0 + kH1) v = args.params[b1 + i - kH0];
@@ -218,12 +235,15 @@ tc_actor_kernel(const __grid_constant__ TcActArgs args) {
   const uint32_t tmem = *tmem_slot;
   TC_STAMP(tr && warp == 2, 1);
 
-  if (warp == 0) {
-    // ===================================================== producer: stream the weight image, tile after tile
+  if (warp == 0 || warp >= 2 + kEpiWarps) {
+    // ===================================================== producers: stream the weight image, tile after tile; producer p
+    // issues the stages n with n % kProducers == p (n counts stages across tiles, the ring slot is n % kStages)
     if (lane == 0) {
-      uint32_t n = 0;   // stages issued so far
+      const int p = warp == 0 ? 0 : warp - (1 + kEpiWarps);
+      uint32_t n = 0;   // stages issued so far by all producers
       for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
         for (int s = 0; s < kStreamStages; ++s, ++n) {
+          if ((int)(n % kProducers) != p) continue;
           const int slot = n % kStages;
           ptx::mbar_wait(&w_empty[slot], ((n / kStages) & 1) ^ 1);
           const uint32_t bytes = s == kStreamStages - 1 ? kLastStageBytes : kStageBytes;
@@ -245,9 +265,12 @@ tc_actor_kernel(const __grid_constant__ TcActArgs args) {
       uint32_t n = 0;            // weight stages consumed
       uint32_t d_uses[kDBufs] = {0, 0, 0, 0}, slot_uses[kRingSlots] = {0, 0, 0};
       uint32_t tiles_done = 0;
+      long long t_w = 0, t_d = 0, t_s = 0;      // diagnostics: cycles this warp spent waiting for weights / accumulators / act2 slices
       auto wait_stage = [&]() -> uint32_t {
         const int slot = n % kStages;
+        const long long c0 = TC_CLOCK();
         ptx::mbar_wait(&w_full[slot], (n / kStages) & 1);
+        t_w += TC_CLOCK() - c0;
         ptx::tc_fence_after();
         return ws + slot * kStageBytes;
       };
@@ -256,7 +279,9 @@ tc_actor_kernel(const __grid_constant__ TcActArgs args) {
         ++n;
       };
       auto acquire_d = [&](int b) {
+        const long long c0 = TC_CLOCK();
         ptx::mbar_wait(&d_empty[b], (d_uses[b] & 1) ^ 1);
+        t_d += TC_CLOCK() - c0;
         ptx::tc_fence_after();
         ++d_uses[b];
       };
@@ -299,7 +324,9 @@ tc_actor_kernel(const __grid_constant__ TcActArgs args) {
         };
         auto l3_partial = [&](int p) {   // act2[:, 64p .. 64p+64] (smem slice) x W3[:, 64p .. 64p+64]^T
           const int slot = p % kRingSlots;
+          const long long c0 = TC_CLOCK();
           ptx::mbar_wait(&slot_ready[slot], slot_uses[slot] & 1);
+          t_s += TC_CLOCK() - c0;
           ++slot_uses[slot];
           ptx::tc_fence_after();
           const uint32_t w_lo = ptx::smem_desc_lo(wait_stage(), 2048);
@@ -351,6 +378,7 @@ tc_actor_kernel(const __grid_constant__ TcActArgs args) {
           if (leader) ptx::mma_commit(&d_full[0]);
           __syncwarp();
           TC_STAMP(tr && tiles_done == 0, 39);
+          if (tr && tiles_done == 0) { g_tc_trace[40] = t_w; g_tc_trace[41] = t_d; g_tc_trace[42] = t_s; }
         }
       }
     }
@@ -373,59 +401,81 @@ tc_actor_kernel(const __grid_constant__ TcActArgs args) {
     };
     const int A = args.out_dim;
     const bool row_noise = args.io.ou_state != nullptr && (A == 1 || A == 2 || A == 4);
-    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++tiles_done) {
-      const uint32_t tpar = tiles_done & 1;
-      const int64_t grow = (int64_t)tile * kTileM + row;
-      // ---- X: scaler + bf16, K padded to 16 (group 0 writes k 0..7, group 1 k 8..15)
-      {
-        float x[8];
+    // X of one tile: raw loads into registers (issued early, consumed a layer later), then scaler + bf16 + smem
+    auto load_x = [&](int tile, float (&x)[8]) {
+      const int64_t r = (int64_t)tile * kTileM + row;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const int c = g * 8 + j;
+        x[j] = (c < args.in_dim && r < args.rows) ? args.io.states[r * args.in_dim + c] : 0.f;
+      }
+    };
+    auto write_x = [&](float (&x)[8]) {     // K padded to 16: group 0 writes k 0..7, group 1 k 8..15
+      if (args.mean != nullptr) {
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
           const int c = g * 8 + j;
-          x[j] = (c < args.in_dim && grow < args.rows) ? args.io.states[grow * args.in_dim + c] : 0.f;
+          if (c < args.in_dim) x[j] = fminf(fmaxf(__fdiv_rn(__fsub_rn(x[j], s_scale[c]), s_scale[kInPad + c]), -5.0f), 5.0f);
         }
-        if (args.mean != nullptr) {
-#pragma unroll
-          for (int j = 0; j < 8; ++j) {
-            const int c = g * 8 + j;
-            if (c < args.in_dim)
-              x[j] = fminf(fmaxf(__fdiv_rn(__fsub_rn(x[j], s_scale[c]), s_scale[kInPad + c]), -5.0f), 5.0f);
-          }
-        }
-        *reinterpret_cast<uint4*>(s_x + g * 2048 + row * 16) =
-            make_uint4(ptx::pack_bf16(x[0], x[1]), ptx::pack_bf16(x[2], x[3]), ptx::pack_bf16(x[4], x[5]), ptx::pack_bf16(x[6], x[7]));
-        ptx::fence_async_smem();
-        warp_arrive(x_ready);
-        TC_STAMP(tr && warp == 2 && tiles_done == 0, 2);
       }
+      *reinterpret_cast<uint4*>(s_x + g * 2048 + row * 16) =
+          make_uint4(ptx::pack_bf16(x[0], x[1]), ptx::pack_bf16(x[2], x[3]), ptx::pack_bf16(x[4], x[5]), ptx::pack_bf16(x[6], x[7]));
+      ptx::fence_async_smem();
+      warp_arrive(x_ready);
+    };
+    float xr[8];
+    if ((int)blockIdx.x < num_tiles) {
+      load_x(blockIdx.x, xr);
+      write_x(xr);
+      TC_STAMP(tr && warp == 2, 2);
+    }
+    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++tiles_done) {
+      const uint32_t tpar = tiles_done & 1;
+      const int64_t grow = (int64_t)tile * kTileM + row;
+      const int next_tile = tile + gridDim.x;
       // ---- layer 1: this group's pieces (64 columns each) -> act1 (TMEM, bf16 pairs)
       for (int q = g; q < 8; q += 2) {
         const int b = q & 3;
         wait_d(b);
-#pragma unroll
-        for (int c = 0; c < 2; ++c) {
-          uint32_t w[16];
-          epi_load_act(t_lane + kColD + b * 64 + c * 32, s_bias + q * 64 + c * 32, w);
-          ptx::tmem_st16(t_lane + kColAct + q * 32 + c * 16, w);
-        }
+        uint32_t v0[32], v1[32];
+        ptx::tmem_ld32(t_lane + kColD + b * 64, v0);
+        ptx::tmem_ld32(t_lane + kColD + b * 64 + 32, v1);
+        ptx::tmem_ld_wait();
+        ptx::tc_fence_before();
+        warp_arrive(&d_empty[b]);                                           // accumulator drained: the MMA warp may refill it
+        uint32_t w[16];
+        epi_act(v0, s_bias + q * 64, w);
+        ptx::tmem_st16(t_lane + kColAct + q * 32, w);
+        epi_act(v1, s_bias + q * 64 + 32, w);
+        ptx::tmem_st16(t_lane + kColAct + q * 32 + 16, w);
         ptx::tmem_st_wait();
         ptx::tc_fence_before();
-        warp_arrive(&d_empty[b]);
         warp_arrive(act1_ready);
         TC_STAMP(tr && (warp == 2 || warp == 6) && tiles_done == 0, 3 + q);
       }
+      long long e_d = 0, e_s = 0;     // diagnostics (OIS_TC_DIAG): layer-2 waits of this warp for accumulators / ring slots
+      // the next tile's observations: loads in flight during layer 2
+      if (next_tile < num_tiles) load_x(next_tile, xr);
       // ---- layer 2: this group's pieces -> one 64-column slice of act2 each, in the shared-memory ring
       for (int q = g; q < 8; q += 2) {
         const int slot = q % kRingSlots;
+        const long long c0 = TC_CLOCK();
         wait_d(g);
-        uint32_t w0[16], w1[16];
-        epi_load_act(t_lane + kColD + g * 64, s_bias + kH0 + q * 64, w0);
-        epi_load_act(t_lane + kColD + g * 64 + 32, s_bias + kH0 + q * 64 + 32, w1);
+        e_d += TC_CLOCK() - c0;
+        uint32_t v0[32], v1[32];
+        ptx::tmem_ld32(t_lane + kColD + g * 64, v0);
+        ptx::tmem_ld32(t_lane + kColD + g * 64 + 32, v1);
+        ptx::tmem_ld_wait();
         ptx::tc_fence_before();
         warp_arrive(&d_empty[g]);                                           // accumulator drained
+        uint32_t w0[16], w1[16];
+        epi_act(v0, s_bias + kH0 + q * 64, w0);
+        epi_act(v1, s_bias + kH0 + q * 64 + 32, w1);
         // slot `slot` is used by the pieces q = slot, slot + 3, (slot + 6): use number = tiles * uses-per-tile + q / 3
         const uint32_t use = tiles_done * (slot == 2 ? 2u : 3u) + (uint32_t)(q / kRingSlots);
+        const long long c1 = TC_CLOCK();
         ptx::mbar_wait(&slot_free[slot], (use & 1) ^ 1);                    // previous user of the slot consumed
+        e_s += TC_CLOCK() - c1;
         uint8_t* dst = s_ring + slot * 16384 + row * 16;
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
@@ -436,6 +486,10 @@ tc_actor_kernel(const __grid_constant__ TcActArgs args) {
         warp_arrive(&slot_ready[slot]);
         TC_STAMP(tr && (warp == 2 || warp == 6) && tiles_done == 0, 11 + q);
       }
+      // every layer-1 MMA of this tile has completed (a layer-2 accumulator was seen full): the X buffer is free, so the
+      // next tile's layer 1 can start the moment the MMA warp gets there
+      if (next_tile < num_tiles) write_x(xr);
+      if (tr && tiles_done == 0 && (warp == 2 || warp == 6)) { g_tc_trace[43 + 2 * g] = e_d; g_tc_trace[44 + 2 * g] = e_s; }
       // ---- exploration noise of this row, prepared while the last layer-2 / layer-3 MMAs run (group 0 owns the output)
       float nz[4] = {0.f, 0.f, 0.f, 0.f};
       bool applied = false;
@@ -470,7 +524,7 @@ tc_actor_kernel(const __grid_constant__ TcActArgs args) {
 #pragma unroll
           for (int j = 0; j < 8; ++j) {
             const float z = __uint_as_float(v[j]) + b4[j];
-            a[j] = args.out_act == OIS_ACT_SIGMOID ? 1.0f / (1.0f + __expf(-z)) : args.out_act == OIS_ACT_TANH ? tanhf(z) : z;
+            a[j] = args.out_act == OIS_ACT_SIGMOID ? sigmoid_fast(z) : args.out_act == OIS_ACT_TANH ? tanh_fast(z) : z;
           }
           if (row_noise) {
             if (applied) {

@@ -43,3 +43,5 @@ for mode in ("warm", "cold"):
     print(f"--- {mode} L2, n={n}")
     for k in sorted(names, key=lambda k: buf[k]):
         print(f"{(buf[k] - t0) / 1e3:8.2f} us  {names[k]}")
+    print(f"MMA warp wait cycles in tile 0: weights {buf[40]}  accumulators {buf[41]}  act2 slices {buf[42]}")
+    print(f"epilogue layer-2 wait cycles: group 0 d_full {buf[43]} slot_free {buf[44]}; group 1 d_full {buf[45]} slot_free {buf[46]}")

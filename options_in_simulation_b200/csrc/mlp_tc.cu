@@ -27,22 +27,29 @@ namespace ois {
 
 namespace tc {
 constexpr int kTileM = 128;
-constexpr int kThreads = 416;             // warp 0 and warps 10-12: bulk-copy producers, warp 1: MMA issuer, warps 2-9: epilogue
-constexpr int kProducers = 4;             // one issuing thread sustains one bulk copy per ~520 cycles whatever its size
-                                          // (profiles/mma_rate.cu: 62 GB/s at 16 KB); four reach ~220 GB/s per SM
+// warp 0 and warps 10-12: bulk-copy producers; warp 1: MMA issuer A (layers 1, 2); warps 2-9: epilogue;
+// warp 13: MMA issuer B (layers 3, 4)
+constexpr int kThreads = 448;
 constexpr int kEpiWarps = 8;
+constexpr int kWarpB = 2 + kEpiWarps + 3;  // 13
 constexpr int kH0 = 512, kH1 = 512, kH2 = 128, kInPad = 16, kOutPad = 16;
-constexpr int kStageBytes = 16384;
-constexpr int kStages = 10;
-constexpr int kRingSlots = 3;             // act2 slices: [8 kc][128 rows][8] bf16 = 16 KB each
-constexpr int kStreamStages = 42;         // 1 (W1) + 32 (W2) + 8 (W3) + 1 (W4)
+constexpr int kStageBytes = 16384;         // unit of the weight image
+constexpr int kW2SlotBytes = 32768;        // layer-2 ring slot: half a 64-column piece (k-blocks 0-1 or 2-3)
+constexpr int kW2Slots = 3;
+constexpr int kW3Slots = 2;                // layer-3 ring slot: one 64-wide K slice of W3, 16 KB
+constexpr int kRingSlots = 3;              // act2 slices: [8 kc][128 rows][8] bf16 = 16 KB each
+constexpr int kStreamStages = 42;          // 1 (W1) + 32 (W2) + 8 (W3) + 1 (W4)
 constexpr int kLastStageBytes = kOutPad * kH2 * 2;                       // 4096
 constexpr size_t kImageBytes = (size_t)(kStreamStages - 1) * kStageBytes + kLastStageBytes;
+constexpr size_t kImgW1 = 0, kImgW2 = kStageBytes, kImgW3 = 33 * (size_t)kStageBytes, kImgW4 = 41 * (size_t)kStageBytes;
 // shared memory map (bytes)
-constexpr int kOffW = 0;                                    // 10 x 16 KB weight ring
-constexpr int kOffRing = kOffW + kStages * kStageBytes;     // 3 x 16 KB act2 slices
-constexpr int kOffX = kOffRing + kRingSlots * 16384;        // [2 kc][128][8] = 4 KB
-constexpr int kOffBias = kOffX + kTileM * kInPad * 2;       // b1 512, b2 512, b3 128, b4 16 fp32
+constexpr int kOffW2 = 0;                                      // 3 x 32 KB layer-2 weight ring
+constexpr int kOffW3 = kOffW2 + kW2Slots * kW2SlotBytes;       // 2 x 16 KB layer-3 weight ring
+constexpr int kOffW1 = kOffW3 + kW3Slots * kStageBytes;        // 16 KB, resident for the whole launch
+constexpr int kOffW4 = kOffW1 + kStageBytes;                   // 4 KB, resident
+constexpr int kOffRing = kOffW4 + kLastStageBytes;             // 3 x 16 KB act2 slices
+constexpr int kOffX = kOffRing + kRingSlots * 16384;           // [2 kc][128][8] = 4 KB
+constexpr int kOffBias = kOffX + kTileM * kInPad * 2;          // b1 512, b2 512, b3 128, b4 16 fp32
 constexpr int kOffScale = kOffBias + (kH0 + kH1 + kH2 + kOutPad) * 4;   // scaler: mean[16], sqrt(var)+eps[16] fp32
 constexpr int kOffBar = kOffScale + 2 * kInPad * 4;
 constexpr int kSmemBytes = kOffBar + 512;
@@ -51,17 +58,13 @@ constexpr int kColAct = 0;      // act1 as bf16 pairs: 256 columns (act3 later r
 constexpr int kColD = 256;      // 64-column fp32 accumulator buffers: 0, 1 (layers 1, 2; layer 4 uses buffer 0) ...
 constexpr int kColD3 = 384;     // ... 2, 3 during layer 1 only; then the 128 columns of layer 3
 constexpr int kDBufs = 4;
+constexpr int kBuf0UsesPerTile = 7;   // layer 1 pieces 0, 4; layer 2 pieces 0, 2, 4, 6; layer 4
 constexpr int kTmemCols = 512;
 
-// stream order: W1 | W2 q0 (4 k-blocks of 128) | W2 q1 | W3 p0 | W2 q2 | W3 p1 | ... | W2 q7 | W3 p6 | W3 p7 | W4
+// image order (16 KB stages): W1 | W2 piece 0 (4 k-blocks of 128) | ... | W2 piece 7 | W3 slice 0 .. 7 | W4 (4 KB)
 __host__ __device__ inline void stage_info(int s, int& layer, int& piece, int& kb) {
   if (s == 0) { layer = 1; piece = 0; kb = 0; }
-  else if (s < 9) { layer = 2; piece = (s - 1) >> 2; kb = (s - 1) & 3; }
-  else if (s < 39) {
-    const int g = (s - 9) / 5, r = (s - 9) % 5;
-    if (r == 0) { layer = 3; piece = g; kb = 0; }
-    else { layer = 2; piece = g + 2; kb = r - 1; }
-  }
+  else if (s < 33) { layer = 2; piece = (s - 1) >> 2; kb = (s - 1) & 3; }
   else if (s < 41) { layer = 3; piece = s - 33; kb = 0; }
   else { layer = 4; piece = 0; kb = 0; }
 }
@@ -175,15 +178,21 @@ __global__ void __launch_bounds__(tc::kThreads, 1)
 tc_actor_kernel(const __grid_constant__ TcActArgs args) {
   using namespace tc;
   extern __shared__ __align__(1024) uint8_t smem[];
-  uint8_t* s_w = smem + kOffW;
+  uint8_t* s_w2 = smem + kOffW2;
+  uint8_t* s_w3 = smem + kOffW3;
+  uint8_t* s_w1 = smem + kOffW1;
+  uint8_t* s_w4 = smem + kOffW4;
   uint8_t* s_ring = smem + kOffRing;
   uint8_t* s_x = smem + kOffX;
   float* s_bias = reinterpret_cast<float*>(smem + kOffBias);
   float* s_scale = reinterpret_cast<float*>(smem + kOffScale);
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + kOffBar);
-  uint64_t* w_full = bars;                    // [10]
-  uint64_t* w_empty = bars + kStages;         // [10]
-  uint64_t* x_ready = bars + 2 * kStages;
+  uint64_t* w2_full = bars;                   // [3]
+  uint64_t* w2_empty = w2_full + kW2Slots;    // [3]
+  uint64_t* w3_full = w2_empty + kW2Slots;    // [2]
+  uint64_t* w3_empty = w3_full + kW3Slots;    // [2]
+  uint64_t* wconst_full = w3_empty + kW3Slots;
+  uint64_t* x_ready = wconst_full + 1;
   uint64_t* d_full = x_ready + 1;             // [4]
   uint64_t* d_empty = d_full + kDBufs;        // [4]
   uint64_t* act1_ready = d_empty + kDBufs;
@@ -200,7 +209,9 @@ tc_actor_kernel(const __grid_constant__ TcActArgs args) {
 
   // ---- one-time setup
   if (threadIdx.x == 0) {
-    for (int i = 0; i < kStages; ++i) { ptx::mbar_init(&w_full[i], 1); ptx::mbar_init(&w_empty[i], 1); }
+    for (int i = 0; i < kW2Slots; ++i) { ptx::mbar_init(&w2_full[i], 1); ptx::mbar_init(&w2_empty[i], 1); }
+    for (int i = 0; i < kW3Slots; ++i) { ptx::mbar_init(&w3_full[i], 1); ptx::mbar_init(&w3_empty[i], 1); }
+    ptx::mbar_init(wconst_full, 1);
     ptx::mbar_init(x_ready, kEpiWarps);
     for (int i = 0; i < kDBufs; ++i) { ptx::mbar_init(&d_full[i], 1); ptx::mbar_init(&d_empty[i], kEpiWarps / 2); }
     ptx::mbar_init(act1_ready, (kEpiWarps / 2) * 8);       // 8 pieces, each finished by the 4 warps of one group
@@ -235,152 +246,161 @@ tc_actor_kernel(const __grid_constant__ TcActArgs args) {
   const uint32_t tmem = *tmem_slot;
   TC_STAMP(tr && warp == 2, 1);
 
-  if (warp == 0 || warp >= 2 + kEpiWarps) {
-    // ===================================================== producers: stream the weight image, tile after tile; producer p
-    // issues the stages n with n % kProducers == p (n counts stages across tiles, the ring slot is n % kStages)
+  if (warp == 0 || (warp >= 2 + kEpiWarps && warp < kWarpB)) {
+    // ===================================================== producers (one thread each; a thread sustains only one bulk copy
+    // per ~520 cycles whatever its size — profiles/mma_rate.cu): 0 and 1 alternate on the 32 KB half-pieces of W2,
+    // 2 streams the 16 KB K-slices of W3, 3 loads W1 and W4 once (they stay resident)
     if (lane == 0) {
       const int p = warp == 0 ? 0 : warp - (1 + kEpiWarps);
-      uint32_t n = 0;   // stages issued so far by all producers
-      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
-        for (int s = 0; s < kStreamStages; ++s, ++n) {
-          if ((int)(n % kProducers) != p) continue;
-          const int slot = n % kStages;
-          ptx::mbar_wait(&w_empty[slot], ((n / kStages) & 1) ^ 1);
-          const uint32_t bytes = s == kStreamStages - 1 ? kLastStageBytes : kStageBytes;
-          ptx::mbar_expect_tx(&w_full[slot], bytes);
-          ptx::bulk_g2s(s_w + slot * kStageBytes, args.image + (size_t)s * kStageBytes, bytes, &w_full[slot]);
+      if (p < 2) {
+        uint32_t n = 0;   // half-pieces issued so far by both W2 producers
+        for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+          for (int h = 0; h < 16; ++h, ++n) {
+            if ((int)(n & 1) != p) continue;
+            const int slot = n % kW2Slots;
+            ptx::mbar_wait(&w2_empty[slot], ((n / kW2Slots) & 1) ^ 1);
+            ptx::mbar_expect_tx(&w2_full[slot], kW2SlotBytes);
+            ptx::bulk_g2s(s_w2 + slot * kW2SlotBytes, args.image + kImgW2 + (size_t)h * kW2SlotBytes, kW2SlotBytes, &w2_full[slot]);
+          }
         }
+      } else if (p == 2) {
+        uint32_t n = 0;
+        for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+          for (int k = 0; k < 8; ++k, ++n) {
+            const int slot = n % kW3Slots;
+            ptx::mbar_wait(&w3_empty[slot], ((n / kW3Slots) & 1) ^ 1);
+            ptx::mbar_expect_tx(&w3_full[slot], kStageBytes);
+            ptx::bulk_g2s(s_w3 + slot * kStageBytes, args.image + kImgW3 + (size_t)k * kStageBytes, kStageBytes, &w3_full[slot]);
+          }
+        }
+      } else {
+        ptx::mbar_expect_tx(wconst_full, kStageBytes + kLastStageBytes);
+        ptx::bulk_g2s(s_w1, args.image + kImgW1, kStageBytes, wconst_full);
+        ptx::bulk_g2s(s_w4, args.image + kImgW4, kLastStageBytes, wconst_full);
       }
     }
   } else if (warp == 1) {
-    // ===================================================== MMA issuer: the whole warp runs the (warp-uniform) control
-    // flow and the mbarrier waits; one elected lane issues tcgen05.mma / tcgen05.commit, so every operand is a
-    // uniform register and no per-instruction election loop is generated
-    {
-      const bool leader = ptx::elect_one();
-      const uint32_t id64 = ptx::idesc_bf16(128, 64), id128 = ptx::idesc_bf16(128, 128), id16 = ptx::idesc_bf16(128, 16);
-      constexpr uint32_t hi = ptx::smem_desc_hi(128);
-      const uint32_t ring = ptx::smem_u32(s_ring), xs = ptx::smem_u32(s_x), ws = ptx::smem_u32(s_w);
-      const uint32_t x_lo = ptx::smem_desc_lo(xs, 2048);
-      uint32_t n = 0;            // weight stages consumed
-      uint32_t d_uses[kDBufs] = {0, 0, 0, 0}, slot_uses[kRingSlots] = {0, 0, 0};
-      uint32_t tiles_done = 0;
-      long long t_w = 0, t_d = 0, t_s = 0;      // diagnostics: cycles this warp spent waiting for weights / accumulators / act2 slices
-      auto wait_stage = [&]() -> uint32_t {
-        const int slot = n % kStages;
-        const long long c0 = TC_CLOCK();
-        ptx::mbar_wait(&w_full[slot], (n / kStages) & 1);
-        t_w += TC_CLOCK() - c0;
-        ptx::tc_fence_after();
-        return ws + slot * kStageBytes;
-      };
-      auto release_stage = [&]() {
-        if (leader) ptx::mma_commit(&w_empty[n % kStages]);
-        ++n;
-      };
-      auto acquire_d = [&](int b) {
-        const long long c0 = TC_CLOCK();
-        ptx::mbar_wait(&d_empty[b], (d_uses[b] & 1) ^ 1);
-        t_d += TC_CLOCK() - c0;
-        ptx::tc_fence_after();
-        ++d_uses[b];
-      };
-      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++tiles_done) {
-        const uint32_t tpar = tiles_done & 1;
-        // ---- layer 1: X[128,16] (smem) x W1^T, eight 64-column pieces
-        ptx::mbar_wait(x_ready, tpar);
-        ptx::tc_fence_after();
-        TC_STAMP(tr && tiles_done == 0, 32);
-        {
-          const uint32_t w_lo = ptx::smem_desc_lo(wait_stage(), 8192);
-          TC_STAMP(tr && tiles_done == 0, 33);
+    // ===================================================== MMA issuer A: layers 1 and 2.  The whole warp runs the
+    // (warp-uniform) control flow and the mbarrier waits; one elected lane issues tcgen05.mma / tcgen05.commit.
+    // The tensor pipe's issue queue is shallow (profiles/mma_rate.cu: a wait + fence + commit between groups of 8 MMAs
+    // costs 24 cycles per MMA), so this warp touches barriers only twice per 64-column piece-half (16 MMAs) and a second
+    // issuer (warp B) feeds the pipe with the layer-3 partial products while this one is between groups.
+    const bool leader = ptx::elect_one();
+    const uint32_t id64 = ptx::idesc_bf16(128, 64);
+    constexpr uint32_t hi = ptx::smem_desc_hi(128);
+    const uint32_t xs = ptx::smem_u32(s_x), ws2 = ptx::smem_u32(s_w2);
+    const uint32_t x_lo = ptx::smem_desc_lo(xs, 2048);
+    const uint32_t w1_lo = ptx::smem_desc_lo(ptx::smem_u32(s_w1), 8192);
+    uint32_t n2 = 0;            // W2 half-pieces consumed
+    uint32_t d_uses[kDBufs] = {0, 0, 0, 0};
+    uint32_t tiles_done = 0;
+    long long t_w = 0, t_d = 0;      // diagnostics (OIS_TC_DIAG): cycles spent waiting for weights / accumulators
+    auto acquire_d = [&](int b) {
+      const long long c0 = TC_CLOCK();
+      ptx::mbar_wait(&d_empty[b], (d_uses[b] & 1) ^ 1);
+      t_d += TC_CLOCK() - c0;
+      ptx::tc_fence_after();
+      ++d_uses[b];
+    };
+    ptx::mbar_wait(wconst_full, 0);
+    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++tiles_done) {
+      const uint32_t tpar = tiles_done & 1;
+      // ---- layer 1: X[128,16] (smem) x W1^T, eight 64-column pieces on four accumulator buffers
+      ptx::mbar_wait(x_ready, tpar);
+      ptx::tc_fence_after();
+      TC_STAMP(tr && tiles_done == 0, 32);
 #pragma unroll
-          for (int q = 0; q < 8; ++q) {    // four accumulator buffers: the layer-3 columns are free during layer 1
-            acquire_d(q & 3);
-            if (leader) {
-              ptx::mma_ss(tmem + kColD + (q & 3) * 64, ptx::make_desc(x_lo, hi), ptx::make_desc(w_lo + q * (1024 >> 4), hi), id64, false);
-              ptx::mma_commit(&d_full[q & 3]);
-            }
-            __syncwarp();
-          }
-          release_stage();
+      for (int q = 0; q < 8; ++q) {
+        acquire_d(q & 3);
+        if (leader) {
+          ptx::mma_ss(tmem + kColD + (q & 3) * 64, ptx::make_desc(x_lo, hi), ptx::make_desc(w1_lo + q * (1024 >> 4), hi), id64, false);
+          ptx::mma_commit(&d_full[q & 3]);
         }
-        auto l2_piece = [&](int q) {     // act1 (TMEM) x W2[64q .. 64q+64, :]^T
-          acquire_d(q & 1);
-          const uint32_t d = tmem + kColD + (q & 1) * 64;
-#pragma unroll
-          for (int kb = 0; kb < 4; ++kb) {
-            const uint32_t w_lo = ptx::smem_desc_lo(wait_stage(), 1024);
-            if (leader) {
-#pragma unroll
-              for (int j = 0; j < 8; ++j)
-                ptx::mma_ts(d, tmem + kColAct + (kb * 8 + j) * 8, ptx::make_desc(w_lo + j * (2048 >> 4), hi), id64, (kb | j) != 0);
-            }
-            __syncwarp();
-            release_stage();
-          }
-          if (leader) ptx::mma_commit(&d_full[q & 1]);
-          __syncwarp();
-        };
-        auto l3_partial = [&](int p) {   // act2[:, 64p .. 64p+64] (smem slice) x W3[:, 64p .. 64p+64]^T
-          const int slot = p % kRingSlots;
-          const long long c0 = TC_CLOCK();
-          ptx::mbar_wait(&slot_ready[slot], slot_uses[slot] & 1);
-          t_s += TC_CLOCK() - c0;
-          ++slot_uses[slot];
-          ptx::tc_fence_after();
-          const uint32_t w_lo = ptx::smem_desc_lo(wait_stage(), 2048);
-          const uint32_t a_lo = ptx::smem_desc_lo(ring + slot * 16384, 2048);
-          if (leader) {
-#pragma unroll
-            for (int j = 0; j < 4; ++j)
-              ptx::mma_ss(tmem + kColD3, ptx::make_desc(a_lo + j * (4096 >> 4), hi), ptx::make_desc(w_lo + j * (4096 >> 4), hi), id128,
-                          (p | j) != 0);
-          }
-          __syncwarp();
-          release_stage();
-          if (leader) {
-            ptx::mma_commit(&slot_free[slot]);
-            if (p == 7) ptx::mma_commit(d3_full);
-          }
-          __syncwarp();
-        };
-        // ---- layer 2 (+ layer-3 partial products one piece behind)
-        TC_STAMP(tr && tiles_done == 0, 34);
-        ptx::mbar_wait(act1_ready, tpar);
-        ptx::tc_fence_after();
-        TC_STAMP(tr && tiles_done == 0, 35);
-        l2_piece(0);
-        TC_STAMP(tr && tiles_done == 0, 36);
-        l2_piece(1);
-#pragma unroll
-        for (int q = 2; q < 8; ++q) {
-          l3_partial(q - 2);
-          l2_piece(q);
-        }
-        TC_STAMP(tr && tiles_done == 0, 37);
-        l3_partial(6);
-        l3_partial(7);
-        TC_STAMP(tr && tiles_done == 0, 38);
-        // ---- layer 4: act3 (TMEM) x W4^T (N padded to 16) into accumulator buffer 0
-        ptx::mbar_wait(act3_ready, tpar);
-        ptx::tc_fence_after();
-        {
-          acquire_d(0);
-          const uint32_t w_lo = ptx::smem_desc_lo(wait_stage(), 256);
-          if (leader) {
-#pragma unroll
-            for (int j = 0; j < 8; ++j)
-              ptx::mma_ts(tmem + kColD, tmem + kColAct + j * 8, ptx::make_desc(w_lo + j * (512 >> 4), hi), id16, j != 0);
-          }
-          __syncwarp();
-          release_stage();
-          if (leader) ptx::mma_commit(&d_full[0]);
-          __syncwarp();
-          TC_STAMP(tr && tiles_done == 0, 39);
-          if (tr && tiles_done == 0) { g_tc_trace[40] = t_w; g_tc_trace[41] = t_d; g_tc_trace[42] = t_s; }
-        }
+        __syncwarp();
       }
+      TC_STAMP(tr && tiles_done == 0, 34);
+      // ---- layer 2: act1 (TMEM) x W2[64q .. 64q+64, :]^T, two 32 KB half-pieces (K = 256 each) per piece
+      ptx::mbar_wait(act1_ready, tpar);
+      ptx::tc_fence_after();
+      TC_STAMP(tr && tiles_done == 0, 35);
+#pragma unroll 1
+      for (int q = 0; q < 8; ++q) {
+        acquire_d(q & 1);
+        const uint32_t d = tmem + kColD + (q & 1) * 64;
+#pragma unroll
+        for (int half = 0; half < 2; ++half) {
+          const int slot = n2 % kW2Slots;
+          const long long c0 = TC_CLOCK();
+          ptx::mbar_wait(&w2_full[slot], (n2 / kW2Slots) & 1);
+          t_w += TC_CLOCK() - c0;
+          ptx::tc_fence_after();
+          if (leader) {
+            const uint32_t w_lo = ptx::smem_desc_lo(ws2 + slot * kW2SlotBytes, 1024);
+#pragma unroll
+            for (int j = 0; j < 16; ++j)
+              ptx::mma_ts(d, tmem + kColAct + (half * 16 + j) * 8, ptx::make_desc(w_lo + j * (2048 >> 4), hi), id64, (half | j) != 0);
+            ptx::mma_commit(&w2_empty[slot]);
+            if (half == 1) ptx::mma_commit(&d_full[q & 1]);
+          }
+          __syncwarp();
+          ++n2;
+        }
+        TC_STAMP(tr && tiles_done == 0 && q == 0, 36);
+      }
+      TC_STAMP(tr && tiles_done == 0, 37);
+      ++d_uses[0];   // layer 4 (issuer B) is the 7th use of accumulator buffer 0 in this tile
+      if (tr && tiles_done == 0) { g_tc_trace[40] = t_w; g_tc_trace[41] = t_d; }
+    }
+  } else if (warp == kWarpB) {
+    // ===================================================== MMA issuer B: layer-3 partial products (A = the act2 slice the
+    // epilogue just wrote to shared memory, accumulating over the eight slices) and layer 4 (A = act3 in TMEM)
+    const bool leader = ptx::elect_one();
+    const uint32_t id128 = ptx::idesc_bf16(128, 128), id16 = ptx::idesc_bf16(128, 16);
+    constexpr uint32_t hi = ptx::smem_desc_hi(128);
+    const uint32_t ring = ptx::smem_u32(s_ring), ws3 = ptx::smem_u32(s_w3);
+    const uint32_t w4_lo = ptx::smem_desc_lo(ptx::smem_u32(s_w4), 256);
+    uint32_t n3 = 0, slot_uses[kRingSlots] = {0, 0, 0}, tiles_done = 0;
+    long long t_s = 0;
+    ptx::mbar_wait(wconst_full, 0);
+    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++tiles_done) {
+      const uint32_t tpar = tiles_done & 1;
+#pragma unroll 1
+      for (int p = 0; p < 8; ++p) {
+        const int slot = p % kRingSlots, wslot = n3 % kW3Slots;
+        const long long c0 = TC_CLOCK();
+        ptx::mbar_wait(&slot_ready[slot], slot_uses[slot] & 1);
+        t_s += TC_CLOCK() - c0;
+        ++slot_uses[slot];
+        ptx::mbar_wait(&w3_full[wslot], (n3 / kW3Slots) & 1);
+        ptx::tc_fence_after();
+        if (leader) {
+          const uint32_t w_lo = ptx::smem_desc_lo(ws3 + wslot * kStageBytes, 2048);
+          const uint32_t a_lo = ptx::smem_desc_lo(ring + slot * 16384, 2048);
+#pragma unroll
+          for (int j = 0; j < 4; ++j)
+            ptx::mma_ss(tmem + kColD3, ptx::make_desc(a_lo + j * (4096 >> 4), hi), ptx::make_desc(w_lo + j * (4096 >> 4), hi), id128,
+                        (p | j) != 0);
+          ptx::mma_commit(&w3_empty[wslot]);
+          ptx::mma_commit(&slot_free[slot]);
+          if (p == 7) ptx::mma_commit(d3_full);
+        }
+        __syncwarp();
+        ++n3;
+      }
+      TC_STAMP(tr && tiles_done == 0, 38);
+      // ---- layer 4: act3 (TMEM) x W4^T (N padded to 16) into accumulator buffer 0 (its 7th use in this tile)
+      ptx::mbar_wait(act3_ready, tpar);
+      ptx::mbar_wait(&d_empty[0], ((tiles_done * kBuf0UsesPerTile + (kBuf0UsesPerTile - 1)) & 1) ^ 1);
+      ptx::tc_fence_after();
+      if (leader) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+          ptx::mma_ts(tmem + kColD, tmem + kColAct + j * 8, ptx::make_desc(w4_lo + j * (512 >> 4), hi), id16, j != 0);
+        ptx::mma_commit(&d_full[0]);
+      }
+      __syncwarp();
+      TC_STAMP(tr && tiles_done == 0, 39);
+      if (tr && tiles_done == 0) g_tc_trace[42] = t_s;
     }
   } else {
     // ===================================================== epilogue warps: two groups of four (one per TMEM lane quadrant)
@@ -434,6 +454,12 @@ tc_actor_kernel(const __grid_constant__ TcActArgs args) {
       const int64_t grow = (int64_t)tile * kTileM + row;
       const int next_tile = tile + gridDim.x;
       // ---- layer 1: this group's pieces (64 columns each) -> act1 (TMEM, bf16 pairs)
+      if (g == 1 && tiles_done > 0) {
+        // act1 overwrites the columns the previous tile's act3 lives in, which layer 4 (issuer B) reads.  Group 0 has
+        // waited for that layer 4 itself (it owns the output); group 1 checks the same phase of d_full[0] here.
+        ptx::mbar_wait(&d_full[0], ((tiles_done - 1) * kBuf0UsesPerTile + (kBuf0UsesPerTile - 1)) & 1);
+        ptx::tc_fence_after();
+      }
       for (int q = g; q < 8; q += 2) {
         const int b = q & 3;
         wait_d(b);

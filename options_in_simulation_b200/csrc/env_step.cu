@@ -231,6 +231,12 @@ __global__ void __launch_bounds__(kEnvThreads, kEnvMinBlocks)
 env_step_kernel(const __grid_constant__ OisEnvParams p, const __grid_constant__ OisEnvState st,
                 const __grid_constant__ OisEnvIO io, const int64_t n) {
   __shared__ float s_stats[OIS_EP_STATS_LEN];
+  // Programmatic dependent launch: this grid may have started while its stream predecessor (normally the actor kernel)
+  // was still running.  The predecessor may be another env step (tests, dynamics-only loops), so nothing is read
+  // before the wait; what overlaps is the launch itself.  The next kernel (the next actor step) is let go at once: it
+  // reads nothing of ours before its own wait.
+  pdl_wait();
+  pdl_trigger();
   if (kStats) {
     if (threadIdx.x < OIS_EP_STATS_LEN) s_stats[threadIdx.x] = 0.f;
     __syncthreads();
@@ -248,7 +254,7 @@ env_step_kernel(const __grid_constant__ OisEnvParams p, const __grid_constant__ 
   __shared__ __align__(16) StageB s_b;
   const int tid = threadIdx.x;
   const int64_t stride = (int64_t)gridDim.x * blockDim.x;
-  auto issue_a = [&](int buf, int64_t j) {
+  auto issue_a_state = [&](int buf, int64_t j) {
     if (j < n) {
       StageA& a = s_a[buf];
       cp_async16(&a.pv[tid], st.pose_vx + 4 * j);
@@ -256,11 +262,20 @@ env_step_kernel(const __grid_constant__ OisEnvParams p, const __grid_constant__ 
       cp_async16(&a.wv[tid], st.wheel_speed + 4 * j);
       cp_async16(&a.cmd[tid], st.commands + 4 * j);
       cp_async8(&a.sim[tid], st.sim_steps + j);
+    }
+  };
+  auto issue_a_actions = [&](int buf, int64_t j) {
+    if (j < n) {
+      StageA& a = s_a[buf];
       if (p.act_dim == 4) cp_async16(&a.act[tid], io.actions + 4 * j);
       else if (p.act_dim == 2) cp_async8(&a.act[tid], io.actions + 2 * j);
       else cp_async4(&a.act[tid], io.actions + j);
     }
     cp_async_commit();
+  };
+  auto issue_a = [&](int buf, int64_t j) {
+    issue_a_state(buf, j);
+    issue_a_actions(buf, j);
   };
   auto issue_b = [&](int64_t j) {
     if (j < n) {
@@ -620,11 +635,12 @@ extern "C" int ois_env_step(const OisEnvParams* params, const OisEnvState* state
     carveout_set = true;
   }
   const bool stats = io->ep_stats != nullptr, ev = params->eval_sums != 0;
-  if (stats && ev) env_step_kernel<true, true><<<grid, kEnvThreads, 0, s>>>(*params, *state, *io, n_envs);
-  else if (stats) env_step_kernel<true, false><<<grid, kEnvThreads, 0, s>>>(*params, *state, *io, n_envs);
-  else if (ev) env_step_kernel<false, true><<<grid, kEnvThreads, 0, s>>>(*params, *state, *io, n_envs);
-  else env_step_kernel<false, false><<<grid, kEnvThreads, 0, s>>>(*params, *state, *io, n_envs);
-  OIS_CHECK_LAUNCH();
+  cudaError_t le;
+  if (stats && ev) le = launch_pdl(env_step_kernel<true, true>, grid, kEnvThreads, 0, s, *params, *state, *io, n_envs);
+  else if (stats) le = launch_pdl(env_step_kernel<true, false>, grid, kEnvThreads, 0, s, *params, *state, *io, n_envs);
+  else if (ev) le = launch_pdl(env_step_kernel<false, true>, grid, kEnvThreads, 0, s, *params, *state, *io, n_envs);
+  else le = launch_pdl(env_step_kernel<false, false>, grid, kEnvThreads, 0, s, *params, *state, *io, n_envs);
+  OIS_CHECK_CUDA(le);
   return OIS_OK;
 }
 

@@ -250,6 +250,8 @@ tc_actor_kernel(const __grid_constant__ TcActArgs args) {
     // ===================================================== producers (one thread each; a thread sustains only one bulk copy
     // per ~520 cycles whatever its size — profiles/mma_rate.cu): 0 and 1 alternate on the 32 KB half-pieces of W2,
     // 2 streams the 16 KB K-slices of W3, 3 loads W1 and W4 once (they stay resident)
+    // (programmatic dependent launch: the weight image, like the parameters, was written at least two kernels ago —
+    // the repack kernel never triggers early — so the producers start streaming before the predecessor has finished)
     if (lane == 0) {
       const int p = warp == 0 ? 0 : warp - (1 + kEpiWarps);
       if (p < 2) {
@@ -443,6 +445,11 @@ tc_actor_kernel(const __grid_constant__ TcActArgs args) {
       ptx::fence_async_smem();
       warp_arrive(x_ready);
     };
+    // Programmatic dependent launch: everything above (barriers, TMEM, biases, the weight stream) overlapped the tail of
+    // the previous kernel; the observations are the first thing that kernel (the env step) produced.  One thread per
+    // CTA lets the NEXT kernel start, after its own wait (ois_common.cuh states the rule).
+    pdl_wait();
+    if (warp == 2 && lane == 0) pdl_trigger();
     float xr[8];
     if ((int)blockIdx.x < num_tiles) {
       load_x(blockIdx.x, xr);
@@ -654,8 +661,7 @@ int tc_actor_forward(OisAgent* a, const float* actor_params, const OisScaler* sc
   args.io = *io;
   const int tiles = (int)((rows + kTileM - 1) / kTileM);
   const int grid = tiles < st->sms ? tiles : st->sms;
-  tc_actor_kernel<<<grid, kThreads, kSmemBytes, s>>>(args);
-  OIS_CHECK_LAUNCH();
+  OIS_CHECK_CUDA(launch_pdl(tc_actor_kernel, grid, kThreads, kSmemBytes, s, args));
   return OIS_OK;
 }
 

@@ -82,6 +82,31 @@ __device__ inline float2 normal2(uint32_t a, uint32_t b) {
   return make_float2(r * c, r * s);
 }
 
+// ---------------------------------------------------------------------------------------------
+// Programmatic dependent launch (sm_90+): a kernel launched with launch_pdl() may start while the previous kernel in
+// the stream is still running; it must execute pdl_wait() before touching anything an earlier kernel wrote, and the
+// earlier kernel lets it go with pdl_trigger().  Rule used throughout: every thread does pdl_wait() and only then
+// pdl_trigger(), so whatever a kernel reads before ITS wait was written no later than by its grand-parent, which had
+// completed before the parent triggered.  A kernel that never triggers behaves as a normal stream predecessor.
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream, Args... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
+
 // streaming 16-byte accesses: every state field is touched once per step
 __device__ inline float4 ld_stream4(const float* p) { return __ldcs(reinterpret_cast<const float4*>(p)); }
 __device__ inline void st_stream4(float* p, const float4& v) { __stcs(reinterpret_cast<float4*>(p), v); }

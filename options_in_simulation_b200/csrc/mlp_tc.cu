@@ -27,27 +27,28 @@ namespace ois {
 
 namespace tc {
 constexpr int kTileM = 128;
-// warp 0 and warps 10-12: bulk-copy producers; warp 1: MMA issuer A (layers 1, 2); warps 2-9: epilogue;
-// warp 13: MMA issuer B (layers 3, 4)
-constexpr int kThreads = 448;
+// warp 0 and warps 10-12: bulk-copy producers; warp 1: MMA issuer A1 (layer 1, even pieces of layer 2); warps 2-9:
+// epilogue; warp 13: MMA issuer B (layers 3, 4); warp 14: MMA issuer A2 (odd pieces of layer 2)
+constexpr int kThreads = 480;
 constexpr int kEpiWarps = 8;
 constexpr int kWarpB = 2 + kEpiWarps + 3;  // 13
+constexpr int kWarpA2 = kWarpB + 1;        // 14
 constexpr int kH0 = 512, kH1 = 512, kH2 = 128, kInPad = 16, kOutPad = 16;
 constexpr int kStageBytes = 16384;         // unit of the weight image
 constexpr int kW2SlotBytes = 32768;        // layer-2 ring slot: half a 64-column piece (k-blocks 0-1 or 2-3)
-constexpr int kW2Slots = 3;
+constexpr int kW2Slots = 4;                // slots 0, 1 serve the even pieces (issuer A1), 2, 3 the odd ones (A2)
 constexpr int kW3Slots = 2;                // layer-3 ring slot: one 64-wide K slice of W3, 16 KB
-constexpr int kRingSlots = 3;              // act2 slices: [8 kc][128 rows][8] bf16 = 16 KB each
+constexpr int kRingSlots = 2;              // act2 slices, one per epilogue group: [8 kc][128 rows][8] bf16 = 16 KB each
 constexpr int kStreamStages = 42;          // 1 (W1) + 32 (W2) + 8 (W3) + 1 (W4)
 constexpr int kLastStageBytes = kOutPad * kH2 * 2;                       // 4096
 constexpr size_t kImageBytes = (size_t)(kStreamStages - 1) * kStageBytes + kLastStageBytes;
 constexpr size_t kImgW1 = 0, kImgW2 = kStageBytes, kImgW3 = 33 * (size_t)kStageBytes, kImgW4 = 41 * (size_t)kStageBytes;
 // shared memory map (bytes)
-constexpr int kOffW2 = 0;                                      // 3 x 32 KB layer-2 weight ring
+constexpr int kOffW2 = 0;                                      // 4 x 32 KB layer-2 weight ring
 constexpr int kOffW3 = kOffW2 + kW2Slots * kW2SlotBytes;       // 2 x 16 KB layer-3 weight ring
 constexpr int kOffW1 = kOffW3 + kW3Slots * kStageBytes;        // 16 KB, resident for the whole launch
 constexpr int kOffW4 = kOffW1 + kStageBytes;                   // 4 KB, resident
-constexpr int kOffRing = kOffW4 + kLastStageBytes;             // 3 x 16 KB act2 slices
+constexpr int kOffRing = kOffW4 + kLastStageBytes;             // 2 x 16 KB act2 slices
 constexpr int kOffX = kOffRing + kRingSlots * 16384;           // [2 kc][128][8] = 4 KB
 constexpr int kOffBias = kOffX + kTileM * kInPad * 2;          // b1 512, b2 512, b3 128, b4 16 fp32
 constexpr int kOffScale = kOffBias + (kH0 + kH1 + kH2 + kOutPad) * 4;   // scaler: mean[16], sqrt(var)+eps[16] fp32
@@ -59,6 +60,8 @@ constexpr int kColD = 256;      // 64-column fp32 accumulator buffers: 0, 1 (lay
 constexpr int kColD3 = 384;     // ... 2, 3 during layer 1 only; then the 128 columns of layer 3
 constexpr int kDBufs = 4;
 constexpr int kBuf0UsesPerTile = 7;   // layer 1 pieces 0, 4; layer 2 pieces 0, 2, 4, 6; layer 4
+constexpr int kBuf1UsesPerTile = 6;   // layer 1 pieces 1, 5; layer 2 pieces 1, 3, 5, 7
+constexpr int kBuf23UsesPerTile = 2;  // layer 1 pieces 2, 6 / 3, 7
 constexpr int kTmemCols = 512;
 
 // image order (16 KB stages): W1 | W2 piece 0 (4 k-blocks of 128) | ... | W2 piece 7 | W3 slice 0 .. 7 | W4 (4 KB)
@@ -187,8 +190,8 @@ tc_actor_kernel(const __grid_constant__ TcActArgs args) {
   float* s_bias = reinterpret_cast<float*>(smem + kOffBias);
   float* s_scale = reinterpret_cast<float*>(smem + kOffScale);
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + kOffBar);
-  uint64_t* w2_full = bars;                   // [3]
-  uint64_t* w2_empty = w2_full + kW2Slots;    // [3]
+  uint64_t* w2_full = bars;                   // [4]
+  uint64_t* w2_empty = w2_full + kW2Slots;    // [4]
   uint64_t* w3_full = w2_empty + kW2Slots;    // [2]
   uint64_t* w3_empty = w3_full + kW3Slots;    // [2]
   uint64_t* wconst_full = w3_empty + kW3Slots;
@@ -196,11 +199,12 @@ tc_actor_kernel(const __grid_constant__ TcActArgs args) {
   uint64_t* d_full = x_ready + 1;             // [4]
   uint64_t* d_empty = d_full + kDBufs;        // [4]
   uint64_t* act1_ready = d_empty + kDBufs;
-  uint64_t* slot_ready = act1_ready + 1;      // [3]
-  uint64_t* slot_free = slot_ready + kRingSlots;   // [3]
+  uint64_t* slot_ready = act1_ready + 1;      // [2]
+  uint64_t* slot_free = slot_ready + kRingSlots;   // [2]
   uint64_t* d3_full = slot_free + kRingSlots;
   uint64_t* act3_ready = d3_full + 1;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(act3_ready + 1);
+  uint64_t* stagger = act3_ready + 1;         // issuer A1 is half a piece into layer 2: issuer A2 may start
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(stagger + 1);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int num_tiles = (int)((args.rows + kTileM - 1) / kTileM);
@@ -218,6 +222,7 @@ tc_actor_kernel(const __grid_constant__ TcActArgs args) {
     for (int i = 0; i < kRingSlots; ++i) { ptx::mbar_init(&slot_ready[i], kEpiWarps / 2); ptx::mbar_init(&slot_free[i], 1); }
     ptx::mbar_init(d3_full, 1);
     ptx::mbar_init(act3_ready, kEpiWarps);
+    ptx::mbar_init(stagger, 1);
     ptx::fence_barrier_init();
   }
   if (warp == 1) ptx::tmem_alloc<kTmemCols>(tmem_slot);
@@ -281,77 +286,95 @@ tc_actor_kernel(const __grid_constant__ TcActArgs args) {
         ptx::bulk_g2s(s_w4, args.image + kImgW4, kLastStageBytes, wconst_full);
       }
     }
-  } else if (warp == 1) {
-    // ===================================================== MMA issuer A: layers 1 and 2.  The whole warp runs the
-    // (warp-uniform) control flow and the mbarrier waits; one elected lane issues tcgen05.mma / tcgen05.commit.
-    // The tensor pipe's issue queue is shallow (profiles/mma_rate.cu: a wait + fence + commit between groups of 8 MMAs
-    // costs 24 cycles per MMA), so this warp touches barriers only twice per 64-column piece-half (16 MMAs) and a second
-    // issuer (warp B) feeds the pipe with the layer-3 partial products while this one is between groups.
+  } else if (warp == 1 || warp == kWarpA2) {
+    // ===================================================== MMA issuers A1 (warp 1: layer 1, even pieces of layer 2) and
+    // A2 (odd pieces of layer 2).  A whole warp runs the (warp-uniform) control flow and the mbarrier waits; one elected
+    // lane issues tcgen05.mma / tcgen05.commit.  The tensor pipe's issue queue is shallow (profiles/mma_rate.cu: a wait +
+    // fence + commit between groups of 16 MMAs costs ~13 cycles per 32-cycle MMA), so two issuers work on two pieces —
+    // two accumulator buffers — at once, A2 half a piece behind A1: whenever one of them is between groups or waiting for
+    // its accumulator to be drained, the other one's MMAs keep the pipe busy.
+    const bool a1 = warp == 1;
+    const int odd = a1 ? 0 : 1;
     const bool leader = ptx::elect_one();
     const uint32_t id64 = ptx::idesc_bf16(128, 64);
     constexpr uint32_t hi = ptx::smem_desc_hi(128);
     const uint32_t xs = ptx::smem_u32(s_x), ws2 = ptx::smem_u32(s_w2);
     const uint32_t x_lo = ptx::smem_desc_lo(xs, 2048);
     const uint32_t w1_lo = ptx::smem_desc_lo(ptx::smem_u32(s_w1), 8192);
-    uint32_t n2 = 0;            // W2 half-pieces consumed
-    uint32_t d_uses[kDBufs] = {0, 0, 0, 0};
     uint32_t tiles_done = 0;
-    long long t_w = 0, t_d = 0;      // diagnostics (OIS_TC_DIAG): cycles spent waiting for weights / accumulators
-    auto acquire_d = [&](int b) {
+    long long t_w = 0, t_d = 0, t_i = 0, t_c = 0, t_l2 = 0;   // diagnostics (OIS_TC_DIAG): cycles waiting for weights /
+                                                              // accumulators, issuing MMAs, committing, whole layer 2
+    // accumulator buffer b, its use number `idx` within the tile (kBuf*UsesPerTile uses per tile, in a fixed order)
+    auto acquire_d = [&](int b, int idx) {
+      const uint32_t per_tile = b == 0 ? kBuf0UsesPerTile : b == 1 ? kBuf1UsesPerTile : kBuf23UsesPerTile;
       const long long c0 = TC_CLOCK();
-      ptx::mbar_wait(&d_empty[b], (d_uses[b] & 1) ^ 1);
+      ptx::mbar_wait(&d_empty[b], ((tiles_done * per_tile + (uint32_t)idx) & 1) ^ 1);
       t_d += TC_CLOCK() - c0;
       ptx::tc_fence_after();
-      ++d_uses[b];
     };
-    ptx::mbar_wait(wconst_full, 0);
+    if (a1) ptx::mbar_wait(wconst_full, 0);
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++tiles_done) {
       const uint32_t tpar = tiles_done & 1;
-      // ---- layer 1: X[128,16] (smem) x W1^T, eight 64-column pieces on four accumulator buffers
-      ptx::mbar_wait(x_ready, tpar);
-      ptx::tc_fence_after();
-      TC_STAMP(tr && tiles_done == 0, 32);
+      if (a1) {
+        // ---- layer 1: X[128,16] (smem) x W1^T, eight 64-column pieces on four accumulator buffers
+        ptx::mbar_wait(x_ready, tpar);
+        ptx::tc_fence_after();
+        TC_STAMP(tr && tiles_done == 0, 32);
 #pragma unroll
-      for (int q = 0; q < 8; ++q) {
-        acquire_d(q & 3);
-        if (leader) {
-          ptx::mma_ss(tmem + kColD + (q & 3) * 64, ptx::make_desc(x_lo, hi), ptx::make_desc(w1_lo + q * (1024 >> 4), hi), id64, false);
-          ptx::mma_commit(&d_full[q & 3]);
+        for (int q = 0; q < 8; ++q) {
+          acquire_d(q & 3, q >> 2);
+          if (leader) {
+            ptx::mma_ss(tmem + kColD + (q & 3) * 64, ptx::make_desc(x_lo, hi), ptx::make_desc(w1_lo + q * (1024 >> 4), hi), id64, false);
+            ptx::mma_commit(&d_full[q & 3]);
+          }
+          __syncwarp();
         }
-        __syncwarp();
+        TC_STAMP(tr && tiles_done == 0, 34);
       }
-      TC_STAMP(tr && tiles_done == 0, 34);
       // ---- layer 2: act1 (TMEM) x W2[64q .. 64q+64, :]^T, two 32 KB half-pieces (K = 256 each) per piece
       ptx::mbar_wait(act1_ready, tpar);
+      if (!a1) ptx::mbar_wait(stagger, tpar);
       ptx::tc_fence_after();
-      TC_STAMP(tr && tiles_done == 0, 35);
+      TC_STAMP(tr && a1 && tiles_done == 0, 35);
+      const long long l2_0 = TC_CLOCK();
 #pragma unroll 1
-      for (int q = 0; q < 8; ++q) {
-        acquire_d(q & 1);
-        const uint32_t d = tmem + kColD + (q & 1) * 64;
+      for (int q = odd; q < 8; q += 2) {
+        acquire_d(odd, 2 + (q >> 1));
+        const uint32_t d = tmem + kColD + odd * 64;
 #pragma unroll
         for (int half = 0; half < 2; ++half) {
+          const uint32_t n2 = tiles_done * 16u + (uint32_t)(q * 2 + half);   // half-piece number in stream order
           const int slot = n2 % kW2Slots;
           const long long c0 = TC_CLOCK();
           ptx::mbar_wait(&w2_full[slot], (n2 / kW2Slots) & 1);
           t_w += TC_CLOCK() - c0;
           ptx::tc_fence_after();
+          const long long c1 = TC_CLOCK();
           if (leader) {
             const uint32_t w_lo = ptx::smem_desc_lo(ws2 + slot * kW2SlotBytes, 1024);
 #pragma unroll
             for (int j = 0; j < 16; ++j)
               ptx::mma_ts(d, tmem + kColAct + (half * 16 + j) * 8, ptx::make_desc(w_lo + j * (2048 >> 4), hi), id64, (half | j) != 0);
-            ptx::mma_commit(&w2_empty[slot]);
-            if (half == 1) ptx::mma_commit(&d_full[q & 1]);
           }
           __syncwarp();
-          ++n2;
+          const long long c2 = TC_CLOCK();
+          if (leader) {
+            ptx::mma_commit(&w2_empty[slot]);
+            if (a1 && q == 0 && half == 0) ptx::mma_commit(stagger);
+            if (half == 1) ptx::mma_commit(&d_full[odd]);
+          }
+          __syncwarp();
+          t_i += c2 - c1;
+          t_c += TC_CLOCK() - c2;
         }
-        TC_STAMP(tr && tiles_done == 0 && q == 0, 36);
+        TC_STAMP(tr && a1 && tiles_done == 0 && q == 0, 36);
       }
-      TC_STAMP(tr && tiles_done == 0, 37);
-      ++d_uses[0];   // layer 4 (issuer B) is the 7th use of accumulator buffer 0 in this tile
-      if (tr && tiles_done == 0) { g_tc_trace[40] = t_w; g_tc_trace[41] = t_d; }
+      TC_STAMP(tr && a1 && tiles_done == 0, 37);
+      t_l2 = TC_CLOCK() - l2_0;
+      if (tr && tiles_done == 0) {
+        const int o = a1 ? 40 : 50;
+        g_tc_trace[o] = t_w; g_tc_trace[o + 1] = t_d; g_tc_trace[o + 3] = t_i; g_tc_trace[o + 4] = t_c; g_tc_trace[o + 5] = t_l2;
+      }
     }
   } else if (warp == kWarpB) {
     // ===================================================== MMA issuer B: layer-3 partial products (A = the act2 slice the
@@ -361,14 +384,14 @@ tc_actor_kernel(const __grid_constant__ TcActArgs args) {
     constexpr uint32_t hi = ptx::smem_desc_hi(128);
     const uint32_t ring = ptx::smem_u32(s_ring), ws3 = ptx::smem_u32(s_w3);
     const uint32_t w4_lo = ptx::smem_desc_lo(ptx::smem_u32(s_w4), 256);
-    uint32_t n3 = 0, slot_uses[kRingSlots] = {0, 0, 0}, tiles_done = 0;
+    uint32_t n3 = 0, slot_uses[kRingSlots] = {0, 0}, tiles_done = 0;
     long long t_s = 0;
     ptx::mbar_wait(wconst_full, 0);
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++tiles_done) {
       const uint32_t tpar = tiles_done & 1;
 #pragma unroll 1
       for (int p = 0; p < 8; ++p) {
-        const int slot = p % kRingSlots, wslot = n3 % kW3Slots;
+        const int slot = p & 1, wslot = n3 % kW3Slots;
         const long long c0 = TC_CLOCK();
         ptx::mbar_wait(&slot_ready[slot], slot_uses[slot] & 1);
         t_s += TC_CLOCK() - c0;
@@ -491,7 +514,7 @@ tc_actor_kernel(const __grid_constant__ TcActArgs args) {
       if (next_tile < num_tiles) load_x(next_tile, xr);
       // ---- layer 2: this group's pieces -> one 64-column slice of act2 each, in the shared-memory ring
       for (int q = g; q < 8; q += 2) {
-        const int slot = q % kRingSlots;
+        const int slot = g;              // each group owns one act2 slice buffer
         const long long c0 = TC_CLOCK();
         wait_d(g);
         e_d += TC_CLOCK() - c0;
@@ -504,8 +527,8 @@ tc_actor_kernel(const __grid_constant__ TcActArgs args) {
         uint32_t w0[16], w1[16];
         epi_act(v0, s_bias + kH0 + q * 64, w0);
         epi_act(v1, s_bias + kH0 + q * 64 + 32, w1);
-        // slot `slot` is used by the pieces q = slot, slot + 3, (slot + 6): use number = tiles * uses-per-tile + q / 3
-        const uint32_t use = tiles_done * (slot == 2 ? 2u : 3u) + (uint32_t)(q / kRingSlots);
+        // this group's slot is used four times per tile (pieces g, g + 2, g + 4, g + 6)
+        const uint32_t use = tiles_done * 4u + (uint32_t)(q >> 1);
         const long long c1 = TC_CLOCK();
         ptx::mbar_wait(&slot_free[slot], (use & 1) ^ 1);                    // previous user of the slot consumed
         e_s += TC_CLOCK() - c1;
@@ -522,7 +545,7 @@ tc_actor_kernel(const __grid_constant__ TcActArgs args) {
       // every layer-1 MMA of this tile has completed (a layer-2 accumulator was seen full): the X buffer is free, so the
       // next tile's layer 1 can start the moment the MMA warp gets there
       if (next_tile < num_tiles) write_x(xr);
-      if (tr && tiles_done == 0 && (warp == 2 || warp == 6)) { g_tc_trace[43 + 2 * g] = e_d; g_tc_trace[44 + 2 * g] = e_s; }
+      if (tr && tiles_done == 0 && (warp == 2 || warp == 6)) { g_tc_trace[46 + 2 * g] = e_d; g_tc_trace[47 + 2 * g] = e_s; }
       // ---- exploration noise of this row, prepared while the last layer-2 / layer-3 MMAs run (group 0 owns the output)
       float nz[4] = {0.f, 0.f, 0.f, 0.f};
       bool applied = false;

@@ -59,7 +59,7 @@ __global__ void __launch_bounds__(128, 1) rate_kernel(int reps, long long* out) 
 
 // Interference test: warp 1 issues N=64 A-from-TMEM MMAs (the layer-2 shape) while, optionally, four threads stream
 // 16 KB bulk copies into shared memory and / or eight warps tcgen05.ld 64 columns in a loop (the epilogue pattern).
-__global__ void __launch_bounds__(448, 1) mix_kernel(const uint8_t* img, int reps, int with_bulk, int with_ldtm, long long* out) {
+__global__ void __launch_bounds__(448, 1) mix_kernel(const uint8_t* img, int reps, int with_bulk, int with_ldtm, int bstride, long long* out) {
   extern __shared__ __align__(1024) uint8_t smem[];
   __shared__ uint64_t bar, full[4][4];
   __shared__ uint32_t slot;
@@ -82,13 +82,13 @@ __global__ void __launch_bounds__(448, 1) mix_kernel(const uint8_t* img, int rep
     const bool leader = ptx::elect_one();
     const uint32_t idesc = ptx::idesc_bf16(128, 64);
     constexpr uint32_t hi = ptx::smem_desc_hi(128);
-    const uint32_t b_lo = ptx::smem_desc_lo(ptx::smem_u32(smem) + 8192, 1024);
+    const uint32_t b_lo = ptx::smem_desc_lo(ptx::smem_u32(smem), 1024);
     const long long t0 = clock64();
     for (int it = 0; it < reps / 16; ++it) {
       if (leader) {
 #pragma unroll
         for (int j = 0; j < 16; ++j)
-          ptx::mma_ts(tmem + 256 + (j & 1) * 64, tmem + (j & 7) * 8, ptx::make_desc(b_lo + (j & 3) * 16, hi), idesc, true);
+          ptx::mma_ts(tmem + 256 + (j & 1) * 64, tmem + (j & 7) * 8 + (j >> 3) * 64, ptx::make_desc(b_lo + j * bstride, hi), idesc, true);
       }
       __syncwarp();
     }
@@ -252,13 +252,15 @@ int main() {
     cudaMalloc(&img, 655360);
     cudaMemset(img, 1, 655360);
     cudaFuncSetAttribute(mix_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 32768 + 131072);
-    for (int bulk = 0; bulk < 2; ++bulk)
-      for (int ldtm = 0; ldtm < 2; ++ldtm) {
-        mix_kernel<<<148, 448, 32768 + 131072>>>(img, 4096, bulk, ldtm, d);
-        long long c = 0;
-        if (cudaMemcpy(&c, d, 8, cudaMemcpyDeviceToHost) != cudaSuccess) { printf("mix error\n"); return 1; }
-        printf("mix  N=64 A-from-TMEM MMAs with bulk copies %d, tcgen05.ld loops %d: %6.1f cycles / MMA\n", bulk, ldtm, (double)c / 4096);
-      }
+    for (int bstride : {1, 128})
+      for (int bulk = 0; bulk < 2; ++bulk)
+        for (int ldtm = 0; ldtm < 2; ++ldtm) {
+          mix_kernel<<<148, 448, 32768 + 131072>>>(img, 4096, bulk, ldtm, bstride, d);
+          long long c = 0;
+          if (cudaMemcpy(&c, d, 8, cudaMemcpyDeviceToHost) != cudaSuccess) { printf("mix error\n"); return 1; }
+          printf("mix  N=64 A-from-TMEM MMAs, B tiles %4d B apart, bulk copies %d, tcgen05.ld loops %d: %6.1f cycles / MMA\n", bstride * 16, bulk,
+                 ldtm, (double)c / 4096);
+        }
   }
   {
     long long* d;

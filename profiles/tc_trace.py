@@ -43,5 +43,9 @@ for mode in ("warm", "cold"):
     print(f"--- {mode} L2, n={n}")
     for k in sorted(names, key=lambda k: buf[k]):
         print(f"{(buf[k] - t0) / 1e3:8.2f} us  {names[k]}")
-    print(f"MMA warp wait cycles in tile 0: weights {buf[40]}  accumulators {buf[41]}  act2 slices {buf[42]}")
-    print(f"epilogue layer-2 wait cycles: group 0 d_full {buf[43]} slot_free {buf[44]}; group 1 d_full {buf[45]} slot_free {buf[46]}")
+    if buf[37] > buf[35] and buf[45]:
+        print(f"SM clock during this launch ~ {buf[45] / (buf[37] - buf[35]):.2f} GHz (cycles of issuer A1's layer 2 / its wall time)")
+    print(f"issuer A1 cycles in tile 0 (OIS_TC_DIAG): layer 2 total {buf[45]}: wait weights {buf[40]} accumulators {buf[41]} (incl. layer 1) "
+          f"MMA issue {buf[43]} commits {buf[44]}")
+    print(f"issuer A2: layer 2 total {buf[55]}: wait weights {buf[50]} accumulators {buf[51]} MMA issue {buf[53]} commits {buf[54]}")
+    print(f"issuer B: wait act2 slices {buf[42]}; epilogue layer-2 waits: group 0 d_full {buf[46]} slot_free {buf[47]}; group 1 d_full {buf[48]} slot_free {buf[49]}")

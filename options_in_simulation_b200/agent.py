@@ -12,7 +12,7 @@ plus the model / preprocessor / noise classes the train scripts build it from
 Parameters, Adam moments and gradients are flat fp32 buffers in HBM (``nn.Sequential`` order); every
 arithmetic step is a kernel of ``libois_b200.so`` (csrc/agent.cu, csrc/mlp_fp32.cu, csrc/mlp_tc.cu).
 ``mixed_precision: False`` (the reference's setting, ddpg.py:163) selects the exact fp32 path;
-``mixed_precision: True`` selects bf16 tcgen05 tensor-core inference (fp32 accumulate, fp32 master weights) —
+``mixed_precision: True`` selects bf16 tcgen05 tensor-core inference AND update (fp32 accumulate, fp32 master weights) —
 the counterpart of the reference's autocast hooks (ddpg.py:165-170,233).
 """
 from __future__ import annotations
@@ -623,7 +623,7 @@ class DDPG:
                 self.policy.reduce_parameters(self._grad_actor)
             L.check(lib.ois_ddpg_update_phase(self._handle, self._scaler_ref(), C.byref(io), 2, scale, stream))
             self._updates += 1
-            self.kernel_launches += UPDATE_LAUNCHES + (0 if self._state_preprocessor is not None else 0)
+            self.kernel_launches += UPDATE_LAUNCHES_BF16 if self._mixed_precision else UPDATE_LAUNCHES
             every = self.cfg["track_stats_interval"] or (1 if self.write_interval > 0 else 0)
             if every and self._updates % every == 0:   # ddpg.py:452-461
                 st = self._stats.tolist()
@@ -681,3 +681,7 @@ class DDPG:
 # critic bwd (4 wgrad + 4 colsum + 3 dgrad) | adam + 4 fwd + 2 copy + 4 fwd + loss + critic dgrad 4 + out-grad +
 # actor bwd 11 | adam + 2 polyak
 UPDATE_LAUNCHES = (2 + 4 + 2 + 4 + 1 + 2 + 4 + 1 + 11) + (1 + 4 + 2 + 4 + 1 + 4 + 1 + 11) + 3
+# on the bf16 tcgen05 path (csrc/update_tc.cu): 2 scaler + 2 weight images (targets) + 2 pack + 4 grouped fwd (target
+# actor || critic) + pack + 4 fwd + td + loss + pack + critic bwd (3 dgrad + grouped wgrad + bias) | adam + pack +
+# image + 4 fwd + pack + image + 4 fwd + loss + pack + critic dgrad (3 + 1) + pack + actor bwd 5 | adam + 2 polyak
+UPDATE_LAUNCHES_BF16 = (2 + 2 + 2 + 4 + 1 + 4 + 1 + 1 + 1 + 5) + (1 + 1 + 1 + 4 + 1 + 1 + 4 + 1 + 1 + 4 + 1 + 5) + 3

@@ -6,6 +6,7 @@
 #include "agent.cuh"
 #include "mlp_fp32.cuh"
 #include "explore.cuh"
+#include "update_tc.cuh"
 
 namespace ois {
 
@@ -350,7 +351,10 @@ extern "C" int ois_agent_create(OisAgent** out, const OisMlpShape* actor, const 
   a->xn = at(o_xn);
   if (precision == OIS_PRECISION_FP32) { a->h0 = at(o_h0); a->h1 = at(o_h1); a->h2 = at(o_h2); }
   if (precision == OIS_PRECISION_BF16) {
-    if (int e = tc_agent_init(a, (cudaStream_t)stream)) {
+    int e = tc_agent_init(a, (cudaStream_t)stream);
+    if (!e) e = tcu_init(a);
+    if (e) {
+      tc_agent_free(a);
       cudaFree(a->ws);
       delete a;
       return e;
@@ -363,6 +367,7 @@ extern "C" int ois_agent_create(OisAgent** out, const OisMlpShape* actor, const 
 extern "C" int ois_agent_destroy(OisAgent* a) {
   if (!a) return OIS_OK;
   tc_agent_free(a);
+  tcu_free(a);
   if (a->ws) cudaFree(a->ws);
   delete a;
   return OIS_OK;
@@ -370,7 +375,7 @@ extern "C" int ois_agent_destroy(OisAgent* a) {
 
 extern "C" int ois_agent_invalidate(OisAgent* a) {
   OIS_CHECK_ARG(a, "null agent");
-  if (a->precision == OIS_PRECISION_BF16) tc_invalidate_weights(a);
+  if (a->precision == OIS_PRECISION_BF16) { tc_invalidate_weights(a); tcu_invalidate(a, -1); }
   return OIS_OK;
 }
 
@@ -436,6 +441,9 @@ extern "C" int ois_ddpg_update_phase(OisAgent* a, const OisScaler* scaler, const
   cudaStream_t s = (cudaStream_t)stream;
   const int B = a->batch, D = a->actor.in_dim, A = a->actor.out_dim, CI = a->critic.in_dim;
   const MlpOffsets oa = mlp_offsets(a->actor), oc = mlp_offsets(a->critic);
+  // OIS_PRECISION_BF16: every contraction below runs as a tcgen05 grouped GEMM (update_tc.cu); the element-wise pieces
+  // (fp64 scaler statistics, TD target, losses, Adam, polyak) are shared with the exact fp32 path
+  const bool tc = a->precision == OIS_PRECISION_BF16;
   if (phase == 0) {
     OIS_CHECK_ARG(io->states && io->actions && io->rewards && io->next_states && io->terminated && io->truncated,
                   "null batch tensor");
@@ -449,6 +457,31 @@ extern "C" int ois_ddpg_update_phase(OisAgent* a, const OisScaler* scaler, const
     } else {
       OIS_CHECK_CUDA(cudaMemcpyAsync(a->u_sn, io->states, sizeof(float) * B * D, cudaMemcpyDeviceToDevice, s));
       OIS_CHECK_CUDA(cudaMemcpyAsync(a->u_s2n, io->next_states, sizeof(float) * B * D, cudaMemcpyDeviceToDevice, s));
+    }
+    if (tc) {
+      // ddpg.py:385-386 target actor on next_states and ddpg.py:399 critic on (states, actions) are independent:
+      // they advance layer by layer in the same grouped launches
+      if (int e = tcu_pack_x(a, TCU_ACTS_SCRATCH, a->u_s2n, D, 0, D, nullptr, 0, 0, nullptr, 0, s)) return e;
+      if (int e = tcu_pack_x(a, TCU_ACTS_CRITIC, a->u_sn, D, 0, D, io->actions, A, A, nullptr, 0, s)) return e;
+      {
+        const int nets[2] = {TCU_ACTOR_T, TCU_CRITIC}, acts[2] = {TCU_ACTS_SCRATCH, TCU_ACTS_CRITIC};
+        const float* P32[2] = {io->actor_target, io->critic};
+        float* y[2] = {a->u_a, a->u_q};
+        if (int e = tcu_forward(a, 2, nets, P32, acts, y, s)) return e;
+      }
+      // ddpg.py:387-396 target critic on (next_states, target actions), TD target
+      if (int e = tcu_pack_x(a, TCU_ACTS_SCRATCH, a->u_s2n, D, 0, D, a->u_a, A, A, nullptr, 0, s)) return e;
+      {
+        const int nets[1] = {TCU_CRITIC_T}, acts[1] = {TCU_ACTS_SCRATCH};
+        const float* P32[1] = {io->critic_target};
+        float* y[1] = {a->u_q2};
+        if (int e = tcu_forward(a, 1, nets, P32, acts, y, s)) return e;
+      }
+      td_target_kernel<<<eg(B, 256), 256, 0, s>>>(io->rewards, io->terminated, io->truncated, a->u_q2, io->discount, a->u_y, B);
+      critic_loss_kernel<<<1, 256, 0, s>>>(a->u_q, a->u_y, a->u_dq, B, io->stats);   // ddpg.py:401-407
+      OIS_CHECK_LAUNCH();
+      if (int e = tcu_pack_x(a, TCU_DZ, a->u_dq, 1, 0, 1, nullptr, 0, 0, nullptr, 0, s)) return e;
+      return tcu_backward(a, TCU_CRITIC, io->critic_grad, TCU_ACTS_CRITIC, nullptr, s);
     }
     // ddpg.py:385-396  target actor / target critic / TD target
     if (int e = mlp_forward_fp32(a->actor, io->actor_target, a->u_s2n, D, a->ah0, a->ah1, a->ah2, a->u_a, B, s)) return e;
@@ -469,6 +502,32 @@ extern "C" int ois_ddpg_update_phase(OisAgent* a, const OisScaler* scaler, const
     // ddpg.py:416  critic optimizer step
     if (int e = adam_step(io->critic, io->critic_m, io->critic_v, io->critic_grad, oc.total, grad_scale, io->critic_lr,
                           io->beta1, io->beta2, io->adam_eps, io->adam_step, io->adam_step_dev, s)) return e;
+    if (tc) {
+      tcu_invalidate(a, TCU_CRITIC);
+      // ddpg.py:420-423 policy loss through the updated critic
+      if (int e = tcu_pack_x(a, TCU_ACTS_ACTOR, a->u_sn, D, 0, D, nullptr, 0, 0, nullptr, 0, s)) return e;
+      {
+        const int nets[1] = {TCU_ACTOR}, acts[1] = {TCU_ACTS_ACTOR};
+        const float* P32[1] = {io->actor};
+        float* y[1] = {a->u_a};
+        if (int e = tcu_forward(a, 1, nets, P32, acts, y, s)) return e;
+      }
+      if (int e = tcu_pack_x(a, TCU_ACTS_CRITIC, a->u_sn, D, 0, D, a->u_a, A, A, nullptr, 0, s)) return e;
+      {
+        const int nets[1] = {TCU_CRITIC}, acts[1] = {TCU_ACTS_CRITIC};
+        const float* P32[1] = {io->critic};
+        float* y[1] = {a->u_q};
+        if (int e = tcu_forward(a, 1, nets, P32, acts, y, s)) return e;
+      }
+      policy_loss_kernel<<<1, 256, 0, s>>>(a->u_q, a->u_dq, B, io->stats);
+      OIS_CHECK_LAUNCH();
+      if (int e = tcu_pack_x(a, TCU_DZ, a->u_dq, 1, 0, 1, nullptr, 0, 0, nullptr, 0, s)) return e;
+      // data gradient only through the critic (its parameter gradients from this pass are discarded by the reference
+      // at the next critic_optimizer.zero_grad(), ddpg.py:406), then through the output activation and the actor
+      if (int e = tcu_backward(a, TCU_CRITIC, nullptr, TCU_ACTS_CRITIC, a->u_dx, s)) return e;
+      if (int e = tcu_pack_x(a, TCU_DZ, a->u_dx, CI, D, A, nullptr, 0, 0, a->u_a, a->actor.out_act, s)) return e;
+      return tcu_backward(a, TCU_ACTOR, io->actor_grad, TCU_ACTS_ACTOR, nullptr, s);
+    }
     // ddpg.py:420-429  policy loss through the (updated) critic
     if (int e = mlp_forward_fp32(a->actor, io->actor, a->u_sn, D, a->ah0, a->ah1, a->ah2, a->u_a, B, s)) return e;
     copy_cols_kernel<<<eg(B * D, 256), 256, 0, s>>>(a->u_sn, D, a->u_x, CI, 0, B, D);
@@ -491,6 +550,11 @@ extern "C" int ois_ddpg_update_phase(OisAgent* a, const OisScaler* scaler, const
   polyak_kernel<<<eg(oa.total, 256), 256, 0, s>>>(io->actor_target, io->actor, oa.total, io->polyak);
   polyak_kernel<<<eg(oc.total, 256), 256, 0, s>>>(io->critic_target, io->critic, oc.total, io->polyak);
   OIS_CHECK_LAUNCH();
-  if (a->precision == OIS_PRECISION_BF16) tc_invalidate_weights(a);
+  if (tc) {
+    tc_invalidate_weights(a);
+    tcu_invalidate(a, TCU_ACTOR);
+    tcu_invalidate(a, TCU_ACTOR_T);
+    tcu_invalidate(a, TCU_CRITIC_T);
+  }
   return OIS_OK;
 }

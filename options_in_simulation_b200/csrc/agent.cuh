@@ -18,6 +18,8 @@ struct OisAgent {
   float *xn = nullptr, *h0 = nullptr, *h1 = nullptr, *h2 = nullptr;
   // bf16 tensor-core path (mlp_tc.cu)
   void* tc = nullptr;
+  // bf16 tensor-core update path (update_tc.cu)
+  void* tcu = nullptr;
 };
 
 namespace ois {

@@ -1,0 +1,158 @@
+"""GPU tests of the bf16 tcgen05 update path (csrc/update_tc.cu):
+  * the grouped-GEMM kernel in its four operand-orientation modes against torch on the same bf16-rounded operands
+    (fp32 accumulation on both sides: <= 2e-3 relative to the largest |C|, i.e. accumulation-order noise only);
+  * DDPG._update with ``mixed_precision=True`` against the exact fp32 path from the same state on the same batches.
+Stated bf16 tolerance of the update (operands, saved activations and back-propagated gradients are rounded to bf16 —
+8 mantissa bits — accumulation, master weights, Adam and polyak are fp32):
+    losses / Q statistics            <= 2e-2 relative to max(1, |ref|)
+    parameter gradients, per network ||g_bf16 - g_fp32||_2 <= 3e-2 ||g_fp32||_2   and cosine >= 0.999
+    updated weights after 3 updates  <= 2 * lr * updates absolute (Adam's step is bounded by lr per update)
+Structure is exact: the same tensors change, the scaler statistics (fp64, shared kernels) are identical."""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+from agent_cases import BATCH_NAMES, load
+
+pytestmark = pytest.mark.gpu
+
+
+def to_blocked(mat, rb):
+    """[R, C] float -> tile-blocked bf16 bytes: [R/rb][C/8][rb][8] (update_tc.cu header)."""
+    import torch
+
+    R, Cc = mat.shape
+    assert R % rb == 0 and Cc % 8 == 0
+    return mat.to(torch.bfloat16).reshape(R // rb, rb, Cc // 8, 8).permute(0, 2, 1, 3).contiguous()
+
+
+def debug_gemm(a_store, a_rb, b_store, b_rb, M, N, K, tile_n, mode, transposed=False):
+    import torch
+
+    from options_in_simulation_b200 import _lib as L
+
+    fn = L.lib().ois_debug_tc_gemm
+    fn.restype = C.c_int
+    fn.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_int, C.c_int] + [C.c_int] * 5 + [C.c_void_p, C.c_int, C.c_int,
+                                                                                                 C.c_void_p]
+    a_blk, b_blk = to_blocked(a_store, a_rb).cuda(), to_blocked(b_store, b_rb).cuda()
+    out = torch.full((N, M) if transposed else (M, N), float("nan"), device="cuda")
+    L.check(fn(a_blk.data_ptr(), a_store.shape[1] // 8, a_rb, b_blk.data_ptr(), b_store.shape[1] // 8, b_rb, M, N, K, tile_n,
+               mode, out.data_ptr(), out.shape[1], int(transposed), L.current_stream()))
+    torch.cuda.synchronize()
+    return out.cpu()
+
+
+@pytest.mark.parametrize("M,N,K,tile_n", [(512, 512, 512, 128), (512, 128, 512, 128), (128, 512, 128, 128), (512, 512, 16, 128),
+                                          (512, 16, 128, 16), (128, 16, 512, 16), (256, 256, 384, 128)])
+@pytest.mark.parametrize("mode", [0, 1, 2, 3])
+def test_tc_gemm_orientations(M, N, K, tile_n, mode):
+    import torch
+
+    k_stage = min(K, 128)
+    g = torch.Generator().manual_seed(M * 7 + N * 3 + K + mode)
+    A = torch.randn(M, K, generator=g).to(torch.bfloat16).float()
+    B = torch.randn(N, K, generator=g).to(torch.bfloat16).float()
+    ref = A @ B.T
+    a_store, a_rb = (A.T.contiguous(), k_stage) if mode & 1 else (A, 128)        # stored [K, M]: contraction over rows
+    b_store, b_rb = (B.T.contiguous(), k_stage) if mode & 2 else (B, tile_n)
+    if a_store.shape[1] % 8 or b_store.shape[1] % 8:
+        pytest.skip("stored matrix needs a multiple of 8 columns")
+    out = debug_gemm(a_store, a_rb, b_store, b_rb, M, N, K, tile_n, mode)
+    assert torch.isfinite(out).all()
+    assert (out - ref).abs().max() <= 2e-3 * ref.abs().max()
+    if mode == 3 and tile_n == 16:
+        out_t = debug_gemm(a_store, a_rb, b_store, b_rb, M, N, K, tile_n, mode, transposed=True)
+        assert torch.equal(out_t.T.contiguous(), out)
+
+
+def _fill(memory, d, meta):
+    import torch
+
+    n = meta["n_envs"]
+    for t in range(meta["rows"] // n):
+        sl = slice(t * n, (t + 1) * n)
+        memory.add_samples(**{k: torch.as_tensor(d[f"mem_{k}"][sl]).cuda().to(torch.bool if k in ("terminated", "truncated") else torch.float32)
+                              for k in BATCH_NAMES})
+
+
+@pytest.mark.parametrize("fname", ["agent_kamma_4d.npz", "agent_kaddpg_2d.npz", "agent_kaddpg_1d.npz", "agent_kamma_eval_tanh.npz"])
+def test_bf16_update_tracks_fp32_update(fname):
+    import torch
+
+    from test_agent_gpu import build_agent
+
+    d, meta = load(fname)
+    if meta["batch"] % 128:
+        pytest.skip("tensor-core update needs batch % 128 == 0")
+    exact, mem_e = build_agent(meta)
+    fast, mem_f = build_agent(meta, mixed_precision=True)
+    assert torch.equal(exact.policy.flat, fast.policy.flat) and torch.equal(exact.critic.flat, fast.critic.flat)
+    _fill(mem_e, d, meta)
+    _fill(mem_f, d, meta)
+    orig = torch.randperm
+    rounds = meta["rounds"]
+    for k in range(rounds):
+        idx = torch.as_tensor(d[f"r{k}_indices"])
+        torch.randperm = lambda n_, **kw: torch.cat([idx, torch.zeros(n_ - idx.numel(), dtype=torch.long)])
+        try:
+            # the comparison is per update: start the fast agent from the exact agent's state
+            for name in ("policy", "target_policy", "critic", "target_critic"):
+                getattr(fast, name).flat.copy_(getattr(exact, name).flat)
+            for name in ("policy_optimizer", "critic_optimizer"):
+                getattr(fast, name).m.copy_(getattr(exact, name).m)
+                getattr(fast, name).v.copy_(getattr(exact, name).v)
+                getattr(fast, name).step = getattr(exact, name).step
+            fast._state_preprocessor.load_state_dict(exact._state_preprocessor.state_dict())
+            fast._weights_changed()
+            t = int(d[f"r{k}_timestep"])
+            exact._update(t, 1000)
+            fast._update(t, 1000)
+        finally:
+            torch.randperm = orig
+        se, sf = exact._stats.cpu().numpy(), fast._stats.cpu().numpy()
+        assert np.all(np.abs(se - sf) <= 2e-2 * np.maximum(1.0, np.abs(se))), (k, se, sf)
+        for ge, gf, name in ((exact._grad_critic, fast._grad_critic, "critic"), (exact._grad_actor, fast._grad_actor, "actor")):
+            ge, gf = ge.double(), gf.double()
+            assert torch.isfinite(gf).all()
+            err = ((ge - gf).norm() / ge.norm()).item()
+            cos = (torch.dot(ge, gf) / (ge.norm() * gf.norm())).item()
+            assert err <= 3e-2 and cos >= 0.999, (name, k, err, cos)
+        for name, lr in (("policy", meta["lr_a"]), ("critic", meta["lr_c"])):
+            we, wf = getattr(exact, name).flat, getattr(fast, name).flat
+            assert (we - wf).abs().max().item() <= 2 * lr, (name, k)
+        for name in ("target_policy", "target_critic"):
+            we, wf = getattr(exact, name).flat, getattr(fast, name).flat
+            assert (we - wf).abs().max().item() <= 2 * meta["polyak"] * meta["lr_c"] + 1e-7, (name, k)
+        sc_e, sc_f = exact._state_preprocessor, fast._state_preprocessor
+        assert torch.equal(sc_e.running_mean, sc_f.running_mean) and torch.equal(sc_e.running_variance, sc_f.running_variance)
+
+
+def test_bf16_update_is_deterministic_and_learns():
+    """Two identical bf16 runs give bit-identical weights (no atomics in the gradient path), and the critic loss on a
+    fixed batch falls over 30 updates."""
+    import torch
+
+    from test_agent_gpu import build_agent
+
+    d, meta = load("agent_kamma_4d.npz")
+    finals, losses = [], []
+    for rep in range(2):
+        agent, mem = build_agent(meta, mixed_precision=True)
+        _fill(mem, d, meta)
+        idx = torch.as_tensor(d["r0_indices"])
+        orig = torch.randperm
+        torch.randperm = lambda n_, **kw: torch.cat([idx, torch.zeros(n_ - idx.numel(), dtype=torch.long)])
+        try:
+            ls = []
+            for i in range(30):
+                agent._update(100 + i, 1000)
+                ls.append(float(agent._stats[0]))
+        finally:
+            torch.randperm = orig
+        finals.append((agent.policy.flat.clone(), agent.critic.flat.clone()))
+        losses.append(ls)
+    assert torch.equal(finals[0][0], finals[1][0]) and torch.equal(finals[0][1], finals[1][1])
+    assert losses[0] == losses[1]
+    assert np.mean(losses[0][-5:]) < 0.7 * np.mean(losses[0][:5]), losses[0]

@@ -196,7 +196,7 @@ class World:
                                        replacement=False)
         cfg_a = {"batch_size": 512, "discount_factor": 0.999, "polyak": 0.005, "actor_learning_rate": 3e-4,
                  "critic_learning_rate": 1e-3, "random_timesteps": 0, "learning_starts": 0,
-                 "mixed_precision": precision == "bf16", "sampler": "device",
+                 "mixed_precision": precision == "bf16", "sampler": "device", "graph_update": True,
                  "state_preprocessor": A.RunningStandardScaler, "state_preprocessor_kwargs": {"size": osp, "device": dev},
                  "exploration": {"noise": A.OrnsteinUhlenbeckNoise(0.15, 0.1, wl["ou"], device=dev),
                                  "initial_scale": 1.0, "final_scale": 1e-4, "timesteps": wl["T_e"]},

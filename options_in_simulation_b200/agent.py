@@ -52,6 +52,8 @@ DDPG_DEFAULT_CONFIG = {   # src/my_agents/ddpg.py:19-61
     # extensions of this implementation (absent from the reference)
     "sampler": "host",        # "host": torch.randperm like the reference; "device": Philox/Feistel kernel (no host sync)
     "track_stats_interval": 0,  # > 0: read losses / Q stats back every that many updates (the reference does every update)
+    "graph_update": False,    # capture gather + the three update phases into ONE CUDA graph and replay it (needs
+                              # sampler "device", world_size 1): ~50 launches per update become one graph launch
 }
 
 _LAYER_KEYS = ("net.0", "net.2", "net.4", "net.6")   # nn.Sequential indices of the Linear layers
@@ -348,6 +350,8 @@ class DDPG:
         self._handle_rows = 0
         self._act_calls = 0
         self._updates = 0
+        self._graph = None            # (torch.cuda.CUDAGraph, idx buffer) of one update, see _update_graphed
+        self._step_dev = None
         self._seed = int(os.environ.get("OIS_SEED", "42")) + self.rank    # skrl set_seed convention: seed + rank
         self._fused_replay = False
         self._supplied = {}
@@ -384,6 +388,7 @@ class DDPG:
     def _weights_changed(self):
         if self._handle is not None:
             L.check(L.lib().ois_agent_invalidate(self._handle))
+        self._graph = None    # a captured update assumes the weight images its previous replay left behind
 
     def __del__(self):
         try:
@@ -603,10 +608,70 @@ class DDPG:
         io.stats = self._stats.data_ptr()
         return io
 
+    def _track_update_stats(self):
+        every = self.cfg["track_stats_interval"] or (1 if self.write_interval > 0 else 0)
+        if every and self._updates % every == 0:   # ddpg.py:452-461
+            st = self._stats.tolist()
+            self.track_data("Loss / Policy loss", st[1])
+            self.track_data("Loss / Critic loss", st[0])
+            self.track_data("Q-network / Q1 (max)", st[2])
+            self.track_data("Q-network / Q1 (min)", st[3])
+            self.track_data("Q-network / Q1 (mean)", st[4])
+            self.track_data("Target / Target (max)", st[5])
+            self.track_data("Target / Target (min)", st[6])
+            self.track_data("Target / Target (mean)", st[7])
+
+    def _update_graphed(self):
+        """One update as ONE CUDA-graph launch: the sampled indices land in a fixed buffer (the Philox sampler runs
+        outside the graph: its offset and the memory length change per call), the graph holds the gather and the
+        three phases; the Adam step count lives on the device (OisUpdateIO.adam_step_dev)."""
+        lib, m = L.lib(), self.memory
+        if m.sampler != "device" or self.is_distributed or m._supplied_indexes:
+            raise L.OisError("graph_update needs sampler='device', world_size 1 and no supplied indexes")
+        if self._graph is None:
+            idx = torch.empty(self._batch_size, dtype=torch.int64, device=self.device)
+            self._step_dev = torch.tensor([self.critic_optimizer.step], dtype=torch.int64, device=self.device)
+            m.draw_indices(idx)
+            batch = m.sample_by_index(self._tensors_names, idx)[0]      # allocates the batch buffers once, eagerly
+            io = self._update_io(batch)
+            io.adam_step_dev = self._step_dev.data_ptr()
+            # this call's update runs eagerly (it also leaves the weight images in their steady state); the same
+            # sequence is then captured — capture records, it does not execute — for every later call
+            self._step_dev.add_(1)
+            for ph in range(3):
+                L.check(lib.ois_ddpg_update_phase(self._handle, self._scaler_ref(), C.byref(io), ph, 1.0, L.current_stream()))
+            torch.cuda.synchronize()
+            graph = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(graph):
+                self._step_dev.add_(1)
+                m.sample_by_index(self._tensors_names, idx)
+                for ph in range(3):
+                    L.check(lib.ois_ddpg_update_phase(self._handle, self._scaler_ref(), C.byref(io), ph, 1.0, L.current_stream()))
+            self._graph = (graph, idx, io, batch)
+        else:
+            graph, idx = self._graph[0], self._graph[1]
+            m.draw_indices(idx)
+            graph.replay()
+        n = 1
+        self.policy_optimizer.step += n
+        self.critic_optimizer.step += n
+        self._updates += n
+        self.kernel_launches += n * (2 + UPDATE_LAUNCHES_BF16 if self._mixed_precision else 2 + UPDATE_LAUNCHES)
+        # host-side "weights changed" flags of the library are not touched by a replay: the actor's inference image
+        # must be rebuilt by the next act()
+        L.check(lib.ois_agent_invalidate(self._handle))
+        return n
+
     def _update(self, timestep, timesteps):
         """ddpg.py:357-465: three C-ABI phases split where skrl all-reduces gradients."""
         self._ensure_handle(self._batch_size)
         lib = L.lib()
+        if self.cfg["graph_update"]:
+            done = 0
+            while done < self._gradient_steps:
+                done += self._update_graphed()
+                self._track_update_stats()
+            return
         for _ in range(self._gradient_steps):
             batch = self.memory.sample(names=self._tensors_names, batch_size=self._batch_size)[0]
             io = self._update_io(batch)
@@ -624,17 +689,7 @@ class DDPG:
             L.check(lib.ois_ddpg_update_phase(self._handle, self._scaler_ref(), C.byref(io), 2, scale, stream))
             self._updates += 1
             self.kernel_launches += UPDATE_LAUNCHES_BF16 if self._mixed_precision else UPDATE_LAUNCHES
-            every = self.cfg["track_stats_interval"] or (1 if self.write_interval > 0 else 0)
-            if every and self._updates % every == 0:   # ddpg.py:452-461
-                st = self._stats.tolist()
-                self.track_data("Loss / Policy loss", st[1])
-                self.track_data("Loss / Critic loss", st[0])
-                self.track_data("Q-network / Q1 (max)", st[2])
-                self.track_data("Q-network / Q1 (min)", st[3])
-                self.track_data("Q-network / Q1 (mean)", st[4])
-                self.track_data("Target / Target (max)", st[5])
-                self.track_data("Target / Target (min)", st[6])
-                self.track_data("Target / Target (mean)", st[7])
+            self._track_update_stats()
 
     # ------------------------------------------------------------------ tracking / checkpoints (base.py:193-249,364-395)
     def write_tracking_data(self, timestep, timesteps):
@@ -681,7 +736,7 @@ class DDPG:
 # critic bwd (4 wgrad + 4 colsum + 3 dgrad) | adam + 4 fwd + 2 copy + 4 fwd + loss + critic dgrad 4 + out-grad +
 # actor bwd 11 | adam + 2 polyak
 UPDATE_LAUNCHES = (2 + 4 + 2 + 4 + 1 + 2 + 4 + 1 + 11) + (1 + 4 + 2 + 4 + 1 + 4 + 1 + 11) + 3
-# on the bf16 tcgen05 path (csrc/update_tc.cu): 2 scaler + 2 weight images (targets) + 2 pack + 4 grouped fwd (target
-# actor || critic) + pack + 4 fwd + td + loss + pack + critic bwd (3 dgrad + grouped wgrad + bias) | adam + pack +
-# image + 4 fwd + pack + image + 4 fwd + loss + pack + critic dgrad (3 + 1) + pack + actor bwd 5 | adam + 2 polyak
-UPDATE_LAUNCHES_BF16 = (2 + 2 + 2 + 4 + 1 + 4 + 1 + 1 + 1 + 5) + (1 + 1 + 1 + 4 + 1 + 1 + 4 + 1 + 1 + 4 + 1 + 5) + 3
+# on the bf16 tcgen05 path (csrc/update_tc.cu; steady state, weight images kept current by Adam / polyak):
+# batch prep + 4 grouped fwd (target actor || critic) + 4 fwd + TD/loss + critic bwd (3 dgrad + grouped wgrad + bias)
+# | adam + 4 fwd + 4 fwd + loss + critic dgrad (3 + 1) + pack + actor bwd 5 | adam + polyak pair
+UPDATE_LAUNCHES_BF16 = (1 + 4 + 4 + 1 + 5) + (1 + 4 + 4 + 1 + 4 + 1 + 5) + 2

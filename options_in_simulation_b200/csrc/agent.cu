@@ -40,37 +40,54 @@ __global__ void scaler_apply_kernel(const float* __restrict__ x, float* __restri
   y[row * ldy + c] = fminf(fmaxf(v, -5.0f), 5.0f);
 }
 
-// RunningStandardScaler(x, train=True) on a [B, dim] batch, one CTA: batch mean / unbiased variance
-// (torch.mean / torch.var are float32 results; we accumulate in fp64 and round once), parallel-variance
-// merge into the fp64 running statistics, then standardise with the UPDATED statistics.
-__global__ void __launch_bounds__(256)
-scaler_train_kernel(const float* __restrict__ x, float* __restrict__ y, int B, int dim, double* __restrict__ mean,
-                    double* __restrict__ var, double* __restrict__ count, int ldy) {
+// RunningStandardScaler(x, train=True) on a [B, dim] batch, one CTA of 256 threads: batch mean / unbiased variance
+// (torch.mean / torch.var are float32 results; we accumulate in fp64 and round once), parallel-variance merge into
+// the fp64 running statistics, then standardise with the UPDATED statistics.  All columns are swept together (one
+// global-memory round trip per pass instead of one per column); the fp64 summation order per column is fixed:
+// thread-strided partial sums -> xor-shuffle tree -> the eight warp totals in warp order.
+__device__ void scaler_train_block(const float* __restrict__ x, float* __restrict__ y, int B, int dim,
+                                   double* __restrict__ mean, double* __restrict__ var, double* __restrict__ count, int ldy) {
   __shared__ double s_sum[8][16];
   __shared__ float s_mu[16], s_sd[16];
   __shared__ double s_bmean[16];
   const int t = threadIdx.x, lane = t & 31, wp = t >> 5;
+  double a[16];
   // pass 1: mean
-  for (int c = 0; c < dim; ++c) {
-    double a = 0.0;
-    for (int r = t; r < B; r += 256) a += (double)x[(size_t)r * dim + c];
-    for (int o = 16; o > 0; o >>= 1) a += __shfl_xor_sync(0xffffffffu, a, o);
-    if (lane == 0) s_sum[wp][c] = a;
+#pragma unroll
+  for (int c = 0; c < 16; ++c) a[c] = 0.0;
+  for (int r = t; r < B; r += 256) {
+#pragma unroll
+    for (int c = 0; c < 16; ++c)
+      if (c < dim) a[c] += (double)x[(size_t)r * dim + c];
+  }
+#pragma unroll
+  for (int c = 0; c < 16; ++c) {
+    if (c < dim) {
+      for (int o = 16; o > 0; o >>= 1) a[c] += __shfl_xor_sync(0xffffffffu, a[c], o);
+      if (lane == 0) s_sum[wp][c] = a[c];
+    }
   }
   __syncthreads();
   if (t < dim) {
-    double a = 0.0;
-    for (int w = 0; w < 8; ++w) a += s_sum[w][t];
-    s_bmean[t] = a / (double)B;
+    double m = 0.0;
+    for (int w = 0; w < 8; ++w) m += s_sum[w][t];
+    s_bmean[t] = m / (double)B;
   }
   __syncthreads();
   // pass 2: centred sum of squares
-  for (int c = 0; c < dim; ++c) {
-    double a = 0.0;
-    const double mu = s_bmean[c];
-    for (int r = t; r < B; r += 256) { const double d = (double)x[(size_t)r * dim + c] - mu; a += d * d; }
-    for (int o = 16; o > 0; o >>= 1) a += __shfl_xor_sync(0xffffffffu, a, o);
-    if (lane == 0) s_sum[wp][c] = a;
+#pragma unroll
+  for (int c = 0; c < 16; ++c) a[c] = 0.0;
+  for (int r = t; r < B; r += 256) {
+#pragma unroll
+    for (int c = 0; c < 16; ++c)
+      if (c < dim) { const double d = (double)x[(size_t)r * dim + c] - s_bmean[c]; a[c] += d * d; }
+  }
+#pragma unroll
+  for (int c = 0; c < 16; ++c) {
+    if (c < dim) {
+      for (int o = 16; o > 0; o >>= 1) a[c] += __shfl_xor_sync(0xffffffffu, a[c], o);
+      if (lane == 0) s_sum[wp][c] = a[c];
+    }
   }
   __syncthreads();
   if (t < dim) {
@@ -96,6 +113,13 @@ scaler_train_kernel(const float* __restrict__ x, float* __restrict__ y, int B, i
     const float v = __fdiv_rn(__fsub_rn(x[i], s_mu[c]), __fadd_rn(s_sd[c], 1e-8f));
     y[(size_t)r * ldy + c] = fminf(fmaxf(v, -5.0f), 5.0f);
   }
+  __syncthreads();                      // y, the statistics and count are complete for whoever runs next in this CTA
+}
+
+__global__ void __launch_bounds__(256)
+scaler_train_kernel(const float* __restrict__ x, float* __restrict__ y, int B, int dim, double* __restrict__ mean,
+                    double* __restrict__ var, double* __restrict__ count, int ldy) {
+  scaler_train_block(x, y, B, dim, mean, var, count, ldy);
 }
 
 // copy [B, w] block into columns [col0, col0+w) of a wider row-major matrix
@@ -118,19 +142,37 @@ __global__ void td_target_kernel(const float* __restrict__ r, const uint8_t* __r
 }
 
 // critic loss = mean((q - y)^2), dq = 2 (q - y) / B; also target stats.   one CTA
+// With r != null the TD target (ddpg.py:391-396) is computed here first; with dz != null the gradient is also written as
+// column 0 of a tile-blocked bf16 [B, 16] matrix (the tensor-core backward's input, update_tc.cu).
 __global__ void __launch_bounds__(256)
-critic_loss_kernel(const float* __restrict__ q, const float* __restrict__ y, float* __restrict__ dq, int B,
-                   float* __restrict__ stats) {
+critic_loss_kernel(const float* __restrict__ q, float* __restrict__ y, float* __restrict__ dq, int B,
+                   float* __restrict__ stats, const float* __restrict__ r, const uint8_t* __restrict__ te,
+                   const uint8_t* __restrict__ tr, const float* __restrict__ q2, float discount, uint8_t* __restrict__ dz) {
   __shared__ float s_sum[8], s_ysum[8], s_ymax[8], s_ymin[8];
+  pdl_wait();
+  if (threadIdx.x == 0) pdl_trigger();
   const int t = threadIdx.x, lane = t & 31, wp = t >> 5;
   float a = 0.f, ys = 0.f, ymx = -INFINITY, ymn = INFINITY;
   for (int i = t; i < B; i += 256) {
-    const float d = q[i] - y[i];
+    float yi;
+    if (r) {
+      const float nd = (te[i] | tr[i]) ? 0.0f : 1.0f;
+      yi = __fadd_rn(r[i], __fmul_rn(__fmul_rn(discount, nd), q2[i]));
+      y[i] = yi;
+    } else {
+      yi = y[i];
+    }
+    const float d = q[i] - yi;
     a += d * d;
-    dq[i] = 2.0f * d / (float)B;
-    ys += y[i];
-    ymx = fmaxf(ymx, y[i]);
-    ymn = fminf(ymn, y[i]);
+    const float g = 2.0f * d / (float)B;
+    dq[i] = g;
+    if (dz) {
+      *reinterpret_cast<uint4*>(dz + tcu_chunk_off(i, 0, 2, 128)) = make_uint4((uint32_t)tcu_bf16_bits(g), 0u, 0u, 0u);
+      *reinterpret_cast<uint4*>(dz + tcu_chunk_off(i, 1, 2, 128)) = make_uint4(0u, 0u, 0u, 0u);
+    }
+    ys += yi;
+    ymx = fmaxf(ymx, yi);
+    ymn = fminf(ymn, yi);
   }
   for (int o = 16; o > 0; o >>= 1) {
     a += __shfl_xor_sync(0xffffffffu, a, o);
@@ -150,8 +192,11 @@ critic_loss_kernel(const float* __restrict__ q, const float* __restrict__ y, flo
 
 // policy loss = -mean(q_pi), dq = -1/B; also Q stats.   one CTA
 __global__ void __launch_bounds__(256)
-policy_loss_kernel(const float* __restrict__ q, float* __restrict__ dq, int B, float* __restrict__ stats) {
+policy_loss_kernel(const float* __restrict__ q, float* __restrict__ dq, int B, float* __restrict__ stats,
+                   uint8_t* __restrict__ dz) {
   __shared__ float s_sum[8], s_max[8], s_min[8];
+  pdl_wait();
+  if (threadIdx.x == 0) pdl_trigger();
   const int t = threadIdx.x, lane = t & 31, wp = t >> 5;
   float a = 0.f, mx = -INFINITY, mn = INFINITY;
   for (int i = t; i < B; i += 256) {
@@ -159,6 +204,10 @@ policy_loss_kernel(const float* __restrict__ q, float* __restrict__ dq, int B, f
     mx = fmaxf(mx, q[i]);
     mn = fminf(mn, q[i]);
     dq[i] = -1.0f / (float)B;
+    if (dz) {
+      *reinterpret_cast<uint4*>(dz + tcu_chunk_off(i, 0, 2, 128)) = make_uint4((uint32_t)tcu_bf16_bits(-1.0f / (float)B), 0u, 0u, 0u);
+      *reinterpret_cast<uint4*>(dz + tcu_chunk_off(i, 1, 2, 128)) = make_uint4(0u, 0u, 0u, 0u);
+    }
   }
   for (int o = 16; o > 0; o >>= 1) {
     a += __shfl_xor_sync(0xffffffffu, a, o);
@@ -190,8 +239,10 @@ __global__ void out_act_grad_kernel(const float* __restrict__ da, int ldda, int 
 __global__ void __launch_bounds__(256)
 adam_kernel(float* __restrict__ p, float* __restrict__ m, float* __restrict__ v, const float* __restrict__ g, int64_t n,
             float grad_scale, double lr, double beta1, double beta2, float eps, int64_t step_host,
-            const int64_t* __restrict__ step_dev) {
+            const int64_t* __restrict__ step_dev, uint8_t* __restrict__ img, int in_dim, int out_dim) {
   __shared__ float s_step_size, s_bc2_sqrt;
+  pdl_wait();
+  if (threadIdx.x == 0) pdl_trigger();
   if (threadIdx.x == 0) {
     const double t = (double)(step_dev ? step_dev[0] : step_host);
     s_step_size = (float)(lr / (1.0 - pow(beta1, t)));
@@ -207,7 +258,68 @@ adam_kernel(float* __restrict__ p, float* __restrict__ m, float* __restrict__ v,
   const float denom = sqrtf(vi) / s_bc2_sqrt + eps;
   m[i] = mi;
   v[i] = vi;
-  p[i] = p[i] - s_step_size * (mi / denom);            // param.addcdiv_(exp_avg, denom, value=-step_size)
+  const float pn = p[i] - s_step_size * (mi / denom);  // param.addcdiv_(exp_avg, denom, value=-step_size)
+  p[i] = pn;
+  if (img) tcu_img_store(img, i, pn, in_dim, out_dim);  // keep the bf16 tensor-core image current (update_tc.cu)
+}
+
+// both target networks in one launch, each optionally with its bf16 tensor-core image kept current
+struct PolyakPair {
+  float* pt[2];
+  const float* p[2];
+  int64_t n[2];
+  uint8_t* img[2];
+  int in_dim[2], out_dim[2];
+};
+__global__ void __launch_bounds__(256)
+polyak_pair_kernel(const __grid_constant__ PolyakPair a, float tau) {
+  pdl_wait();
+  if (threadIdx.x == 0) pdl_trigger();
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  int k = 0;
+  if (i >= a.n[0]) { i -= a.n[0]; k = 1; }
+  if (i >= a.n[k]) return;
+  const float v = __fadd_rn(__fmul_rn(a.pt[k][i], 1.0f - tau), __fmul_rn(tau, a.p[k][i]));
+  a.pt[k][i] = v;
+  if (a.img[k]) tcu_img_store(a.img[k], i, v, a.in_dim[k], a.out_dim[k]);
+}
+
+// the tensor-core update's batch preparation in ONE CTA: ddpg.py:381-382 (scaler, train=True, on states then on
+// next_states — sequentially dependent through the running statistics), then the bf16 network inputs:
+//   x_critic  = [scaled states, sampled actions]   (critic input; its first D columns are also the actor's input)
+//   x_scratch = [scaled next_states, 0]            (target actor input; the target actions land in columns D.. later)
+__global__ void __launch_bounds__(256)
+tcu_batch_prep_kernel(const float* __restrict__ states, const float* __restrict__ next_states,
+                      const float* __restrict__ actions, float* __restrict__ sn, float* __restrict__ s2n, int B, int D, int A,
+                      double* __restrict__ mean, double* __restrict__ var, double* __restrict__ count,
+                      uint8_t* __restrict__ x_critic, uint8_t* __restrict__ x_scratch) {
+  pdl_wait();
+  if (threadIdx.x == 0) pdl_trigger();
+  if (mean) {
+    scaler_train_block(states, sn, B, D, mean, var, count, D);
+    scaler_train_block(next_states, s2n, B, D, mean, var, count, D);
+  } else {
+    for (int i = threadIdx.x; i < B * D; i += 256) { sn[i] = states[i]; s2n[i] = next_states[i]; }
+    __syncthreads();
+  }
+  for (int i = threadIdx.x; i < B * 2; i += 256) {
+    const int r = i >> 1, c8 = i & 1;
+    uint16_t vc[8], vs[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const int c = c8 * 8 + j;
+      const float xc = c < D ? sn[(size_t)r * D + c] : c < D + A ? actions[(size_t)r * A + (c - D)] : 0.f;
+      const float xs = c < D ? s2n[(size_t)r * D + c] : 0.f;
+      vc[j] = tcu_bf16_bits(xc);
+      vs[j] = tcu_bf16_bits(xs);
+    }
+    auto pk = [](const uint16_t* v) {
+      return make_uint4((uint32_t)v[0] | ((uint32_t)v[1] << 16), (uint32_t)v[2] | ((uint32_t)v[3] << 16),
+                        (uint32_t)v[4] | ((uint32_t)v[5] << 16), (uint32_t)v[6] | ((uint32_t)v[7] << 16));
+    };
+    *reinterpret_cast<uint4*>(x_critic + tcu_chunk_off(r, c8, 2, 128)) = pk(vc);
+    *reinterpret_cast<uint4*>(x_scratch + tcu_chunk_off(r, c8, 2, 128)) = pk(vs);
+  }
 }
 
 // Model.update_parameters: p_t.mul_(1 - polyak); p_t.add_(polyak * p)
@@ -287,9 +399,10 @@ static int mlp_backward_fp32(const OisMlpShape& sh, const float* P, float* G, co
 }
 
 static int adam_step(float* p, float* m, float* v, const float* g, int64_t n, float grad_scale, double lr, double b1,
-                     double b2, double eps, int64_t step, const int64_t* step_dev, cudaStream_t s) {
-  adam_kernel<<<eg(n, 256), 256, 0, s>>>(p, m, v, g, n, grad_scale, lr, b1, b2, (float)eps, step, step_dev);
-  OIS_CHECK_LAUNCH();
+                     double b2, double eps, int64_t step, const int64_t* step_dev, uint8_t* img, const OisMlpShape& sh,
+                     cudaStream_t s) {
+  OIS_CHECK_CUDA(launch_pdl(adam_kernel, eg(n, 256), 256, 0, s, p, m, v, g, n, grad_scale, lr, b1, b2, (float)eps, step,
+                            step_dev, img, (int)sh.in_dim, (int)sh.out_dim));
   return OIS_OK;
 }
 
@@ -441,14 +554,45 @@ extern "C" int ois_ddpg_update_phase(OisAgent* a, const OisScaler* scaler, const
   cudaStream_t s = (cudaStream_t)stream;
   const int B = a->batch, D = a->actor.in_dim, A = a->actor.out_dim, CI = a->critic.in_dim;
   const MlpOffsets oa = mlp_offsets(a->actor), oc = mlp_offsets(a->critic);
-  // OIS_PRECISION_BF16: every contraction below runs as a tcgen05 grouped GEMM (update_tc.cu); the element-wise pieces
-  // (fp64 scaler statistics, TD target, losses, Adam, polyak) are shared with the exact fp32 path
+  const bool has_scaler = scaler && scaler->running_mean;
+  // OIS_PRECISION_BF16: every contraction below runs as a tcgen05 grouped GEMM (update_tc.cu) and the element-wise
+  // pieces (fp64 scaler statistics, TD target, losses, Adam, polyak — the same arithmetic as the exact fp32 path) are
+  // fused around them; every launch is a programmatic dependent launch, so prologues overlap the predecessor's tail
   const bool tc = a->precision == OIS_PRECISION_BF16;
   if (phase == 0) {
     OIS_CHECK_ARG(io->states && io->actions && io->rewards && io->next_states && io->terminated && io->truncated,
                   "null batch tensor");
+    if (tc) {
+      // ddpg.py:381-382 scaler(train=True) on states, then next_states; bf16 inputs of the critic and the target actor
+      uint8_t* x_critic = tcu_x_buffer(a, TCU_ACTS_CRITIC);
+      uint8_t* x_scratch = tcu_x_buffer(a, TCU_ACTS_SCRATCH);
+      OIS_CHECK_CUDA(launch_pdl(tcu_batch_prep_kernel, 1, 256, 0, s, io->states, io->next_states, io->actions, a->u_sn, a->u_s2n, B,
+                                D, A, has_scaler ? scaler->running_mean : (double*)nullptr,
+                                has_scaler ? scaler->running_variance : (double*)nullptr,
+                                has_scaler ? scaler->current_count : (double*)nullptr, x_critic, x_scratch));
+      // ddpg.py:385-386 target actor on next_states and ddpg.py:399 critic on (states, actions) are independent: they
+      // advance layer by layer in the same grouped launches; the target actions land in the scratch input's columns D..
+      {
+        const int nets[2] = {TCU_ACTOR_T, TCU_CRITIC}, acts[2] = {TCU_ACTS_SCRATCH, TCU_ACTS_CRITIC};
+        const float* P32[2] = {io->actor_target, io->critic};
+        float* y[2] = {a->u_a, a->u_q};
+        uint8_t* xo[2] = {x_scratch, nullptr};
+        if (int e = tcu_forward(a, 2, nets, P32, acts, y, xo, D, s)) return e;
+      }
+      // ddpg.py:387-396 target critic on (next_states, target actions)
+      {
+        const int nets[1] = {TCU_CRITIC_T}, acts[1] = {TCU_ACTS_SCRATCH};
+        const float* P32[1] = {io->critic_target};
+        float* y[1] = {a->u_q2};
+        if (int e = tcu_forward(a, 1, nets, P32, acts, y, nullptr, 0, s)) return e;
+      }
+      // TD target + MSE + d(loss)/dq as the backward's bf16 input (ddpg.py:391-407)
+      OIS_CHECK_CUDA(launch_pdl(critic_loss_kernel, 1, 256, 0, s, (const float*)a->u_q, a->u_y, a->u_dq, B, io->stats, io->rewards,
+                                io->terminated, io->truncated, (const float*)a->u_q2, io->discount, tcu_x_buffer(a, TCU_DZ)));
+      return tcu_backward(a, TCU_CRITIC, io->critic_grad, TCU_ACTS_CRITIC, nullptr, s);
+    }
     // ddpg.py:381-382  scaler(train=True) on states, then on next_states
-    if (scaler && scaler->running_mean) {
+    if (has_scaler) {
       scaler_train_kernel<<<1, 256, 0, s>>>(io->states, a->u_sn, B, D, scaler->running_mean, scaler->running_variance,
                                             scaler->current_count, D);
       scaler_train_kernel<<<1, 256, 0, s>>>(io->next_states, a->u_s2n, B, D, scaler->running_mean,
@@ -457,31 +601,6 @@ extern "C" int ois_ddpg_update_phase(OisAgent* a, const OisScaler* scaler, const
     } else {
       OIS_CHECK_CUDA(cudaMemcpyAsync(a->u_sn, io->states, sizeof(float) * B * D, cudaMemcpyDeviceToDevice, s));
       OIS_CHECK_CUDA(cudaMemcpyAsync(a->u_s2n, io->next_states, sizeof(float) * B * D, cudaMemcpyDeviceToDevice, s));
-    }
-    if (tc) {
-      // ddpg.py:385-386 target actor on next_states and ddpg.py:399 critic on (states, actions) are independent:
-      // they advance layer by layer in the same grouped launches
-      if (int e = tcu_pack_x(a, TCU_ACTS_SCRATCH, a->u_s2n, D, 0, D, nullptr, 0, 0, nullptr, 0, s)) return e;
-      if (int e = tcu_pack_x(a, TCU_ACTS_CRITIC, a->u_sn, D, 0, D, io->actions, A, A, nullptr, 0, s)) return e;
-      {
-        const int nets[2] = {TCU_ACTOR_T, TCU_CRITIC}, acts[2] = {TCU_ACTS_SCRATCH, TCU_ACTS_CRITIC};
-        const float* P32[2] = {io->actor_target, io->critic};
-        float* y[2] = {a->u_a, a->u_q};
-        if (int e = tcu_forward(a, 2, nets, P32, acts, y, s)) return e;
-      }
-      // ddpg.py:387-396 target critic on (next_states, target actions), TD target
-      if (int e = tcu_pack_x(a, TCU_ACTS_SCRATCH, a->u_s2n, D, 0, D, a->u_a, A, A, nullptr, 0, s)) return e;
-      {
-        const int nets[1] = {TCU_CRITIC_T}, acts[1] = {TCU_ACTS_SCRATCH};
-        const float* P32[1] = {io->critic_target};
-        float* y[1] = {a->u_q2};
-        if (int e = tcu_forward(a, 1, nets, P32, acts, y, s)) return e;
-      }
-      td_target_kernel<<<eg(B, 256), 256, 0, s>>>(io->rewards, io->terminated, io->truncated, a->u_q2, io->discount, a->u_y, B);
-      critic_loss_kernel<<<1, 256, 0, s>>>(a->u_q, a->u_y, a->u_dq, B, io->stats);   // ddpg.py:401-407
-      OIS_CHECK_LAUNCH();
-      if (int e = tcu_pack_x(a, TCU_DZ, a->u_dq, 1, 0, 1, nullptr, 0, 0, nullptr, 0, s)) return e;
-      return tcu_backward(a, TCU_CRITIC, io->critic_grad, TCU_ACTS_CRITIC, nullptr, s);
     }
     // ddpg.py:385-396  target actor / target critic / TD target
     if (int e = mlp_forward_fp32(a->actor, io->actor_target, a->u_s2n, D, a->ah0, a->ah1, a->ah2, a->u_a, B, s)) return e;
@@ -493,35 +612,35 @@ extern "C" int ois_ddpg_update_phase(OisAgent* a, const OisScaler* scaler, const
     copy_cols_kernel<<<eg(B * D, 256), 256, 0, s>>>(a->u_sn, D, a->u_x, CI, 0, B, D);
     copy_cols_kernel<<<eg(B * A, 256), 256, 0, s>>>(io->actions, A, a->u_x, CI, D, B, A);
     if (int e = mlp_forward_fp32(a->critic, io->critic, a->u_x, CI, a->ch0, a->ch1, a->ch2, a->u_q, B, s)) return e;
-    critic_loss_kernel<<<1, 256, 0, s>>>(a->u_q, a->u_y, a->u_dq, B, io->stats);
+    critic_loss_kernel<<<1, 256, 0, s>>>(a->u_q, a->u_y, a->u_dq, B, io->stats, nullptr, nullptr, nullptr, nullptr, 0.f, nullptr);
     OIS_CHECK_LAUNCH();
     return mlp_backward_fp32(a->critic, io->critic, io->critic_grad, a->u_x, CI, a->ch0, a->ch1, a->ch2, a->u_dq, a->d2,
                              a->d1, a->d0, nullptr, B, s);
   }
   if (phase == 1) {
-    // ddpg.py:416  critic optimizer step
+    // ddpg.py:416  critic optimizer step (bf16 path: the critic's tensor-core image is kept current by the same kernel)
+    uint8_t* cimg = tc ? tcu_image_if_valid(a, TCU_CRITIC, io->critic) : nullptr;
+    if (tc && !cimg) tcu_invalidate(a, TCU_CRITIC);
     if (int e = adam_step(io->critic, io->critic_m, io->critic_v, io->critic_grad, oc.total, grad_scale, io->critic_lr,
-                          io->beta1, io->beta2, io->adam_eps, io->adam_step, io->adam_step_dev, s)) return e;
+                          io->beta1, io->beta2, io->adam_eps, io->adam_step, io->adam_step_dev, cimg, a->critic, s)) return e;
     if (tc) {
-      tcu_invalidate(a, TCU_CRITIC);
-      // ddpg.py:420-423 policy loss through the updated critic
-      if (int e = tcu_pack_x(a, TCU_ACTS_ACTOR, a->u_sn, D, 0, D, nullptr, 0, 0, nullptr, 0, s)) return e;
+      // ddpg.py:420-423 policy loss through the updated critic.  The actor reads the first D columns of the critic's
+      // input buffer (its image has zero weights beyond them) and writes its action into columns D.. of the same buffer
+      uint8_t* x_critic = tcu_x_buffer(a, TCU_ACTS_CRITIC);
       {
-        const int nets[1] = {TCU_ACTOR}, acts[1] = {TCU_ACTS_ACTOR};
+        const int nets[1] = {TCU_ACTOR}, acts[1] = {TCU_ACTS_ACTOR};   // its input buffer IS the critic's (update_tc.cu)
         const float* P32[1] = {io->actor};
         float* y[1] = {a->u_a};
-        if (int e = tcu_forward(a, 1, nets, P32, acts, y, s)) return e;
+        uint8_t* xo[1] = {x_critic};
+        if (int e = tcu_forward(a, 1, nets, P32, acts, y, xo, D, s)) return e;
       }
-      if (int e = tcu_pack_x(a, TCU_ACTS_CRITIC, a->u_sn, D, 0, D, a->u_a, A, A, nullptr, 0, s)) return e;
       {
         const int nets[1] = {TCU_CRITIC}, acts[1] = {TCU_ACTS_CRITIC};
         const float* P32[1] = {io->critic};
         float* y[1] = {a->u_q};
-        if (int e = tcu_forward(a, 1, nets, P32, acts, y, s)) return e;
+        if (int e = tcu_forward(a, 1, nets, P32, acts, y, nullptr, 0, s)) return e;
       }
-      policy_loss_kernel<<<1, 256, 0, s>>>(a->u_q, a->u_dq, B, io->stats);
-      OIS_CHECK_LAUNCH();
-      if (int e = tcu_pack_x(a, TCU_DZ, a->u_dq, 1, 0, 1, nullptr, 0, 0, nullptr, 0, s)) return e;
+      OIS_CHECK_CUDA(launch_pdl(policy_loss_kernel, 1, 256, 0, s, (const float*)a->u_q, a->u_dq, B, io->stats, tcu_x_buffer(a, TCU_DZ)));
       // data gradient only through the critic (its parameter gradients from this pass are discarded by the reference
       // at the next critic_optimizer.zero_grad(), ddpg.py:406), then through the output activation and the actor
       if (int e = tcu_backward(a, TCU_CRITIC, nullptr, TCU_ACTS_CRITIC, a->u_dx, s)) return e;
@@ -533,7 +652,7 @@ extern "C" int ois_ddpg_update_phase(OisAgent* a, const OisScaler* scaler, const
     copy_cols_kernel<<<eg(B * D, 256), 256, 0, s>>>(a->u_sn, D, a->u_x, CI, 0, B, D);
     copy_cols_kernel<<<eg(B * A, 256), 256, 0, s>>>(a->u_a, A, a->u_x, CI, D, B, A);
     if (int e = mlp_forward_fp32(a->critic, io->critic, a->u_x, CI, a->ch0, a->ch1, a->ch2, a->u_q, B, s)) return e;
-    policy_loss_kernel<<<1, 256, 0, s>>>(a->u_q, a->u_dq, B, io->stats);
+    policy_loss_kernel<<<1, 256, 0, s>>>(a->u_q, a->u_dq, B, io->stats, nullptr);
     OIS_CHECK_LAUNCH();
     // dgrad only through the critic (its parameter gradients from this pass are discarded by the reference at
     // the next critic_optimizer.zero_grad(), ddpg.py:406), then the actor's full backward
@@ -545,16 +664,26 @@ extern "C" int ois_ddpg_update_phase(OisAgent* a, const OisScaler* scaler, const
                              a->d0, nullptr, B, s);
   }
   // phase 2: ddpg.py:438 actor optimizer step, :443-444 polyak
+  uint8_t* aimg = tc ? tcu_image_if_valid(a, TCU_ACTOR, io->actor) : nullptr;
   if (int e = adam_step(io->actor, io->actor_m, io->actor_v, io->actor_grad, oa.total, grad_scale, io->actor_lr, io->beta1,
-                        io->beta2, io->adam_eps, io->adam_step, io->adam_step_dev, s)) return e;
+                        io->beta2, io->adam_eps, io->adam_step, io->adam_step_dev, aimg, a->actor, s)) return e;
+  if (tc) {
+    PolyakPair pp;
+    pp.pt[0] = io->actor_target; pp.p[0] = io->actor; pp.n[0] = oa.total;
+    pp.pt[1] = io->critic_target; pp.p[1] = io->critic; pp.n[1] = oc.total;
+    pp.img[0] = tcu_image_if_valid(a, TCU_ACTOR_T, io->actor_target);
+    pp.img[1] = tcu_image_if_valid(a, TCU_CRITIC_T, io->critic_target);
+    pp.in_dim[0] = a->actor.in_dim; pp.out_dim[0] = a->actor.out_dim;
+    pp.in_dim[1] = a->critic.in_dim; pp.out_dim[1] = a->critic.out_dim;
+    OIS_CHECK_CUDA(launch_pdl(polyak_pair_kernel, eg(oa.total + oc.total, 256), 256, 0, s, pp, io->polyak));
+    tc_invalidate_weights(a);                       // the inference kernel's own stream image is rebuilt by the next act
+    if (!aimg) tcu_invalidate(a, TCU_ACTOR);
+    if (!pp.img[0]) tcu_invalidate(a, TCU_ACTOR_T);
+    if (!pp.img[1]) tcu_invalidate(a, TCU_CRITIC_T);
+    return OIS_OK;
+  }
   polyak_kernel<<<eg(oa.total, 256), 256, 0, s>>>(io->actor_target, io->actor, oa.total, io->polyak);
   polyak_kernel<<<eg(oc.total, 256), 256, 0, s>>>(io->critic_target, io->critic, oc.total, io->polyak);
   OIS_CHECK_LAUNCH();
-  if (tc) {
-    tc_invalidate_weights(a);
-    tcu_invalidate(a, TCU_ACTOR);
-    tcu_invalidate(a, TCU_ACTOR_T);
-    tcu_invalidate(a, TCU_CRITIC_T);
-  }
   return OIS_OK;
 }

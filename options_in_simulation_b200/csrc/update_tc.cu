@@ -29,7 +29,7 @@ constexpr int kThreads = 192;
 constexpr int kStages = 3;
 constexpr int kHalfStage = 32768;
 constexpr int kStageBytes = 2 * kHalfStage;           // A (128 x 128 bf16) + B (<= 128 x 128 bf16)
-constexpr int kSmemBytes = kStages * kStageBytes + 128;
+constexpr int kSmemBytes = kStages * kStageBytes + 128 + 512;
 constexpr int kTmemCols = 128;
 constexpr int kMaxProblems = 8;
 
@@ -52,6 +52,8 @@ struct Problem {
   uint8_t* out_bf16;        // tile-blocked [M, N], RB = 128
   float* out_f32;
   int ld, m_valid, n_valid, transposed;
+  uint8_t* x_out;           // EPI_OUT: also bf16 into columns x_col.. of a tile-blocked [M, 16] buffer
+  int x_col;
   int tile_begin;
 };
 
@@ -60,12 +62,19 @@ struct Group {
   int count;
 };
 
-__host__ __device__ inline size_t chunk_off(int r, int c8, int C8, int rb) {
-  return ((size_t)((r / rb) * C8 + c8) * rb + (r % rb)) * 16;
-}
+__host__ __device__ inline size_t chunk_off(int r, int c8, int C8, int rb) { return tcu_chunk_off(r, c8, C8, rb); }
 
 __device__ __forceinline__ float bf16_lo(uint32_t w) { return __uint_as_float(w << 16); }
 __device__ __forceinline__ float bf16_hi(uint32_t w) { return __uint_as_float(w & 0xFFFF0000u); }
+
+// Diagnostics (not part of the public ABI): %globaltimer stamps of CTA 0, read by profiles/tcu_trace.py
+__device__ unsigned long long g_tcu_trace[16];
+__device__ __forceinline__ void tcu_stamp(int slot) {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  g_tcu_trace[slot] = t;
+}
+#define TCU_STAMP(cond, slot) do { if (cond) tcu_stamp(slot); } while (0)
 
 __global__ void __launch_bounds__(kThreads, 1)
 tc_gemm_kernel(const __grid_constant__ Group g) {
@@ -74,12 +83,15 @@ tc_gemm_kernel(const __grid_constant__ Group g) {
   uint64_t* empty = full + kStages;
   uint64_t* d_full = empty + kStages;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(d_full + 1);
+  float* s_bias = reinterpret_cast<float*>(smem + kStages * kStageBytes + 128);   // [128]
+  const bool tr = blockIdx.x == 0 && (threadIdx.x & 31) == 0;
+  TCU_STAMP(tr && threadIdx.x == 0, 0);
 
   int pi = 0;
 #pragma unroll 1
   for (int i = 1; i < g.count; ++i)
     if ((int)blockIdx.x >= g.p[i].tile_begin) pi = i;
-  const Problem& P = g.p[pi];
+  const Problem P = g.p[pi];   // by value: registers, immune to the memory clobbers of the inline-PTX wrappers
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int t = blockIdx.x - P.tile_begin;
   const int tile_n = P.tile_n;
@@ -100,8 +112,10 @@ tc_gemm_kernel(const __grid_constant__ Group g) {
   ptx::tc_fence_after();
   const uint32_t tmem = *tmem_slot;
   // programmatic dependent launch: the set-up above overlapped the predecessor's tail (ois_common.cuh states the rule)
+  TCU_STAMP(tr && threadIdx.x == 0, 1);
   pdl_wait();
   if (threadIdx.x == 0) pdl_trigger();
+  TCU_STAMP(tr && threadIdx.x == 0, 2);
 
   if (warp == 0) {
     // ===================================================== producer: one contiguous bulk copy per operand per K stage
@@ -135,6 +149,7 @@ tc_gemm_kernel(const __grid_constant__ Group g) {
       const int slot = s % kStages;
       ptx::mbar_wait(&full[slot], (s / kStages) & 1);
       ptx::tc_fence_after();
+      TCU_STAMP(tr && s < 4, 3 + s);
       if (leader) {
         const uint32_t sa = ptx::smem_u32(smem + slot * kStageBytes), sb = sa + kHalfStage;
         for (int kk = 0; kk < (k_stage >> 4); ++kk)
@@ -147,29 +162,56 @@ tc_gemm_kernel(const __grid_constant__ Group g) {
     }
   } else {
     // ===================================================== epilogue: one warp per TMEM lane quadrant
+    // (parameter fields are copied to registers once: the inline-PTX wrappers carry memory clobbers, which would
+    //  otherwise force a re-load of every P.field after each of them)
+    const int epi = P.epi, Ncols = P.N, ld = P.ld, m_valid = P.m_valid, n_valid = P.n_valid, transposed = P.transposed;
+    const int out_act = P.out_act, x_col = P.x_col;
+    const float* const bias = P.bias;
+    const uint8_t* const hsrc = P.h;
+    uint8_t* const out_bf16 = P.out_bf16;
+    uint8_t* const x_out = P.x_out;
+    float* const out_f32 = P.out_f32;
     const int quad = warp & 3;
     const int m = quad * 32 + lane;
     const int gm = tm * 128 + m;
     const int n0 = tn * tile_n;
     const uint32_t t_lane = tmem + ((uint32_t)(quad * 32) << 16);
+    // everything the epilogue needs from global memory is fetched while the MMAs run: the bias slice goes to shared
+    // memory, the saved activations of this thread's row (ELU') to registers
+    const int et = threadIdx.x - 64;
+    if (epi == EPI_HIDDEN || epi == EPI_OUT)
+      if (et < tile_n) s_bias[et] = (n0 + et < n_valid || epi == EPI_HIDDEN) ? bias[n0 + et] : 0.f;
+    uint4 hreg[16];
+    if (epi == EPI_DGRAD) {
+      const uint4* hp = reinterpret_cast<const uint4*>(hsrc + chunk_off(gm, n0 >> 3, Ncols >> 3, 128));
+#pragma unroll
+      for (int c = 0; c < 16; ++c) hreg[c] = (c * 8 < tile_n) ? hp[c * 128] : make_uint4(0, 0, 0, 0);
+    }
+    asm volatile("bar.sync 1, 128;" ::: "memory");      // the four epilogue warps only: s_bias is complete
     ptx::mbar_wait(d_full, 0);
     ptx::tc_fence_after();
-    for (int c0 = 0; c0 < tile_n; c0 += 16) {
+    TCU_STAMP(tr && warp == 2, 8);
+#pragma unroll
+    for (int c = 0; c < 8; ++c) {
+      const int c0 = c * 16;
+      if (c0 >= tile_n) break;
       uint32_t v[16];
       ptx::tmem_ld16(t_lane + c0, v);
       ptx::tmem_ld_wait();
       const int n = n0 + c0;
-      if (P.epi == EPI_HIDDEN || P.epi == EPI_DGRAD) {
+      if (epi == EPI_HIDDEN || epi == EPI_DGRAD) {
         float x[16];
-        if (P.epi == EPI_HIDDEN) {
+        if (epi == EPI_HIDDEN) {
 #pragma unroll
           for (int j = 0; j < 16; ++j) {
-            const float z = __uint_as_float(v[j]) + P.bias[n + j];
-            x[j] = z > 0.f ? z : expm1f(z);
+            // ELU: exp(z) - 1 with ONE MUFU.EX2 (ex2.approx.ftz; abs. error ~1e-7, far below the bf16 rounding that follows)
+            const float z = __uint_as_float(v[j]) + s_bias[c0 + j];
+            float ez;
+            asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(ez) : "f"(z * 1.4426950408889634f));
+            x[j] = z > 0.f ? z : ez - 1.0f;
           }
         } else {
-          const uint4* hp = reinterpret_cast<const uint4*>(P.h + chunk_off(gm, n >> 3, P.N >> 3, 128));
-          const uint4 h0 = hp[0], h1 = hp[128];   // the next column chunk is 128 rows * 16 B further
+          const uint4 h0 = hreg[2 * c], h1 = hreg[2 * c + 1];
           const uint32_t hw[8] = {h0.x, h0.y, h0.z, h0.w, h1.x, h1.y, h1.z, h1.w};
 #pragma unroll
           for (int j = 0; j < 8; ++j) {
@@ -178,39 +220,44 @@ tc_gemm_kernel(const __grid_constant__ Group g) {
             x[2 * j + 1] = __uint_as_float(v[2 * j + 1]) * (hb > 0.f ? 1.f : hb + 1.f);
           }
         }
-        uint4* op = reinterpret_cast<uint4*>(P.out_bf16 + chunk_off(gm, n >> 3, P.N >> 3, 128));
+        uint4* op = reinterpret_cast<uint4*>(out_bf16 + chunk_off(gm, n >> 3, Ncols >> 3, 128));
         op[0] = make_uint4(ptx::pack_bf16(x[0], x[1]), ptx::pack_bf16(x[2], x[3]), ptx::pack_bf16(x[4], x[5]), ptx::pack_bf16(x[6], x[7]));
         op[128] = make_uint4(ptx::pack_bf16(x[8], x[9]), ptx::pack_bf16(x[10], x[11]), ptx::pack_bf16(x[12], x[13]), ptx::pack_bf16(x[14], x[15]));
-      } else if (P.epi == EPI_OUT) {
-        if (gm < P.m_valid) {
+      } else if (epi == EPI_OUT) {
+        if (gm < m_valid) {
 #pragma unroll
           for (int j = 0; j < 16; ++j) {
-            if (n + j < P.n_valid) {
-              const float z = __uint_as_float(v[j]) + P.bias[n + j];
-              P.out_f32[(size_t)gm * P.ld + n + j] =
-                  P.out_act == OIS_ACT_SIGMOID ? 1.0f / (1.0f + expf(-z)) : P.out_act == OIS_ACT_TANH ? tanhf(z) : z;
+            if (n + j < n_valid) {
+              const float z = __uint_as_float(v[j]) + s_bias[c0 + j];
+              const float o = out_act == OIS_ACT_SIGMOID ? 1.0f / (1.0f + expf(-z)) : out_act == OIS_ACT_TANH ? tanhf(z) : z;
+              out_f32[(size_t)gm * ld + n + j] = o;
+              if (x_out) {
+                const int xc = x_col + n + j;
+                *reinterpret_cast<uint16_t*>(x_out + chunk_off(gm, xc >> 3, 2, 128) + (xc & 7) * 2) = tcu_bf16_bits(o);
+              }
             }
           }
         }
       } else {
-        if (gm < P.m_valid) {
-          if (P.transposed) {
+        if (gm < m_valid) {
+          if (transposed) {
 #pragma unroll
             for (int j = 0; j < 16; ++j)
-              if (n + j < P.n_valid) P.out_f32[(size_t)(n + j) * P.ld + gm] = __uint_as_float(v[j]);
-          } else if (n + 16 <= P.n_valid && (P.ld & 3) == 0) {
-            float4* o = reinterpret_cast<float4*>(P.out_f32 + (size_t)gm * P.ld + n);
+              if (n + j < n_valid) out_f32[(size_t)(n + j) * ld + gm] = __uint_as_float(v[j]);
+          } else if (n + 16 <= n_valid && (ld & 3) == 0) {
+            float4* o = reinterpret_cast<float4*>(out_f32 + (size_t)gm * ld + n);
 #pragma unroll
             for (int j = 0; j < 4; ++j)
               o[j] = make_float4(__uint_as_float(v[4 * j]), __uint_as_float(v[4 * j + 1]), __uint_as_float(v[4 * j + 2]), __uint_as_float(v[4 * j + 3]));
           } else {
 #pragma unroll
             for (int j = 0; j < 16; ++j)
-              if (n + j < P.n_valid) P.out_f32[(size_t)gm * P.ld + n + j] = __uint_as_float(v[j]);
+              if (n + j < n_valid) out_f32[(size_t)gm * ld + n + j] = __uint_as_float(v[j]);
           }
         }
       }
     }
+    TCU_STAMP(tr && warp == 2, 9);
   }
   ptx::tc_fence_before();
   __syncthreads();
@@ -248,6 +295,8 @@ pack_weights_kernel(const float* __restrict__ P, uint8_t* __restrict__ img, int 
 __global__ void __launch_bounds__(256)
 pack_rows_kernel(const float* __restrict__ s1, int ld1, int col1, int w1, const float* __restrict__ s2, int ld2, int w2,
                  const float* __restrict__ act_out, int act, uint8_t* __restrict__ dst, int B) {
+  pdl_wait();
+  if (threadIdx.x == 0) pdl_trigger();
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= B * 2) return;
   const int r = i >> 1, c8 = i & 1;
@@ -281,17 +330,27 @@ struct BiasGradArgs {
 };
 __global__ void __launch_bounds__(256)
 bias_grad_kernel(const __grid_constant__ BiasGradArgs a) {
+  pdl_wait();
+  if (threadIdx.x == 0) pdl_trigger();
   int w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const int lane = threadIdx.x & 31;
   int l = 0;
   while (l < 4 && w >= a.c8[l]) { w -= a.c8[l]; ++l; }
   if (l == 4) return;
   float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-  for (int r = lane; r < a.B; r += 32) {
-    const uint4 q = *reinterpret_cast<const uint4*>(a.d[l] + chunk_off(r, w, a.c8[l], 128));
-    const uint32_t ws[4] = {q.x, q.y, q.z, q.w};
+  for (int r0 = 0; r0 < a.B; r0 += 256) {      // eight independent 16-byte loads in flight per lane; fixed summation order
+    uint4 q[8];
 #pragma unroll
-    for (int j = 0; j < 4; ++j) { acc[2 * j] += bf16_lo(ws[j]); acc[2 * j + 1] += bf16_hi(ws[j]); }
+    for (int u = 0; u < 8; ++u) {
+      const int r = r0 + u * 32 + lane;
+      q[u] = r < a.B ? *reinterpret_cast<const uint4*>(a.d[l] + chunk_off(r, w, a.c8[l], 128)) : make_uint4(0, 0, 0, 0);
+    }
+#pragma unroll
+    for (int u = 0; u < 8; ++u) {
+      const uint32_t ws[4] = {q[u].x, q[u].y, q[u].z, q[u].w};
+#pragma unroll
+      for (int j = 0; j < 4; ++j) { acc[2 * j] += bf16_lo(ws[j]); acc[2 * j + 1] += bf16_hi(ws[j]); }
+    }
   }
 #pragma unroll
   for (int j = 0; j < 8; ++j)
@@ -336,7 +395,7 @@ static Problem base_problem() {
 
 // layer l of y = mlp(x): A = the layer input (rows = batch, contraction over its columns), B = W_l (rows = n_out)
 static Problem fwd_problem(const OisMlpShape& sh, const float* P32, const uint8_t* img, int l, const uint8_t* in,
-                           uint8_t* out_bf16, float* y, int B) {
+                           uint8_t* out_bf16, float* y, uint8_t* x_out, int x_col, int B) {
   const MlpOffsets o = mlp_offsets(sh);
   const int kin[4] = {16, 512, 512, 128}, nout[4] = {512, 512, 128, 16};
   const size_t wo[4] = {kImgW1, kImgW2, kImgW3, kImgW4};
@@ -346,7 +405,7 @@ static Problem fwd_problem(const OisMlpShape& sh, const float* P32, const uint8_
   p.M = B; p.N = nout[l]; p.K = kin[l]; p.tile_n = l == 3 ? 16 : 128;
   p.bias = P32 + o.b[l];
   if (l < 3) { p.epi = EPI_HIDDEN; p.out_bf16 = out_bf16; }
-  else { p.epi = EPI_OUT; p.out_f32 = y; p.ld = sh.out_dim; p.n_valid = sh.out_dim; p.m_valid = B; p.out_act = sh.out_act; }
+  else { p.epi = EPI_OUT; p.out_f32 = y; p.ld = sh.out_dim; p.n_valid = sh.out_dim; p.m_valid = B; p.out_act = sh.out_act; p.x_out = x_out; p.x_col = x_col; }
   return p;
 }
 
@@ -354,14 +413,14 @@ struct NetActs { uint8_t *x, *h0, *h1, *h2; };
 
 // up to two independent networks advance layer by layer in the same launches
 static int forward(int count, const OisMlpShape* const* sh, const float* const* P32, const uint8_t* const* img,
-                   const NetActs* acts, float* const* y, int B, cudaStream_t s) {
+                   const NetActs* acts, float* const* y, uint8_t* const* x_out, int x_col, int B, cudaStream_t s) {
   for (int l = 0; l < 4; ++l) {
     Group g;
     g.count = count;
     for (int i = 0; i < count; ++i) {
       const uint8_t* in = l == 0 ? acts[i].x : l == 1 ? acts[i].h0 : l == 2 ? acts[i].h1 : acts[i].h2;
       uint8_t* out = l == 0 ? acts[i].h0 : l == 1 ? acts[i].h1 : acts[i].h2;
-      g.p[i] = fwd_problem(*sh[i], P32[i], img[i], l, in, out, y[i], B);
+      g.p[i] = fwd_problem(*sh[i], P32[i], img[i], l, in, out, y[i], x_out ? x_out[i] : nullptr, x_col, B);
     }
     if (int e = launch_group(g, s)) return e;
   }
@@ -433,8 +492,7 @@ static int backward(const OisMlpShape& sh, const uint8_t* img, float* G, const N
     for (int l = 0; l < 4; ++l) ba.out[l] = G + o.b[l];
     ba.B = B;
     const int warps = 64 + 64 + 16 + 2;
-    bias_grad_kernel<<<(warps * 32 + 255) / 256, 256, 0, s>>>(ba);
-    OIS_CHECK_LAUNCH();
+    OIS_CHECK_CUDA(launch_pdl(bias_grad_kernel, (warps * 32 + 255) / 256, 256, 0, s, ba));
   }
   return OIS_OK;
 }
@@ -481,6 +539,9 @@ int tcu_init(OisAgent* a) {
   uint8_t* p = st->slab;
   for (int i = 0; i < 4; ++i) { st->img[i] = p; p += kImgBytes; }
   for (NetActs& n : st->acts) { n.x = p; p += thin; n.h0 = p; p += wide; n.h1 = p; p += wide; n.h2 = p; p += mid; }
+  // the actor reads the first in_dim columns of the CRITIC's input buffer (its image has zero weights beyond them) and
+  // its action is written into the following columns of the same buffer: one buffer, no concatenation kernel
+  st->acts[TCU_ACTS_ACTOR].x = st->acts[TCU_ACTS_CRITIC].x;
   st->dz = p; p += thin; st->d2 = p; p += mid; st->d1 = p; p += wide; st->d0 = p; p += wide;
   a->tcu = st;
   return OIS_OK;
@@ -516,18 +577,27 @@ int tcu_image(OisAgent* a, int net, const float* P32, cudaStream_t s) {
   return OIS_OK;
 }
 
+uint8_t* tcu_image_if_valid(OisAgent* a, int net, const float* P32) {
+  State* st = (State*)a->tcu;
+  return (st && st->valid[net] && st->packed_from[net] == P32) ? st->img[net] : nullptr;
+}
+
+uint8_t* tcu_x_buffer(OisAgent* a, int which) {
+  State* st = (State*)a->tcu;
+  return !st ? nullptr : which == TCU_DZ ? st->dz : st->acts[which].x;
+}
+
 int tcu_pack_x(OisAgent* a, int dst, const float* s1, int ld1, int col1, int w1, const float* s2, int ld2, int w2,
                const float* act_out, int act, cudaStream_t s) {
   State* st = (State*)a->tcu;
   OIS_CHECK_ARG(st && w1 + w2 <= 16, "bad pack request");
   uint8_t* out = dst == TCU_DZ ? st->dz : st->acts[dst].x;
-  pack_rows_kernel<<<(a->batch * 2 + 255) / 256, 256, 0, s>>>(s1, ld1, col1, w1, s2, ld2, w2, act_out, act, out, a->batch);
-  OIS_CHECK_LAUNCH();
+  OIS_CHECK_CUDA(launch_pdl(pack_rows_kernel, (a->batch * 2 + 255) / 256, 256, 0, s, s1, ld1, col1, w1, s2, ld2, w2, act_out, act, out, a->batch));
   return OIS_OK;
 }
 
 int tcu_forward(OisAgent* a, int count, const int* nets, const float* const* P32, const int* acts, float* const* y,
-                cudaStream_t s) {
+                uint8_t* const* x_out, int x_col, cudaStream_t s) {
   State* st = (State*)a->tcu;
   OIS_CHECK_ARG(st && count >= 1 && count <= 2, "bad forward request");
   const OisMlpShape* sh[2];
@@ -539,7 +609,7 @@ int tcu_forward(OisAgent* a, int count, const int* nets, const float* const* P32
     img[i] = st->img[nets[i]];
     na[i] = st->acts[acts[i]];
   }
-  return forward(count, sh, P32, img, na, y, a->batch, s);
+  return forward(count, sh, P32, img, na, y, x_out, x_col, a->batch, s);
 }
 
 int tcu_backward(OisAgent* a, int net, float* G, int acts, float* dx, cudaStream_t s) {
@@ -551,7 +621,8 @@ int tcu_backward(OisAgent* a, int net, float* G, int acts, float* dx, cudaStream
 // diagnostics hook for tests (deliberately not declared in include/ois_b200.h): C = op(A) op(B) on the tensor cores
 // from tile-blocked bf16 operands the caller prepared; mode bits: 1 = A contracts over its rows, 2 = B likewise
 int tcu_debug_gemm(const void* a, int a_c8, int a_rb, const void* b, int b_c8, int b_rb, int M, int N, int K, int tile_n,
-                   int mode, float* out, int ld, int transposed, cudaStream_t s) {
+                   int mode, float* out, int ld, int transposed, cudaStream_t s, int epi = EPI_F32, const float* bias = nullptr,
+                   const void* h = nullptr, void* out_bf16 = nullptr) {
   static bool attr = false;
   if (!attr) {
     OIS_CHECK_CUDA(cudaFuncSetAttribute(tc_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
@@ -563,12 +634,25 @@ int tcu_debug_gemm(const void* a, int a_c8, int a_rb, const void* b, int b_c8, i
   p.a = (const uint8_t*)a; p.a_c8 = a_c8; p.a_rb = a_rb; p.a_mn = mode & 1;
   p.b = (const uint8_t*)b; p.b_c8 = b_c8; p.b_rb = b_rb; p.b_mn = (mode >> 1) & 1;
   p.M = M; p.N = N; p.K = K; p.tile_n = tile_n;
-  p.epi = EPI_F32; p.out_f32 = out; p.ld = ld; p.transposed = transposed; p.m_valid = M; p.n_valid = N;
+  p.epi = epi; p.out_f32 = out; p.ld = ld; p.transposed = transposed; p.m_valid = M; p.n_valid = N;
+  p.bias = bias; p.h = (const uint8_t*)h; p.out_bf16 = (uint8_t*)out_bf16;
   g.p[0] = p;
   return launch_group(g, s);
 }
 
 }  // namespace ois
+
+extern "C" int ois_debug_tcu_trace(unsigned long long* out_host, int n) {
+  if (n > 16) n = 16;
+  return cudaMemcpyFromSymbol(out_host, ois::tcu::g_tcu_trace, sizeof(unsigned long long) * n) == cudaSuccess ? 0 : -2;
+}
+
+extern "C" int ois_debug_tc_gemm_epi(const void* a, int a_c8, int a_rb, const void* b, int b_c8, int b_rb, int M, int N, int K,
+                                     int tile_n, int mode, int epi, const float* bias, const void* h, void* out_bf16,
+                                     void* stream) {
+  return ois::tcu_debug_gemm(a, a_c8, a_rb, b, b_c8, b_rb, M, N, K, tile_n, mode, nullptr, N, 0, (cudaStream_t)stream, epi, bias, h,
+                             out_bf16);
+}
 
 extern "C" int ois_debug_tc_gemm(const void* a, int a_c8, int a_rb, const void* b, int b_c8, int b_rb, int M, int N, int K,
                                  int tile_n, int mode, float* out, int ld, int transposed, void* stream) {

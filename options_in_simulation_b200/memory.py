@@ -107,6 +107,14 @@ class Memory:
         ``torch.randperm(len)[:B]`` produced) instead of drawing their own."""
         self._supplied_indexes.extend(torch.as_tensor(i, dtype=torch.int64) for i in index_sets)
 
+    def draw_indices(self, idx: torch.Tensor) -> None:
+        """Device sampler into a caller-owned index buffer (the CUDA-graph update keeps one fixed buffer)."""
+        L.check(L.lib().ois_replay_sample_indices(L.ptr(idx), idx.numel(), len(self), self._seed, self._draws,
+                                                  L.current_stream()))
+        self._draws += 1
+        self.kernel_launches += 1
+        self.sampling_indexes = idx
+
     def sample(self, names, batch_size: int, mini_batches: int = 1, sequence_length: int = 1):
         size = len(self)
         if self._supplied_indexes:

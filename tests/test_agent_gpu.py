@@ -27,7 +27,7 @@ class _Box:
         self.high = np.full(n, high, np.float32)
 
 
-def build_agent(meta, *, mixed_precision=False, n_envs=None, sampler="host", rows=None):
+def build_agent(meta, *, mixed_precision=False, n_envs=None, sampler="host", rows=None, **extra_cfg):
     import torch
 
     import options_in_simulation_b200 as ois
@@ -49,6 +49,7 @@ def build_agent(meta, *, mixed_precision=False, n_envs=None, sampler="host", row
            "exploration": {"noise": A.OrnsteinUhlenbeckNoise(0.15, 0.1, meta["base_scale"], device="cuda:0"),
                            "final_scale": 1e-4, "timesteps": meta["T_e"]},
            "experiment": {"write_interval": 0, "checkpoint_interval": 0}, "track_stats_interval": 1}
+    cfg.update(extra_cfg)
     agent = A.DDPG(models=models, memory=memory, cfg=cfg, observation_space=obs_space, action_space=act_space,
                    device="cuda:0")
     agent.init({"timesteps": 1000})

@@ -156,3 +156,57 @@ def test_bf16_update_is_deterministic_and_learns():
     assert torch.equal(finals[0][0], finals[1][0]) and torch.equal(finals[0][1], finals[1][1])
     assert losses[0] == losses[1]
     assert np.mean(losses[0][-5:]) < 0.7 * np.mean(losses[0][:5]), losses[0]
+
+
+@pytest.mark.parametrize("mixed_precision", [True, False])
+def test_graph_update_equals_eager_update(mixed_precision):
+    """cfg graph_update=True replays the gather + three phases as one CUDA graph: same kernels, same order, same
+    device-side sampler draws -> bit-identical weights, optimizer state and scaler statistics."""
+    import torch
+
+    from test_agent_gpu import build_agent
+
+    d, meta = load("agent_kamma_4d.npz")
+    agents = []
+    for graph in (False, True):
+        agent, mem = build_agent(meta, mixed_precision=mixed_precision, sampler="device", graph_update=graph)
+        _fill(mem, d, meta)
+        for i in range(6):
+            agent._update(100 + i, 1000)
+            if i == 2:      # inference between updates must see the updated weights (image rebuilt after a replay)
+                states = torch.as_tensor(d["r0_states"]).cuda()
+                agent.supply_draws(normals=np.zeros((states.shape[0], meta["act_dim"]), np.float32))
+                agent._probe = agent.act(states, 500, 1000)[0].clone()
+        torch.cuda.synchronize()
+        agents.append(agent)
+    e, g = agents
+    assert g._graph is not None and e._graph is None
+    for name in ("policy", "target_policy", "critic", "target_critic"):
+        assert torch.equal(getattr(e, name).flat, getattr(g, name).flat), name
+    assert torch.equal(e.policy_optimizer.m, g.policy_optimizer.m) and torch.equal(e.critic_optimizer.v, g.critic_optimizer.v)
+    assert e.policy_optimizer.step == g.policy_optimizer.step == 6
+    assert torch.equal(e._state_preprocessor.running_mean, g._state_preprocessor.running_mean)
+    assert float(e._state_preprocessor.current_count) == float(g._state_preprocessor.current_count)
+    assert torch.equal(e._probe, g._probe)
+    assert torch.equal(e._stats, g._stats)
+
+
+def test_incremental_weight_images_equal_full_repack():
+    """Adam / polyak keep the bf16 tensor-core weight images current element by element; forcing a full repack from the
+    fp32 masters before every update must give bit-identical results."""
+    import torch
+
+    from test_agent_gpu import build_agent
+
+    d, meta = load("agent_kamma_4d.npz")
+    out = []
+    for repack in (False, True):
+        agent, mem = build_agent(meta, mixed_precision=True, sampler="device")
+        _fill(mem, d, meta)
+        for i in range(5):
+            if repack:
+                agent._weights_changed()
+            agent._update(100 + i, 1000)
+        out.append(agent)
+    for name in ("policy", "target_policy", "critic", "target_critic"):
+        assert torch.equal(getattr(out[0], name).flat, getattr(out[1], name).flat), name

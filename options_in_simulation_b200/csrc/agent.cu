@@ -559,6 +559,7 @@ extern "C" int ois_ddpg_update_phase(OisAgent* a, const OisScaler* scaler, const
   // pieces (fp64 scaler statistics, TD target, losses, Adam, polyak — the same arithmetic as the exact fp32 path) are
   // fused around them; every launch is a programmatic dependent launch, so prologues overlap the predecessor's tail
   const bool tc = a->precision == OIS_PRECISION_BF16;
+  OIS_CHECK_ARG(!tc || a->tcu, "the bf16 tcgen05 update needs batch_size to be a multiple of 128 (use OIS_PRECISION_FP32 otherwise)");
   if (phase == 0) {
     OIS_CHECK_ARG(io->states && io->actions && io->rewards && io->next_states && io->terminated && io->truncated,
                   "null batch tensor");

@@ -516,7 +516,7 @@ int tcu_init(OisAgent* a) {
     OIS_CHECK_ARG(sh->h0 == 512 && sh->h1 == 512 && sh->h2 == 128, "the tcgen05 update is built for 512-512-128 hidden layers");
     OIS_CHECK_ARG(sh->in_dim <= 16 && sh->out_dim <= 16, "in_dim and out_dim must be <= 16");
   }
-  OIS_CHECK_ARG(a->batch % 128 == 0, "the tcgen05 update needs batch_size to be a multiple of 128");
+  if (a->batch % 128 != 0) return OIS_OK;   // inference-only use stays possible; ois_ddpg_update_phase reports the reason
   State* st = new (std::nothrow) State();
   OIS_CHECK_ARG(st, "out of host memory");
   const size_t B = (size_t)a->batch;

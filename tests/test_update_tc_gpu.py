@@ -210,3 +210,21 @@ def test_incremental_weight_images_equal_full_repack():
         out.append(agent)
     for name in ("policy", "target_policy", "critic", "target_critic"):
         assert torch.equal(getattr(out[0], name).flat, getattr(out[1], name).flat), name
+
+
+def test_bf16_agent_with_other_batch_sizes_still_acts_and_update_says_why():
+    """The tensor-core update needs batch_size % 128 == 0; inference must not depend on it, and _update must fail
+    loudly (no silent fp32 fallback) when it cannot run."""
+    import torch
+
+    from options_in_simulation_b200 import _lib as L
+    from test_agent_gpu import build_agent
+
+    d, meta = load("agent_kamma_4d.npz")
+    meta = dict(meta, batch=64)
+    agent, mem = build_agent(meta, mixed_precision=True)
+    _fill(mem, d, meta)
+    a = agent.act(torch.zeros(300, meta["obs_dim"], device="cuda"), 500, 1000)[0]
+    assert a.shape == (300, meta["act_dim"]) and torch.isfinite(a).all()
+    with pytest.raises(L.OisError, match="multiple of 128"):
+        agent._update(100, 1000)

@@ -43,6 +43,11 @@ UNIT = "env-steps/s"
 ENV_BYTES = {"KAMMA_medium": 265, "KA_DDPG_2D": 253, "KA_DDPG_1D": 249}   # SURVEY.md §8(d), per env-step
 REPLAY_BYTES = 70
 ACTOR_FLOP = {4: 662528, 2: 662016, 1: 661760}                             # 2 * MACs, SURVEY.md §8(d)
+UPDATE_FLOP = 6645248 * 512                                                # SURVEY.md §8 row A11, B = 512
+# dram__bytes_read.sum + dram__bytes_write.sum per launch, from the committed `ncu --set full` captures
+# (profiles/r01b_ncu_full_summary.txt; kamma_4d): {(kernel, envs): bytes}
+NCU_TRAFFIC = {("env", 4096): 652032, ("actor", 4096): 924672, ("env", 1048576): 159505664 + 233138688,
+               ("actor", 1048576): 42704896 + 218112}
 WORKLOADS = {
     "kamma_4d": dict(variant="KAMMA_medium", act_dim=4, envs=4096, ou=0.05, T_e=5e5, memory_total=1_000_000,
                      name="KAMMA-4d nofifo random RLIL (BASELINE.json configs[2])"),
@@ -306,6 +311,26 @@ def update_timed(world, iters=30):
     return a.elapsed_time(b) / iters
 
 
+def train_timed(world, flush, steps=30):
+    """One policy step followed by two updates (the reference trainer's cadence), device-timed."""
+    torch = world.torch
+    for _ in range(3):
+        world.step()
+        world.agent._update(world.t, world.T)
+        world.agent._update(world.t, world.T)
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
+    torch.cuda.synchronize()
+    for a, b in ev:
+        flush.zero_()
+        a.record()
+        world.step()
+        world.agent._update(world.t, world.T)
+        world.agent._update(world.t, world.T)
+        b.record()
+    torch.cuda.synchronize()
+    return sum(a.elapsed_time(b) for a, b in ev) / steps
+
+
 def main():
     args = parse()
     wl = WORKLOADS[args.workload]
@@ -379,10 +404,11 @@ def main():
         act_ms, env_ms = kernel_split(world, min(args.steps, 100), flush)
         env_bytes = (ENV_BYTES[wl["variant"]] + REPLAY_BYTES) * n
         act_flop = ACTOR_FLOP[wl["act_dim"]] * n
+        tr = (lambda k: NCU_TRAFFIC.get((k, n)) if args.workload == "kamma_4d" else None)
         env_roof = {"kernel": "env_step_kernel", "bound": "hbm", "achieved": env_bytes / (env_ms * 1e-3) / 1e9,
-                    "peak": hbm_peak, "unit": "GB/s", "traffic": None, "ms": env_ms}
+                    "peak": hbm_peak, "unit": "GB/s", "traffic": tr("env"), "ms": env_ms}
         act_roof = {"kernel": "actor MLP (ois_agent_act)", "bound": "tensor", "achieved": act_flop / (act_ms * 1e-3) / 1e12,
-                    "peak": tc_peak, "unit": "TFLOP/s", "traffic": None, "ms": act_ms}
+                    "peak": tc_peak, "unit": "TFLOP/s", "traffic": tr("actor"), "ms": act_ms}
         for r in (env_roof, act_roof):
             r["frac"] = r["achieved"] / r["peak"]
             r["peak_source"] = peak_src
@@ -390,8 +416,13 @@ def main():
         out["roofline"] = dom
         out["roofline_other"] = other
         if not args.no_extras and world_size == 1:
-            out["update"] = {"ms_per_update": update_timed(world), "batch": 512,
-                             "note": "DDPG._update, reference cadence = 2 per env step (base_KA_DDPG.py:265,283); not in the metric"}
+            upd_ms = update_timed(world)
+            train_ms = train_timed(world, flush)
+            out["update"] = {"ms_per_update": upd_ms, "batch": 512, "tflops": UPDATE_FLOP / (upd_ms * 1e-3) / 1e12,
+                             "path": "bf16 tcgen05 grouped GEMMs, one CUDA graph per update" if args.precision == "bf16" else "fp32 SIMT",
+                             "train_ms_per_step": train_ms, "train_env_steps_per_s": n * 1e3 / train_ms,
+                             "note": "DDPG._update; train_* = one policy step + 2 updates, the reference cadence "
+                                     "(base_KA_DDPG.py:265,283); not in the metric"}
             scale = []
             del world
             torch.cuda.empty_cache()
@@ -402,6 +433,7 @@ def main():
                     w.step()
                 m, _ = device_timed(w, 20, 3, None)
                 scale.append({"envs": big, "value": big * 1e3 / m, "ms_per_step": m, "act_ms": a_ms, "env_ms": e_ms,
+                              "env_traffic": NCU_TRAFFIC.get(("env", big)), "act_traffic": NCU_TRAFFIC.get(("actor", big)),
                               "env_hbm_frac": (ENV_BYTES[wl["variant"]] + REPLAY_BYTES) * big / (e_ms * 1e-3) / 1e9 / hbm_peak,
                               "act_tensor_frac": ACTOR_FLOP[wl["act_dim"]] * big / (a_ms * 1e-3) / 1e12 / tc_peak,
                               "l2": "state exceeds L2" if big >= 1048576 else "L2-resident"})

@@ -297,6 +297,57 @@ def e2e_timed(world, steps, warmup):
     return a.elapsed_time(b) / steps, n * 6 * 4, n * (6 * 4 + 4 + 1)
 
 
+def e2e_graph_timed(world, steps, warmup):
+    """The same host-in-the-loop step through rollout.RolloutGraph: ONE graph launch per step holding the H2D copy of
+    the observations, act, env step (+ replay append), the step-control advance and ONE packed D2H copy of
+    (obs | rew | reset); the host synchronises and hands the new observations back every step."""
+    from options_in_simulation_b200.rollout import RolloutGraph
+
+    torch = world.torch
+    n = world.n
+    g = RolloutGraph(world.env, world.agent, world.t, world.T, host_io=True)
+    g.h_states.copy_(world.obs)
+
+    def one():
+        obs, rew, term = g.step()          # synchronised: results are in pinned host memory
+        g.h_states.copy_(obs)              # the host consumes them: next step's input (host memcpy, 96 KB at N = 4096)
+
+    for _ in range(warmup + 2):            # +2: the eager warm-up step and the capture
+        one()
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize()
+    a.record()
+    for _ in range(steps):
+        one()
+    b.record()
+    torch.cuda.synchronize()
+    world.t = g.timestep
+    world.obs = world.task.obs_clipped
+    return a.elapsed_time(b) / steps, n * 6 * 4, n * 29
+
+
+def graph_device_timed(world, steps, warmup, flush):
+    """Device-resident loop through rollout.RolloutGraph (no host buffers): events around every replay."""
+    from options_in_simulation_b200.rollout import RolloutGraph
+
+    torch = world.torch
+    g = RolloutGraph(world.env, world.agent, world.t, world.T, host_io=False)
+    for _ in range(warmup + 2):
+        g.step()
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
+    torch.cuda.synchronize()
+    for a, b in ev:
+        if flush is not None:
+            flush.zero_()
+        a.record()
+        g.step()
+        b.record()
+    torch.cuda.synchronize()
+    world.t = g.timestep
+    world.obs = world.task.obs_clipped
+    return sum(a.elapsed_time(b) for a, b in ev) / steps
+
+
 def update_timed(world, iters=30):
     torch = world.torch
     for _ in range(3):
@@ -377,12 +428,16 @@ def main():
     ms, launches = device_timed(world, args.steps, args.warmup, flush)
     barrier()
     clocks = sampler.stop() if rank == 0 else None
-    e2e_ms, h2d, d2h = e2e_timed(world, min(args.steps, 200), 5)
+    e2e_eager_ms, _, _ = e2e_timed(world, min(args.steps, 200), 5)
+    barrier()
+    e2e_ms, h2d, d2h = e2e_graph_timed(world, min(args.steps, 200), 5)
+    barrier()
+    graph_ms = graph_device_timed(world, min(args.steps, 200), 5, flush)
     barrier()
     if world_size > 1:
-        t = torch.tensor([ms, e2e_ms], device=device, dtype=torch.float64)
+        t = torch.tensor([ms, e2e_ms, e2e_eager_ms, graph_ms], device=device, dtype=torch.float64)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        ms, e2e_ms = t.tolist()
+        ms, e2e_ms, e2e_eager_ms, graph_ms = t.tolist()
     value = world_size * n * 1e3 / ms
     e2e_value = world_size * n * 1e3 / e2e_ms
 
@@ -396,7 +451,14 @@ def main():
                    "l2": "flushed between timed steps (256 MiB memset outside the event brackets)",
                    "parallelism": f"env/replay shards x{world_size}, no data-path collective"},
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                "ms_per_step": e2e_ms},
+                "ms_per_step": e2e_ms,
+                "path": "rollout.RolloutGraph(host_io=True): one CUDA-graph launch per step (H2D obs, act, env step + "
+                        "replay append, step-control advance, one packed D2H of obs|rew|reset), host sync every step",
+                "call_by_call_ms_per_step": e2e_eager_ms,
+                "call_by_call_value": world_size * n * 1e3 / e2e_eager_ms},
+        "graph_replay": {"ms_per_step": graph_ms, "value": world_size * n * 1e3 / graph_ms,
+                         "note": "the device-resident step replayed through rollout.RolloutGraph (3 kernels per replay); "
+                                 "`value` itself is the call-by-call path"},
         "gpu_launches": launches, "clocks": clocks,
     }
 

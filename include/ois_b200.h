@@ -32,7 +32,7 @@ extern "C" {
 #define OIS_ERR_CUDA (-2)
 #define OIS_ERR_UNSUPPORTED (-3)
 
-#define OIS_ABI_VERSION 1
+#define OIS_ABI_VERSION 2
 
 /* ------------------------------------------------------------------------------------------------
  * Environment: TorqueDistributionTask (src/my_envs/KAMMA_medium.py and its variants)
@@ -82,6 +82,27 @@ typedef struct OisEnvState {
   int64_t* episode_count;/* [N] */
 } OisEnvState;
 
+/* Device-resident per-step scalars, for CUDA-graph replay of the rollout step (the graph's kernel arguments are frozen
+ * at capture, so what changes from one policy step to the next lives here instead).  When OisEnvIO.ctl / OisActIO.ctl is
+ * non-NULL the kernels take these values in place of the like-named by-value fields; ois_step_ctl_advance moves the
+ * block to the next step with ONE single-thread launch at the end of the captured step.  The host initialises it with
+ * a plain host->device copy of this struct. */
+typedef struct OisStepCtl {
+  int64_t step;                /* steps taken since the host initialised the block */
+  uint64_t env_philox_offset;  /* OisEnvIO.philox_offset of this step */
+  uint64_t act_philox_offset;  /* OisActIO.philox_offset of this step */
+  int64_t replay_row;          /* memory_index: the ring slot the fused append writes (ddpg.py:313 -> Memory.add_samples) */
+  int64_t replay_rows;         /* memory_size */
+  int32_t flag_slot;           /* OisEnvIO.flag_slot of this step */
+  float noise_scale;           /* OisActIO.noise_scale of this step (ddpg.py:247-251) */
+  double timestep;             /* trainer timestep of this step */
+  double expl_timesteps, expl_initial_scale, expl_final_scale;   /* ddpg.py:105-107 */
+} OisStepCtl;
+
+/* ctl := the next policy step (offsets + 1, replay_row + 1 mod replay_rows, flag_slot + 1 mod 3, timestep + 1 and the
+ * decayed noise scale of ddpg.py:247-251 evaluated in double as the host path does). */
+int ois_step_ctl_advance(OisStepCtl* ctl, void* stream);
+
 #define OIS_EP_STATS_LEN 24   /* see ois_env_step */
 #define OIS_COMP0_LEN 32
 
@@ -119,6 +140,8 @@ typedef struct OisEnvIO {
                                    (clipActions, rl_task.py:100); <= 0: no clamp */
   float* obs_clipped;           /* [N,6] nullable: clamp(obs, +-clip_obs) — what the env wrapper hands to the agent;
                                    `obs` itself stays the raw obs_buf */
+  const OisStepCtl* ctl;        /* nullable; when set: philox_offset and flag_slot come from it, and the replay_* pointers
+                                   are the BASE of the (memory_size, N, dim) tensors, row ctl->replay_row is written */
 } OisEnvIO;
 
 /* One policy step for all envs: pre_physics_step + decimation physics sub-steps + post_physics_step
@@ -200,6 +223,7 @@ typedef struct OisActIO {
   float noise_scale;         /* decayed scale of ddpg.py:247-251, <0: timestep > exploration timesteps (no noise added) */
   float clip_low, clip_high; /* action space bounds (ddpg.py:255) */
   float* noise_stats;        /* [3] max, min, sum of the applied noises (ddpg.py:258-260), nullable */
+  const OisStepCtl* ctl;     /* nullable; when set: philox_offset and noise_scale come from it */
 } OisActIO;
 
 typedef struct OisAgent OisAgent;   /* opaque: workspaces, bf16 weight copies, TMA descriptors, graphs */
@@ -210,6 +234,11 @@ int ois_agent_destroy(OisAgent* agent);
 /* The caller changed parameter buffers behind the handle's back (load_state_dict, checkpoint load):
  * drop cached bf16 weight images.  ois_ddpg_update_phase invalidates by itself. */
 int ois_agent_invalidate(OisAgent* agent);
+
+/* Bring the handle's cached bf16 image of the actor weights up to date with `actor_params` (a no-op when nothing
+ * changed, and for fp32 handles).  ois_agent_act does this by itself; a captured CUDA graph of the rollout step cannot,
+ * so its owner calls this before each replay (DDPG._update changes the weights between replays). */
+int ois_agent_sync_weights(OisAgent* agent, const float* actor_params, void* stream);
 
 /* DDPG.act (ddpg.py:215-268): scaler -> actor MLP -> OU noise -> clamp, N rows. */
 int ois_agent_act(OisAgent* agent, const float* actor_params, const OisScaler* scaler, const OisActIO* io,

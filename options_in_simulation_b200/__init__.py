@@ -22,4 +22,7 @@ def __getattr__(name):   # lazy: importing the package must not need torch.cuda
     if name in ("SequentialTrainer",):
         from . import trainer
         return getattr(trainer, name)
+    if name in ("RolloutGraph",):
+        from . import rollout
+        return getattr(rollout, name)
     raise AttributeError(name)

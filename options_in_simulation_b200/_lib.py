@@ -52,8 +52,15 @@ class EnvIO(C.Structure):
         ("guiding", _p), ("ep_stats", _p), ("comp0", _p), ("any_reset_flags", _p), ("flag_slot", _i32),
         ("replay_states", _p), ("replay_actions", _p), ("replay_rewards", _p), ("replay_next_states", _p),
         ("replay_terminated", _p), ("replay_truncated", _p), ("relabel", _i32), ("clip_obs", _f),
-        ("clip_actions", _f), ("obs_clipped", _p),
+        ("clip_actions", _f), ("obs_clipped", _p), ("ctl", _p),
     ]
+
+
+class StepCtl(C.Structure):
+    """OisStepCtl: per-step scalars kept on the device for CUDA-graph replay of the rollout step."""
+    _fields_ = [("step", _i64), ("env_philox_offset", _u64), ("act_philox_offset", _u64), ("replay_row", _i64),
+                ("replay_rows", _i64), ("flag_slot", _i32), ("noise_scale", _f), ("timestep", C.c_double),
+                ("expl_timesteps", C.c_double), ("expl_initial_scale", C.c_double), ("expl_final_scale", C.c_double)]
 
 
 class MlpShape(C.Structure):
@@ -69,7 +76,7 @@ class ActIO(C.Structure):
         ("states", _p), ("actions", _p), ("ou_state", _p), ("normals", _p), ("uniforms", _p),
         ("philox_seed", _u64), ("philox_offset", _u64), ("random_phase", _i32),
         ("theta", _f), ("sigma", _f), ("base_scale", _f), ("noise_scale", _f), ("clip_low", _f), ("clip_high", _f),
-        ("noise_stats", _p),
+        ("noise_stats", _p), ("ctl", _p),
     ]
 
 
@@ -95,9 +102,11 @@ SYMBOLS = {
     "ois_agent_destroy": (C.c_int, [_p]),
     "ois_agent_invalidate": (C.c_int, [_p]),
     "ois_agent_act": (C.c_int, [_p, _p, _PP(Scaler), _PP(ActIO), _i64, _p]),
+    "ois_agent_sync_weights": (C.c_int, [_p, _p, _p]),
     "ois_scaler_forward": (C.c_int, [_PP(Scaler), _p, _p, _i64, _i32, _i32, _p]),
     "ois_mlp_forward": (C.c_int, [_p, _PP(MlpShape), _p, _p, _p, _i64, _p]),
     "ois_ddpg_update_phase": (C.c_int, [_p, _PP(Scaler), _PP(UpdateIO), _i32, _f, _p]),
+    "ois_step_ctl_advance": (C.c_int, [_p, _p]),
     "ois_last_error_string": (C.c_char_p, []),
     "ois_abi_version": (C.c_int, []),
     "ois_build_info": (C.c_char_p, []),
@@ -133,7 +142,7 @@ def lib() -> C.CDLL:
             fn = getattr(handle, name)    # AttributeError if the symbol is not exported
             fn.restype = res
             fn.argtypes = args
-        if handle.ois_abi_version() != 1:
+        if handle.ois_abi_version() != 2:
             raise OisError("libois_b200.so ABI version mismatch")
         _lib = handle
     return _lib

@@ -339,13 +339,13 @@ explore_kernel(const __grid_constant__ OisActIO io, int64_t n, int A) {
     if (io.random_phase) {   // Uniform(low, high).sample(): rand * (high - low) + low
       float u;
       if (io.uniforms) u = io.uniforms[i];
-      else { const uint4 r = Philox(io.philox_seed)((uint64_t)(i >> 2), io.philox_offset * 2 + 1); u = u01(((const uint32_t*)&r)[i & 3]); }
+      else { const uint4 r = Philox(io.philox_seed)((uint64_t)(i >> 2), act_philox_offset(io) * 2 + 1); u = u01(((const uint32_t*)&r)[i & 3]); }
       io.actions[i] = __fadd_rn(__fmul_rn(u, __fsub_rn(io.clip_high, io.clip_low)), io.clip_low);
     } else if (io.ou_state) {
       io.actions[i] = explore_elem(io, i, io.actions[i], nz, have);
     }
   }
-  if (io.noise_stats && !io.random_phase && io.ou_state && io.noise_scale >= 0.f)
+  if (io.noise_stats && !io.random_phase && io.ou_state && act_noise_scale(io) >= 0.f)
     noise_stats_warp(io, have ? nz : -INFINITY, have ? nz : INFINITY, have ? nz : 0.f);
 }
 
@@ -513,6 +513,12 @@ extern "C" int ois_mlp_forward(OisAgent* a, const OisMlpShape* shape, const floa
   OIS_CHECK_ARG(shape->h0 <= a->actor.h0 && shape->h1 <= a->actor.h1 && shape->h2 <= a->actor.h2, "hidden sizes exceed workspace");
   if (n_rows == 0) return OIS_OK;
   return mlp_forward_fp32(*shape, params, x, shape->in_dim, a->h0, a->h1, a->h2, y, n_rows, (cudaStream_t)stream);
+}
+
+extern "C" int ois_agent_sync_weights(OisAgent* a, const float* actor_params, void* stream) {
+  OIS_CHECK_ARG(a && actor_params, "null argument");
+  if (a->precision != OIS_PRECISION_BF16) return OIS_OK;   // the fp32 path reads the master weights directly
+  return tc_sync_image(a, actor_params, (cudaStream_t)stream);
 }
 
 extern "C" int ois_agent_act(OisAgent* a, const float* actor_params, const OisScaler* scaler, const OisActIO* io,

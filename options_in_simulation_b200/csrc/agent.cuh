@@ -37,6 +37,7 @@ int mlp_forward_fp32(const OisMlpShape& sh, const float* P, const float* x, int 
 int tc_agent_init(OisAgent* a, cudaStream_t s);
 void tc_agent_free(OisAgent* a);
 void tc_invalidate_weights(OisAgent* a);
+int tc_sync_image(OisAgent* a, const float* actor_params, cudaStream_t s);
 // scaler -> 4-layer MLP -> (OU noise, scale, clamp when io->ou_state) in ONE launch
 int tc_actor_forward(OisAgent* a, const float* actor_params, const OisScaler* scaler, const OisActIO* io, int64_t rows,
                      cudaStream_t s);

@@ -25,6 +25,32 @@ extern "C" int ois_struct_size(int which) {
     case 4: return (int)sizeof(OisScaler);
     case 5: return (int)sizeof(OisActIO);
     case 6: return (int)sizeof(OisUpdateIO);
+    case 7: return (int)sizeof(OisStepCtl);
     default: return -1;
   }
+}
+
+// The one place the per-step scalars of a graph-replayed rollout step are derived (see OisStepCtl): a single thread,
+// launched last in the captured step.  The noise scale follows ddpg.py:247-251 in double, as the host path
+// (agent.py: DDPG.act) evaluates it before narrowing to float.
+namespace ois {
+__global__ void step_ctl_advance_kernel(OisStepCtl* c) {
+  c->step += 1;
+  c->env_philox_offset += 1;
+  c->act_philox_offset += 1;
+  c->replay_row = c->replay_rows > 0 ? (c->replay_row + 1) % c->replay_rows : 0;
+  c->flag_slot = (c->flag_slot + 1) % 3;
+  const double t = c->timestep + 1.0;
+  c->timestep = t;
+  c->noise_scale = t <= c->expl_timesteps
+      ? (float)((1.0 - t / c->expl_timesteps) * (c->expl_initial_scale - c->expl_final_scale) + c->expl_final_scale)
+      : -1.0f;
+}
+}  // namespace ois
+
+extern "C" int ois_step_ctl_advance(OisStepCtl* ctl, void* stream) {
+  OIS_CHECK_ARG(ctl, "null ctl");
+  ois::step_ctl_advance_kernel<<<1, 1, 0, (cudaStream_t)stream>>>(ctl);
+  OIS_CHECK_LAUNCH();
+  return OIS_OK;
 }

@@ -226,6 +226,16 @@ struct StageB {
   float2 obs[3][kEnvThreads];
 };
 
+// Per-step scalars: by value for a plain launch, from the device-resident OisStepCtl under CUDA-graph replay.
+__device__ __forceinline__ uint64_t env_philox_offset(const OisEnvIO& io) {
+  return io.ctl ? io.ctl->env_philox_offset : io.philox_offset;
+}
+__device__ __forceinline__ int env_flag_slot(const OisEnvIO& io) { return io.ctl ? io.ctl->flag_slot : io.flag_slot; }
+// first row of this step's ring slot, in rows of the flattened (memory_size * N, dim) view
+__device__ __forceinline__ int64_t replay_row_base(const OisEnvIO& io, int64_t n) {
+  return io.ctl ? io.ctl->replay_row * n : 0;
+}
+
 template <bool kStats, bool kEval>
 __global__ void __launch_bounds__(kEnvThreads, kEnvMinBlocks)
 env_step_kernel(const __grid_constant__ OisEnvParams p, const __grid_constant__ OisEnvState st,
@@ -247,7 +257,7 @@ env_step_kernel(const __grid_constant__ OisEnvParams p, const __grid_constant__ 
     for (int k = 0; k < OIS_EP_STATS_LEN; ++k) acc[k] = 0.f;
   }
   int any_reset_local = 0;
-  const bool zero_old = kEval && io.any_reset_flags != nullptr && io.any_reset_flags[io.flag_slot] != 0;
+  const bool zero_old = kEval && io.any_reset_flags != nullptr && io.any_reset_flags[env_flag_slot(io)] != 0;
   const bool replay = io.replay_states != nullptr;
 
   __shared__ __align__(16) StageA s_a[2];
@@ -332,7 +342,7 @@ env_step_kernel(const __grid_constant__ OisEnvParams p, const __grid_constant__ 
     const float g2 = gamma_assist(p.gamma2_mode, p.gamma2_const, sim, p.max_sim_steps);
     float tq[4], wt[4];
     if (p.blend == OIS_BLEND_SWITCH) {          // :632-636
-      const float rm = need_mask_draw ? u01(Philox(io.philox_seed)((uint64_t)i, io.philox_offset * 4).x) : __ldcs(io.rand_mask + i);
+      const float rm = need_mask_draw ? u01(Philox(io.philox_seed)((uint64_t)i, env_philox_offset(io) * 4).x) : __ldcs(io.rand_mask + i);
       const float mask = rm < g1 ? 1.0f : 0.0f;
       const float nmask = sub(1.0f, mask);
 #pragma unroll
@@ -382,9 +392,10 @@ env_step_kernel(const __grid_constant__ OisEnvParams p, const __grid_constant__ 
         replay_act = make_float4(dvd(wt[0], p.action_scale), dvd(wt[1], p.action_scale), dvd(wt[2], p.action_scale),
                                  dvd(wt[3], p.action_scale));
       else replay_act = make_float4(a4[0], a4[1], a4[2], a4[3]);
-      if (io.relabel == OIS_RELABEL_EXECUTED || p.act_dim == 4) st_stream4(io.replay_actions + 4 * i, replay_act);
-      else if (p.act_dim == 2) reinterpret_cast<float2*>(io.replay_actions)[i] = make_float2(a4[0], a4[2]);
-      else io.replay_actions[i] = a4[0];
+      const int64_t ri = replay_row_base(io, n) + i;
+      if (io.relabel == OIS_RELABEL_EXECUTED || p.act_dim == 4) st_stream4(io.replay_actions + 4 * ri, replay_act);
+      else if (p.act_dim == 2) reinterpret_cast<float2*>(io.replay_actions)[ri] = make_float2(a4[0], a4[2]);
+      else io.replay_actions[ri] = a4[0];
     }
 
     // ------------------------------------------------------------------ physics :646-653 (replaces PhysX)
@@ -463,7 +474,7 @@ env_step_kernel(const __grid_constant__ OisEnvParams p, const __grid_constant__ 
         const float4 ub = __ldcs(reinterpret_cast<const float4*>(io.reset_uniforms + 8 * i + 4));
         d.u[0] = ua.x; d.u[1] = ua.y; d.u[2] = ua.z; d.u[3] = ua.w; d.u[4] = ub.x; d.u[5] = ub.y; d.u[6] = ub.z;
       } else {   // resets are rare: the first Philox block is recomputed here rather than held across the physics
-        d = philox_reset_draws(io.philox_seed, io.philox_offset, i, Philox(io.philox_seed)((uint64_t)i, io.philox_offset * 4));
+        d = philox_reset_draws(io.philox_seed, env_philox_offset(io), i, Philox(io.philox_seed)((uint64_t)i, env_philox_offset(io) * 4));
       }
       apply_reset(p, d, sim, s, cmd);
       eb = 0;                                                   // :462
@@ -508,17 +519,18 @@ env_step_kernel(const __grid_constant__ OisEnvParams p, const __grid_constant__ 
 #pragma unroll
         for (int k = 0; k < 6; ++k) prev_obs[k] = clipf(prev_obs[k], -io.clip_obs, io.clip_obs);
       }
-      float2* rs = reinterpret_cast<float2*>(io.replay_states + 6 * i);
+      const int64_t ri = replay_row_base(io, n) + i;
+      float2* rs = reinterpret_cast<float2*>(io.replay_states + 6 * ri);
       rs[0] = make_float2(prev_obs[0], prev_obs[1]);
       rs[1] = make_float2(prev_obs[2], prev_obs[3]);
       rs[2] = make_float2(prev_obs[4], prev_obs[5]);
-      float2* rn = reinterpret_cast<float2*>(io.replay_next_states + 6 * i);
+      float2* rn = reinterpret_cast<float2*>(io.replay_next_states + 6 * ri);
       rn[0] = make_float2(oc[0], oc[1]);
       rn[1] = make_float2(oc[2], oc[3]);
       rn[2] = make_float2(oc[4], oc[5]);
-      io.replay_rewards[i] = rew;
-      io.replay_terminated[i] = reset ? 1 : 0;
-      io.replay_truncated[i] = 0;
+      io.replay_rewards[ri] = rew;
+      io.replay_terminated[ri] = reset ? 1 : 0;
+      io.replay_truncated[ri] = 0;
     }
   }
 
@@ -533,8 +545,8 @@ env_step_kernel(const __grid_constant__ OisEnvParams p, const __grid_constant__ 
     if (threadIdx.x < OIS_EP_STATS_LEN && s_stats[threadIdx.x] != 0.f) atomicAdd(io.ep_stats + threadIdx.x, s_stats[threadIdx.x]);
   }
   if (kEval && io.any_reset_flags != nullptr) {
-    if (__syncthreads_or(any_reset_local) && threadIdx.x == 0) atomicOr(io.any_reset_flags + (io.flag_slot + 1) % 3, 1);
-    if (blockIdx.x == 0 && threadIdx.x == 0) io.any_reset_flags[(io.flag_slot + 2) % 3] = 0;
+    if (__syncthreads_or(any_reset_local) && threadIdx.x == 0) atomicOr(io.any_reset_flags + (env_flag_slot(io) + 1) % 3, 1);
+    if (blockIdx.x == 0 && threadIdx.x == 0) io.any_reset_flags[(env_flag_slot(io) + 2) % 3] = 0;
   }
 }
 

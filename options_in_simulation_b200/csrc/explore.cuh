@@ -6,12 +6,18 @@
 
 namespace ois {
 
+// Per-step scalars: by value for a plain launch, from the device-resident OisStepCtl under CUDA-graph replay.
+__device__ __forceinline__ uint64_t act_philox_offset(const OisActIO& io) {
+  return io.ctl ? io.ctl->act_philox_offset : io.philox_offset;
+}
+__device__ __forceinline__ float act_noise_scale(const OisActIO& io) { return io.ctl ? io.ctl->noise_scale : io.noise_scale; }
+
 __device__ __forceinline__ float explore_elem(const OisActIO& io, int64_t i, float action, float& nz, bool& have) {
   float z;
   if (io.normals) {
     z = io.normals[i];
   } else {
-    const uint4 r = Philox(io.philox_seed)((uint64_t)(i >> 2), io.philox_offset * 2);
+    const uint4 r = Philox(io.philox_seed)((uint64_t)(i >> 2), act_philox_offset(io) * 2);
     const float2 n01 = normal2(r.x, r.y), n23 = normal2(r.z, r.w);
     const int k = (int)(i & 3);
     z = k == 0 ? n01.x : k == 1 ? n01.y : k == 2 ? n23.x : n23.y;
@@ -19,8 +25,8 @@ __device__ __forceinline__ float explore_elem(const OisActIO& io, int64_t i, flo
   const float st = io.ou_state[i];
   const float ns = __fadd_rn(st, __fadd_rn(__fmul_rn(-st, io.theta), __fmul_rn(io.sigma, z)));   // state += -state*theta + sigma*N
   io.ou_state[i] = ns;
-  if (io.noise_scale >= 0.f) {
-    nz = __fmul_rn(__fmul_rn(io.base_scale, ns), io.noise_scale);
+  if (act_noise_scale(io) >= 0.f) {
+    nz = __fmul_rn(__fmul_rn(io.base_scale, ns), act_noise_scale(io));
     have = true;
     return fminf(fmaxf(__fadd_rn(action, nz), io.clip_low), io.clip_high);
   }
@@ -35,7 +41,7 @@ __device__ __forceinline__ void explore_row4(const OisActIO& io, int64_t row, fl
     const float4 n4 = *reinterpret_cast<const float4*>(io.normals + 4 * row);
     z[0] = n4.x; z[1] = n4.y; z[2] = n4.z; z[3] = n4.w;
   } else {
-    const uint4 r = Philox(io.philox_seed)((uint64_t)row, io.philox_offset * 2);
+    const uint4 r = Philox(io.philox_seed)((uint64_t)row, act_philox_offset(io) * 2);
     const float2 n01 = normal2(r.x, r.y), n23 = normal2(r.z, r.w);
     z[0] = n01.x; z[1] = n01.y; z[2] = n23.x; z[3] = n23.y;
   }
@@ -44,8 +50,8 @@ __device__ __forceinline__ void explore_row4(const OisActIO& io, int64_t row, fl
 #pragma unroll
   for (int k = 0; k < 4; ++k) {
     st[k] = __fadd_rn(st[k], __fadd_rn(__fmul_rn(-st[k], io.theta), __fmul_rn(io.sigma, z[k])));
-    if (io.noise_scale >= 0.f) {
-      const float nz = __fmul_rn(__fmul_rn(io.base_scale, st[k]), io.noise_scale);
+    if (act_noise_scale(io) >= 0.f) {
+      const float nz = __fmul_rn(__fmul_rn(io.base_scale, st[k]), act_noise_scale(io));
       mx = fmaxf(mx, nz); mn = fminf(mn, nz); sm += nz;
       a[k] = fminf(fmaxf(__fadd_rn(a[k], nz), io.clip_low), io.clip_high);
     }
@@ -64,7 +70,7 @@ __device__ __forceinline__ void explore_row_prepare(const OisActIO& io, int64_t 
 #pragma unroll
     for (int k = 0; k < 4; ++k) if (k < A) z[k] = io.normals[i0 + k];
   } else {
-    const uint4 r = Philox(io.philox_seed)((uint64_t)(i0 >> 2), io.philox_offset * 2);
+    const uint4 r = Philox(io.philox_seed)((uint64_t)(i0 >> 2), act_philox_offset(io) * 2);
     const int l0 = (int)(i0 & 3);
     if (A == 4) {
       const float2 n01 = normal2(r.x, r.y), n23 = normal2(r.z, r.w);
@@ -75,7 +81,7 @@ __device__ __forceinline__ void explore_row_prepare(const OisActIO& io, int64_t 
       else z[0] = (l0 & 1) ? nn.y : nn.x;
     }
   }
-  applied = io.noise_scale >= 0.f;
+  applied = act_noise_scale(io) >= 0.f;
 #pragma unroll
   for (int k = 0; k < 4; ++k) {
     nz[k] = 0.f;
@@ -83,7 +89,7 @@ __device__ __forceinline__ void explore_row_prepare(const OisActIO& io, int64_t 
       const float st = io.ou_state[i0 + k];
       const float ns = __fadd_rn(st, __fadd_rn(__fmul_rn(-st, io.theta), __fmul_rn(io.sigma, z[k])));
       io.ou_state[i0 + k] = ns;
-      if (applied) nz[k] = __fmul_rn(__fmul_rn(io.base_scale, ns), io.noise_scale);
+      if (applied) nz[k] = __fmul_rn(__fmul_rn(io.base_scale, ns), act_noise_scale(io));
     }
   }
 }

@@ -611,7 +611,7 @@ tc_actor_kernel(const __grid_constant__ TcActArgs args) {
             for (int j = 0; j < 8; ++j) if (j < A) out[j] = a[j];
           }
         }
-        if (args.io.noise_stats && args.io.ou_state && args.io.noise_scale >= 0.f) noise_stats_warp(args.io, mx, mn, sm);
+        if (args.io.noise_stats && args.io.ou_state && act_noise_scale(args.io) >= 0.f) noise_stats_warp(args.io, mx, mn, sm);
         TC_STAMP(tr && warp == 2 && tiles_done == 0, 22);
       }
     }
@@ -660,8 +660,8 @@ void tc_invalidate_weights(OisAgent* a) {
   if (a->tc) ((TcState*)a->tc)->valid = false;
 }
 
-int tc_actor_forward(OisAgent* a, const float* actor_params, const OisScaler* scaler, const OisActIO* io, int64_t rows,
-                     cudaStream_t s) {
+// (Re)build the inference kernel's bf16 stream image if the fp32 master changed since it was packed.
+int tc_sync_image(OisAgent* a, const float* actor_params, cudaStream_t s) {
   using namespace tc;
   TcState* st = (TcState*)a->tc;
   OIS_CHECK_ARG(st, "agent was not created with OIS_PRECISION_BF16");
@@ -672,6 +672,14 @@ int tc_actor_forward(OisAgent* a, const float* actor_params, const OisScaler* sc
     st->valid = true;
     st->packed_from = actor_params;
   }
+  return OIS_OK;
+}
+
+int tc_actor_forward(OisAgent* a, const float* actor_params, const OisScaler* scaler, const OisActIO* io, int64_t rows,
+                     cudaStream_t s) {
+  using namespace tc;
+  if (int e = tc_sync_image(a, actor_params, s)) return e;
+  TcState* st = (TcState*)a->tc;
   TcActArgs args;
   args.params = actor_params;
   args.image = (const uint8_t*)st->image;

@@ -140,10 +140,16 @@ class TorqueDistributionTask:
         self.obs_buf = torch.zeros(n, 6, dtype=torch.float32, device=dev)
         # clamp(obs_buf, +-clipObservations) as the env wrapper returns it; two buffers alternate so the previous
         # step's observations (the trainer's `states`) stay intact while the next step is written
-        self._obs_clipped = [torch.zeros(n, 6, dtype=torch.float32, device=dev) for _ in range(2)]
+        # what a step hands back — clamped observations (buffer 0), rewards, reset flags — is ONE allocation
+        # [obs N*24 B | rew N*4 B | reset N B], so that a host in the loop gets it with a single device->host copy
+        # (rollout.RolloutGraph); the tensors below are views into it
+        self._out_pack = torch.zeros(n * 29, dtype=torch.uint8, device=dev)
+        self._obs_clipped = [self._out_pack[: n * 24].view(torch.float32).view(n, 6),
+                             torch.zeros(n, 6, dtype=torch.float32, device=dev)]
         self.obs_clipped = self._obs_clipped[0]
-        self.rew_buf = torch.zeros(n, dtype=torch.float32, device=dev)
-        self.reset_buf = torch.ones(n, dtype=torch.bool, device=dev)
+        self.rew_buf = self._out_pack[n * 24: n * 28].view(torch.float32)
+        self.reset_buf = self._out_pack[n * 28:].view(torch.bool)
+        self.reset_buf.fill_(True)
         self.timeout_buf = zl()
         self.progress_buf = zl()
         self.states_buf = torch.zeros(n, 0, dtype=torch.float32, device=dev)
@@ -285,11 +291,12 @@ class TorqueDistributionTask:
 
     def reset(self):
         """RLTask.reset (rl_task.py:251-253): flag every env for reset."""
-        self.reset_buf = torch.ones_like(self.reset_buf)
+        self.reset_buf.fill_(True)   # in place: the buffer is a view of _out_pack (the reference allocates a new one)
 
-    def pre_physics_step(self, actions, record: bool = True):
+    def pre_physics_step(self, actions, record: bool = True, _ctl=None):
         """KAMMA_medium.py:596-656 — and, fused behind it, everything post_physics_step computes.
-        ``record=False`` suppresses the fused replay append for this step (the wrapper's reset step)."""
+        ``record=False`` suppresses the fused replay append for this step (the wrapper's reset step).
+        ``_ctl`` (rollout.RolloutGraph): device OisStepCtl the kernel takes its per-step scalars and replay row from."""
         if self._env is not None and hasattr(self._env, "world") and not self._env.world.is_playing():
             return
         if not (actions.is_cuda and actions.dtype == torch.float32 and actions.is_contiguous()
@@ -305,7 +312,8 @@ class TorqueDistributionTask:
         io.obs, io.rew, io.reset = self.obs_buf.data_ptr(), self.rew_buf.data_ptr(), self.reset_buf.data_ptr()
         io.wheel_torqs, io.timeout = self.wheel_torqs.data_ptr(), self.timeout_buf.data_ptr()
         io.torques, io.guiding = self.torques.data_ptr(), self.guiding_reward.data_ptr()
-        want_stats = self.stats_interval > 0 and (self._launches % self.stats_interval == 0)
+        io.ctl = _ctl
+        want_stats = _ctl is None and self.stats_interval > 0 and (self._launches % self.stats_interval == 0)
         if want_stats:
             self._ep_stats.zero_()
             io.ep_stats = self._ep_stats.data_ptr()
@@ -314,11 +322,11 @@ class TorqueDistributionTask:
             io.any_reset_flags = self._any_reset_flags.data_ptr()
         io.flag_slot = self._launches % 3
         io.clip_obs = self.clip_obs if math.isfinite(self.clip_obs) else -1.0
-        self.obs_clipped = self._obs_clipped[self._launches & 1]
+        self.obs_clipped = self._obs_clipped[0 if _ctl is not None else self._launches & 1]
         io.obs_clipped = self.obs_clipped.data_ptr()
         if self._replay is not None and record:
             m = self._replay
-            r = m.memory_index
+            r = m.memory_index if _ctl is None else 0   # with a ctl block the kernel offsets the base by ctl->replay_row
             io.replay_states = m.tensors["states"][r].data_ptr()
             io.replay_actions = m.tensors["actions"][r].data_ptr()
             io.replay_rewards = m.tensors["rewards"][r].data_ptr()
@@ -339,8 +347,8 @@ class TorqueDistributionTask:
         self.progress_buf += 1
         return self.obs_buf, self.rew_buf, self.reset_buf, self.extras
 
-    def step(self, actions, record: bool = True):
-        self.pre_physics_step(actions, record)
+    def step(self, actions, record: bool = True, _ctl=None):
+        self.pre_physics_step(actions, record, _ctl)
         return self.obs_buf, self.rew_buf, self.reset_buf, self.extras
 
     def get_observations(self):   # :825-869

@@ -1,0 +1,167 @@
+"""``RolloutGraph`` — one policy step of the trainer's loop body replayed as ONE CUDA-graph launch.
+
+The step is what src/my_trainers/base_KA_DDPG.py:175-219 does per timestep::
+
+    actions = agent.act(states, t, T)                       src/my_agents/ddpg.py:215-268
+    next_states, rewards, terminated, ... = env.step(actions)   src/my_envs/KAMMA_medium.py:596-727
+    agent.record_transition(...)                             src/my_agents/ddpg.py:270-329 (fused into the env kernel)
+
+Issued call by call, that is two C-ABI calls plus (with a host in the loop) four torch copies per step: at 4096 envs
+the GPU work is ~30 us and the host issue cost is of the same order.  Captured once, the step is one
+``cudaGraphLaunch``.  A captured launch has frozen arguments, so everything that changes from step to step (Philox
+offsets, the decayed exploration scale, the replay ring slot, the eval flag slot) lives in a device-resident
+``OisStepCtl`` block (include/ois_b200.h) that a single-thread kernel at the end of the captured step advances.
+The host mirrors (``agent._act_calls``, ``task._launches``, ``memory.memory_index`` / ``filled``) are advanced
+arithmetically per replay, so eager calls and graph replays can be interleaved and produce the same stream of results
+as eager calls alone (tests/test_rollout_graph_gpu.py checks bit-equality).
+
+Limits: the agent must be past ``random_timesteps`` (that branch launches a different kernel), noise statistics
+tracking and the strided env statistics are not gathered on replayed steps (``write_interval`` / ``stats_interval``
+reads need a host round trip per step anyway), supplied parity draws are not supported.
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import torch
+
+from . import _lib as L
+
+
+class RolloutGraph:
+    """``host_io=False``: device-resident loop — ``step()`` returns the (fixed) device tensors
+    ``(next_states, rewards[N,1], terminated[N,1])`` without synchronising.
+    ``host_io=True``: the observations of each step arrive in the pinned host tensor ``h_states`` (the caller fills it
+    before ``step()``), and the step's results are returned in pinned host tensors after ONE packed device->host copy
+    and a synchronise — the host-in-the-loop shape ``bench.py`` times as ``e2e``."""
+
+    def __init__(self, env, agent, timestep: int, timesteps: int, host_io: bool = False):
+        task = env.task
+        if not agent._fused_replay or task._replay is None:
+            raise L.OisError("RolloutGraph needs agent.fuse_replay_with(task) (the append is part of the captured kernel)")
+        if timestep < agent._random_timesteps:
+            raise L.OisError("RolloutGraph starts after random_timesteps (that phase launches a different kernel)")
+        if agent._supplied or task._supplied_mask is not None or task._supplied_reset is not None:
+            raise L.OisError("RolloutGraph does not take supplied parity draws")
+        if agent.write_interval > 0:
+            raise L.OisError("RolloutGraph does not gather the per-step noise statistics (write_interval must be 0)")
+        self.env, self.task, self.agent, self.memory = env, task, agent, task._replay
+        self.timestep, self.timesteps = int(timestep), int(timesteps)
+        self.host_io = host_io
+        self.kernel_launches = 0
+        dev, n, A = task.device, task.num_envs, task.num_actions
+        self._ctl = torch.zeros(C.sizeof(L.StepCtl), dtype=torch.uint8, device=dev)
+        self._actions = torch.empty(n, A, dtype=torch.float32, device=dev)
+        # the state the captured actor launch reads: the env's own clamped-observation buffer (device loop) or the
+        # landing buffer of the host->device copy (host loop)
+        self.states = task._obs_clipped[0]
+        if host_io:
+            self.h_states = torch.empty(n, 6, dtype=torch.float32).pin_memory()
+            self._d_states = torch.empty(n, 6, dtype=torch.float32, device=dev)
+            # obs [N,6] f32 | rew [N] f32 | terminated [N] u8: the task keeps them in ONE allocation (envs.py: _out_pack)
+            self._h_pack = torch.empty(n * 29, dtype=torch.uint8).pin_memory()
+            self.h_next_states = self._h_pack[: n * 24].view(torch.float32).view(n, 6)
+            self.h_rewards = self._h_pack[n * 24: n * 28].view(torch.float32).view(n, 1)
+            self.h_terminated = self._h_pack[n * 28:].view(torch.bool).view(n, 1)
+        self._graph = None
+        self._warm = False
+        self._per_step = (1, 1)
+
+    # ------------------------------------------------------------------ the per-step scalars
+    def _write_ctl(self):
+        """Host -> device copy of the block for the NEXT step, from the host mirrors (so eager steps may have run)."""
+        a, t, m = self.agent, self.task, self.memory
+        c = L.StepCtl()
+        c.step = 0
+        c.env_philox_offset, c.act_philox_offset = t._launches, a._act_calls
+        c.replay_row, c.replay_rows = m.memory_index, m.memory_size
+        c.flag_slot = t._launches % 3
+        if a._exploration_timesteps is None:
+            a._exploration_timesteps = self.timesteps      # ddpg.py:244-245
+        T_e = a._exploration_timesteps
+        c.timestep, c.expl_timesteps = float(self.timestep), float(T_e)
+        c.expl_initial_scale, c.expl_final_scale = a._exploration_initial_scale, a._exploration_final_scale
+        c.noise_scale = ((1 - self.timestep / T_e) * (a._exploration_initial_scale - a._exploration_final_scale)
+                         + a._exploration_final_scale) if self.timestep <= T_e else -1.0
+        host = torch.frombuffer(bytearray(bytes(c)), dtype=torch.uint8)
+        self._ctl.copy_(host)
+        self._mirror = (t._launches, a._act_calls, m.memory_index, self.timestep)
+
+    def _mirrors_moved(self):
+        t, a, m = self.task, self.agent, self.memory
+        return self._mirror != (t._launches, a._act_calls, m.memory_index, self.timestep)
+
+    def _issue(self):
+        """The launches of one step, on the current stream (eagerly once to warm up, then under capture)."""
+        ctl = self._ctl.data_ptr()
+        if self.host_io:
+            self._d_states.copy_(self.h_states, non_blocking=True)
+            states = self._d_states
+        else:
+            states = self.states
+        self.agent.act(states, self.timestep, self.timesteps, _ctl=ctl, _out=self._actions)
+        self.task.step(self._actions, True, _ctl=ctl)
+        L.check(L.lib().ois_step_ctl_advance(ctl, L.current_stream()))
+        if self.host_io:
+            self._h_pack.copy_(self.task._out_pack, non_blocking=True)
+
+    def _host_state(self):
+        t, a, m = self.task, self.agent, self.memory
+        return (t._launches, t.kernel_launches, a._act_calls, a.kernel_launches, m.memory_index, m.filled)
+
+    def _set_host_state(self, s):
+        t, a, m = self.task, self.agent, self.memory
+        t._launches, t.kernel_launches, a._act_calls, a.kernel_launches, m.memory_index, m.filled = s
+
+    def _capture(self):
+        saved = self._host_state()            # capture runs the Python bookkeeping of one step without executing it
+        graph = torch.cuda.CUDAGraph()
+        # "relaxed": Python's collector may run a finaliser while the step is being captured (an old agent handle or
+        # graph going away -> cudaFree), which the stricter modes treat as an error; nothing captured here depends on
+        # memory that such a call could touch (every buffer is held by this object, the task, the agent or the memory)
+        with torch.cuda.graph(graph, capture_error_mode="relaxed"):
+            self._issue()
+        self._set_host_state(saved)
+        self._graph = graph
+
+    def _advance_host(self):
+        """What one eager act + step would have done to the host mirrors."""
+        t, a, m = self.task, self.agent, self.memory
+        t._launches += 1
+        t.kernel_launches += self._per_step[0]
+        a._act_calls += 1
+        a.kernel_launches += self._per_step[1]
+        m.advance()
+        t.obs_clipped = t._obs_clipped[0]
+        self.env._obs = t.obs_clipped
+        self.kernel_launches += 1             # the ctl-advance kernel
+        self.timestep += 1
+        self._mirror = (t._launches, a._act_calls, m.memory_index, self.timestep)
+
+    # ------------------------------------------------------------------ public
+    def step(self):
+        """One policy step.  The first call issues the launches eagerly (lazy initialisation inside the library must
+        not happen under capture), the second captures, every later call is one graph launch."""
+        a, t = self.agent, self.task
+        if not self.host_io and t.obs_clipped.data_ptr() != self.states.data_ptr():
+            self.states.copy_(t.obs_clipped)          # an eager step left the current observation in the other buffer
+        if not self._warm or self._mirrors_moved():
+            self._write_ctl()                          # (re)seed the device block from the host mirrors
+        if not self._warm:
+            before = self._host_state()
+            self._issue()
+            after = self._host_state()
+            self._per_step = (after[1] - before[1], after[3] - before[3])
+            self._set_host_state(before)
+            self._warm = True
+        else:
+            # the bf16 image of the actor weights follows DDPG._update; a no-op when nothing changed
+            L.check(L.lib().ois_agent_sync_weights(a._handle, L.ptr(a.policy.flat), L.current_stream()))
+            if self._graph is None:
+                self._capture()
+            self._graph.replay()
+        self._advance_host()
+        if self.host_io:
+            torch.cuda.current_stream().synchronize()
+            return self.h_next_states, self.h_rewards, self.h_terminated
+        return t.obs_clipped, t.rew_buf.view(-1, 1), t.reset_buf.view(-1, 1)

@@ -34,6 +34,8 @@ SEQUENTIAL_TRAINER_DEFAULT_CONFIG = {   # src/my_trainers/sequential.py:14-20
     "kind": "auto",          # "KA_DDPG" (relabel) | "KA" (no relabel) | "auto": the env variant's pairing
     "log_interval": None,    # steps between env-0 / episode logging reads; None = agent.write_interval
     "pre_step_hook": None,   # callable(trainer, timestep) run at the top of every timestep (parity tests supply draws)
+    "graph_rollout": False,  # act + env.step (+ fused replay append) as ONE CUDA-graph launch per timestep once past
+                             # random_timesteps (rollout.RolloutGraph; needs agent.fuse_replay_with(task), write_interval 0)
 }
 
 # observed_components key -> TensorBoard tag suffix (base_KA_DDPG.py:229-254)
@@ -107,10 +109,22 @@ class SequentialTrainer:
         agent.set_running_mode("train")
         states, infos = env.reset()
         hook = self.cfg["pre_step_hook"]
+        graph = None
+        if self.cfg["graph_rollout"]:
+            from .rollout import RolloutGraph
+            graph = RolloutGraph(env, agent, max(self.initial_timestep, agent._random_timesteps), self.timesteps)
         for timestep in self._progress():
             if hook is not None:
                 hook(self, timestep)
             agent.pre_interaction(timestep=timestep, timesteps=self.timesteps)
+            if graph is not None and timestep >= agent._random_timesteps:
+                graph.timestep = timestep       # act + step + record_transition: one graph launch
+                next_states, rewards, terminated = graph.step()
+                truncated, infos = env._truncated, env.task.extras
+                agent.post_interaction(timestep=timestep, timesteps=self.timesteps)     # base_KA_DDPG.py:265
+                states = self._next_states(next_states, terminated, truncated)
+                agent.post_interaction(timestep=timestep, timesteps=self.timesteps)     # base_KA_DDPG.py:283 (again)
+                continue
             with torch.no_grad():
                 actions = agent.act(states, timestep=timestep, timesteps=self.timesteps)[0]
                 next_states, rewards, terminated, truncated, infos = env.step(actions)

@@ -91,6 +91,10 @@ class TorqueDistributionTask:
         self._launches = 0          # policy steps issued: Philox offset and eval flag slot
         self.kernel_launches = 0    # CUDA kernels launched by this object (bench "gpu_launches")
         self.stats_interval = 0     # > 0: refresh extras["episode"] every that many steps (one small D2H)
+        # device-side statistics log (evaluate.tracking_error_sweep): a zeroed [T, OIS_EP_STATS_LEN] float tensor; step k
+        # reduces its episode statistics into row k and the host reads the whole log ONCE at the end (no per-step sync)
+        self.stats_log = None
+        self._stats_row = 0
         self.extras: dict = {}
         self._supplied_mask = None
         self._supplied_reset = None
@@ -314,6 +318,10 @@ class TorqueDistributionTask:
         io.torques, io.guiding = self.torques.data_ptr(), self.guiding_reward.data_ptr()
         io.ctl = _ctl
         want_stats = _ctl is None and self.stats_interval > 0 and (self._launches % self.stats_interval == 0)
+        if self.stats_log is not None and _ctl is None and self._stats_row < self.stats_log.shape[0]:
+            want_stats = False
+            io.ep_stats = self.stats_log[self._stats_row].data_ptr()
+            self._stats_row += 1
         if want_stats:
             self._ep_stats.zero_()
             io.ep_stats = self._ep_stats.data_ptr()

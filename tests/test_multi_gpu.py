@@ -37,3 +37,9 @@ def test_bench_two_ranks_prints_one_aggregate_line():
     assert len(lines) == 1
     d = json.loads(lines[0])
     assert d["n_gpus"] == 2 and d["scaling"] == "weak" and d["value"] > 0 and d["e2e"]["value"] > 0
+
+
+@pytest.mark.skipif(_gpus() < 2, reason="needs 2 GPUs")
+def test_eval_sweep_shards_over_ranks_and_reduces_once():
+    r = _torchrun(2, os.path.join("tests", "scripts", "eval_sweep_ranks.py"), port=29521)
+    assert r.returncode == 0 and "eval_sweep_ranks ok" in r.stdout, r.stdout[-2000:] + r.stderr[-4000:]

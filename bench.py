@@ -297,15 +297,16 @@ def e2e_timed(world, steps, warmup):
     return a.elapsed_time(b) / steps, n * 6 * 4, n * (6 * 4 + 4 + 1)
 
 
-def e2e_graph_timed(world, steps, warmup):
-    """The same host-in-the-loop step through rollout.RolloutGraph: ONE graph launch per step holding the H2D copy of
-    the observations, act, env step (+ replay append), the step-control advance and ONE packed D2H copy of
-    (obs | rew | reset); the host synchronises and hands the new observations back every step."""
+def e2e_graph_timed(world, steps, warmup, mode=True):
+    """The same host-in-the-loop step through rollout.RolloutGraph: ONE graph launch per step.  mode=True: the actor
+    kernel reads the observations from pinned host memory in place and the env kernel stores (obs | rew | reset) to
+    pinned host memory in place (zero-copy over PCIe); mode="copy": an H2D copy node, the two kernels and ONE packed
+    D2H copy node.  Either way the host synchronises and hands the new observations back every step."""
     from options_in_simulation_b200.rollout import RolloutGraph
 
     torch = world.torch
     n = world.n
-    g = RolloutGraph(world.env, world.agent, world.t, world.T, host_io=True)
+    g = RolloutGraph(world.env, world.agent, world.t, world.T, host_io=mode)
     g.h_states.copy_(world.obs)
 
     def one():
@@ -322,6 +323,7 @@ def e2e_graph_timed(world, steps, warmup):
     b.record()
     torch.cuda.synchronize()
     world.t = g.timestep
+    world.task._obs_clipped[0].copy_(g.h_next_states)     # zero-copy mode leaves the task's device-side copy untouched
     world.obs = world.task.obs_clipped
     return a.elapsed_time(b) / steps, n * 6 * 4, n * 29
 
@@ -432,12 +434,14 @@ def main():
     barrier()
     e2e_ms, h2d, d2h = e2e_graph_timed(world, min(args.steps, 200), 5)
     barrier()
+    e2e_copy_ms, _, _ = e2e_graph_timed(world, min(args.steps, 200), 5, mode="copy")
+    barrier()
     graph_ms = graph_device_timed(world, min(args.steps, 200), 5, flush)
     barrier()
     if world_size > 1:
-        t = torch.tensor([ms, e2e_ms, e2e_eager_ms, graph_ms], device=device, dtype=torch.float64)
+        t = torch.tensor([ms, e2e_ms, e2e_eager_ms, graph_ms, e2e_copy_ms], device=device, dtype=torch.float64)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        ms, e2e_ms, e2e_eager_ms, graph_ms = t.tolist()
+        ms, e2e_ms, e2e_eager_ms, graph_ms, e2e_copy_ms = t.tolist()
     value = world_size * n * 1e3 / ms
     e2e_value = world_size * n * 1e3 / e2e_ms
 
@@ -452,12 +456,15 @@ def main():
                    "parallelism": f"env/replay shards x{world_size}, no data-path collective"},
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                 "ms_per_step": e2e_ms,
-                "path": "rollout.RolloutGraph(host_io=True): one CUDA-graph launch per step (H2D obs, act, env step + "
-                        "replay append, step-control advance, one packed D2H of obs|rew|reset), host sync every step",
+                "path": "rollout.RolloutGraph(host_io=True): one CUDA-graph launch per step = actor kernel reading the "
+                        "observations from pinned host memory in place + env kernel (step, replay append, step-control "
+                        "advance) storing obs|rew|reset to pinned host memory in place; host sync every step; the bytes "
+                        "below cross PCIe every step as zero-copy loads / stores",
+                "copy_nodes_ms_per_step": e2e_copy_ms,
                 "call_by_call_ms_per_step": e2e_eager_ms,
                 "call_by_call_value": world_size * n * 1e3 / e2e_eager_ms},
         "graph_replay": {"ms_per_step": graph_ms, "value": world_size * n * 1e3 / graph_ms,
-                         "note": "the device-resident step replayed through rollout.RolloutGraph (3 kernels per replay); "
+                         "note": "the device-resident step replayed through rollout.RolloutGraph (2 kernels per replay); "
                                  "`value` itself is the call-by-call path"},
         "gpu_launches": launches, "clocks": clocks,
     }

@@ -84,8 +84,9 @@ typedef struct OisEnvState {
 
 /* Device-resident per-step scalars, for CUDA-graph replay of the rollout step (the graph's kernel arguments are frozen
  * at capture, so what changes from one policy step to the next lives here instead).  When OisEnvIO.ctl / OisActIO.ctl is
- * non-NULL the kernels take these values in place of the like-named by-value fields; ois_step_ctl_advance moves the
- * block to the next step with ONE single-thread launch at the end of the captured step.  The host initialises it with
+ * non-NULL the kernels take these values in place of the like-named by-value fields.  The block moves to the next step
+ * either inside ois_env_step (self_advance = 1: the last CTA of the env kernel to finish does it, after every reader of
+ * the block is done) or with ONE single-thread launch of ois_step_ctl_advance at the end of the captured step.  The host initialises it with
  * a plain host->device copy of this struct. */
 typedef struct OisStepCtl {
   int64_t step;                /* steps taken since the host initialised the block */
@@ -97,6 +98,9 @@ typedef struct OisStepCtl {
   float noise_scale;           /* OisActIO.noise_scale of this step (ddpg.py:247-251) */
   double timestep;             /* trainer timestep of this step */
   double expl_timesteps, expl_initial_scale, expl_final_scale;   /* ddpg.py:105-107 */
+  int32_t self_advance;        /* 1: ois_env_step advances this block itself (its last CTA to finish, see `ticket`), so a
+                                  captured step needs no ois_step_ctl_advance launch */
+  uint32_t ticket;             /* CTAs of the current env step that have finished; 0 between steps */
 } OisStepCtl;
 
 /* ctl := the next policy step (offsets + 1, replay_row + 1 mod replay_rows, flag_slot + 1 mod 3, timestep + 1 and the

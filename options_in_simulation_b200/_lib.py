@@ -60,7 +60,8 @@ class StepCtl(C.Structure):
     """OisStepCtl: per-step scalars kept on the device for CUDA-graph replay of the rollout step."""
     _fields_ = [("step", _i64), ("env_philox_offset", _u64), ("act_philox_offset", _u64), ("replay_row", _i64),
                 ("replay_rows", _i64), ("flag_slot", _i32), ("noise_scale", _f), ("timestep", C.c_double),
-                ("expl_timesteps", C.c_double), ("expl_initial_scale", C.c_double), ("expl_final_scale", C.c_double)]
+                ("expl_timesteps", C.c_double), ("expl_initial_scale", C.c_double), ("expl_final_scale", C.c_double),
+                ("self_advance", _i32), ("ticket", C.c_uint32)]
 
 
 class MlpShape(C.Structure):

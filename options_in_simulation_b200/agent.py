@@ -481,19 +481,22 @@ class DDPG:
     def pre_interaction(self, timestep, timesteps):
         pass
 
-    def act(self, states, timestep, timesteps, *, _ctl=None, _out=None):
+    def act(self, states, timestep, timesteps, *, _ctl=None, _out=None, _states_ptr=None):
         """ddpg.py:215-268 as ONE C-ABI call: scaler -> actor MLP -> OU noise -> scale -> clamp
         (or U[low, high] while timestep < random_timesteps).
         ``_ctl`` / ``_out`` are for rollout.RolloutGraph: a device OisStepCtl the kernel takes its per-step scalars
-        from, and a fixed output buffer (a captured launch cannot have either change between replays)."""
-        states = states.to(self.device, torch.float32).contiguous() if not (states.is_cuda and states.is_contiguous()) else states
+        from, and a fixed output buffer (a captured launch cannot have either change between replays).
+        ``_states_ptr``: device-visible address of ``states`` when it is a pinned HOST tensor the kernel reads in place
+        (zero-copy over PCIe / C2C; the observations of one step are read exactly once, so a staging copy buys nothing)."""
+        if _states_ptr is None:
+            states = states.to(self.device, torch.float32).contiguous() if not (states.is_cuda and states.is_contiguous()) else states
         n = states.shape[0]
         self._ensure_handle(n)
         A = self.policy.shape.out_dim
         actions = torch.empty(n, A, dtype=torch.float32, device=self.device) if _out is None else _out
         io = L.ActIO()
         io.ctl = _ctl
-        io.states, io.actions = states.data_ptr(), actions.data_ptr()
+        io.states, io.actions = (states.data_ptr() if _states_ptr is None else _states_ptr), actions.data_ptr()
         io.philox_seed, io.philox_offset = self._seed, self._act_calls
         io.clip_low, io.clip_high = self._clip
         io.normals = L.ptr(self._supplied.get("normals"))

@@ -30,23 +30,11 @@ extern "C" int ois_struct_size(int which) {
   }
 }
 
-// The one place the per-step scalars of a graph-replayed rollout step are derived (see OisStepCtl): a single thread,
-// launched last in the captured step.  The noise scale follows ddpg.py:247-251 in double, as the host path
-// (agent.py: DDPG.act) evaluates it before narrowing to float.
+// Stand-alone advance of the step-control block (ois_common.cuh: step_ctl_advance) for callers that do not let the env
+// kernel do it (OisStepCtl.self_advance = 0): a single thread, launched last in the captured step.
 namespace ois {
-__global__ void step_ctl_advance_kernel(OisStepCtl* c) {
-  c->step += 1;
-  c->env_philox_offset += 1;
-  c->act_philox_offset += 1;
-  c->replay_row = c->replay_rows > 0 ? (c->replay_row + 1) % c->replay_rows : 0;
-  c->flag_slot = (c->flag_slot + 1) % 3;
-  const double t = c->timestep + 1.0;
-  c->timestep = t;
-  c->noise_scale = t <= c->expl_timesteps
-      ? (float)((1.0 - t / c->expl_timesteps) * (c->expl_initial_scale - c->expl_final_scale) + c->expl_final_scale)
-      : -1.0f;
+__global__ void step_ctl_advance_kernel(OisStepCtl* c) { step_ctl_advance(c); }
 }
-}  // namespace ois
 
 extern "C" int ois_step_ctl_advance(OisStepCtl* ctl, void* stream) {
   OIS_CHECK_ARG(ctl, "null ctl");

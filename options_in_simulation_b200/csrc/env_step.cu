@@ -548,6 +548,20 @@ env_step_kernel(const __grid_constant__ OisEnvParams p, const __grid_constant__ 
     if (__syncthreads_or(any_reset_local) && threadIdx.x == 0) atomicOr(io.any_reset_flags + (env_flag_slot(io) + 1) % 3, 1);
     if (blockIdx.x == 0 && threadIdx.x == 0) io.any_reset_flags[(env_flag_slot(io) + 2) % 3] = 0;
   }
+  // Graph replay: the last CTA to finish moves the step-control block to the next step.  Every reader of the block — the
+  // actor kernel, which completed before this grid's pdl_wait returned, and all CTAs of this grid, which take their
+  // ticket only after their last use of it — is done by then.
+  if (io.ctl != nullptr && io.ctl->self_advance) {
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      OisStepCtl* c = const_cast<OisStepCtl*>(io.ctl);
+      __threadfence();
+      if (atomicAdd(&c->ticket, 1u) == gridDim.x - 1) {
+        c->ticket = 0;
+        step_ctl_advance(c);
+      }
+    }
+  }
 }
 
 __global__ void __launch_bounds__(kEnvThreads)

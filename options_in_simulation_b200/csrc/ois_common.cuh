@@ -109,6 +109,22 @@ inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, s
   return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
 }
 
+// The one place the per-step scalars of a graph-replayed rollout step are derived (see OisStepCtl in ois_b200.h); run by a
+// single thread.  The noise scale follows ddpg.py:247-251 in double, as the host path (agent.py: DDPG.act) evaluates it
+// before narrowing to float.
+__device__ inline void step_ctl_advance(OisStepCtl* c) {
+  c->step += 1;
+  c->env_philox_offset += 1;
+  c->act_philox_offset += 1;
+  c->replay_row = c->replay_rows > 0 ? (c->replay_row + 1) % c->replay_rows : 0;
+  c->flag_slot = (c->flag_slot + 1) % 3;
+  const double t = c->timestep + 1.0;
+  c->timestep = t;
+  c->noise_scale = t <= c->expl_timesteps
+      ? (float)((1.0 - t / c->expl_timesteps) * (c->expl_initial_scale - c->expl_final_scale) + c->expl_final_scale)
+      : -1.0f;
+}
+
 // streaming 16-byte accesses: every state field is touched once per step
 __device__ inline float4 ld_stream4(const float* p) { return __ldcs(reinterpret_cast<const float4*>(p)); }
 __device__ inline void st_stream4(float* p, const float4& v) { __stcs(reinterpret_cast<float4*>(p), v); }

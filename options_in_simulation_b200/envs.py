@@ -297,10 +297,12 @@ class TorqueDistributionTask:
         """RLTask.reset (rl_task.py:251-253): flag every env for reset."""
         self.reset_buf.fill_(True)   # in place: the buffer is a view of _out_pack (the reference allocates a new one)
 
-    def pre_physics_step(self, actions, record: bool = True, _ctl=None):
+    def pre_physics_step(self, actions, record: bool = True, _ctl=None, _host_out=None):
         """KAMMA_medium.py:596-656 — and, fused behind it, everything post_physics_step computes.
         ``record=False`` suppresses the fused replay append for this step (the wrapper's reset step).
-        ``_ctl`` (rollout.RolloutGraph): device OisStepCtl the kernel takes its per-step scalars and replay row from."""
+        ``_ctl`` (rollout.RolloutGraph): device OisStepCtl the kernel takes its per-step scalars and replay row from.
+        ``_host_out``: device-visible addresses (obs_clipped, rew, reset) of pinned HOST memory the kernel stores this
+        step's results to directly, in place of the task's own device buffers."""
         if self._env is not None and hasattr(self._env, "world") and not self._env.world.is_playing():
             return
         if not (actions.is_cuda and actions.dtype == torch.float32 and actions.is_contiguous()
@@ -332,6 +334,8 @@ class TorqueDistributionTask:
         io.clip_obs = self.clip_obs if math.isfinite(self.clip_obs) else -1.0
         self.obs_clipped = self._obs_clipped[0 if _ctl is not None else self._launches & 1]
         io.obs_clipped = self.obs_clipped.data_ptr()
+        if _host_out is not None:
+            io.obs_clipped, io.rew, io.reset = _host_out
         if self._replay is not None and record:
             m = self._replay
             r = m.memory_index if _ctl is None else 0   # with a ctl block the kernel offsets the base by ctl->replay_row
@@ -355,8 +359,8 @@ class TorqueDistributionTask:
         self.progress_buf += 1
         return self.obs_buf, self.rew_buf, self.reset_buf, self.extras
 
-    def step(self, actions, record: bool = True, _ctl=None):
-        self.pre_physics_step(actions, record, _ctl)
+    def step(self, actions, record: bool = True, _ctl=None, _host_out=None):
+        self.pre_physics_step(actions, record, _ctl, _host_out)
         return self.obs_buf, self.rew_buf, self.reset_buf, self.extras
 
     def get_observations(self):   # :825-869

@@ -10,7 +10,7 @@ Issued call by call, that is two C-ABI calls plus (with a host in the loop) four
 the GPU work is ~30 us and the host issue cost is of the same order.  Captured once, the step is one
 ``cudaGraphLaunch``.  A captured launch has frozen arguments, so everything that changes from step to step (Philox
 offsets, the decayed exploration scale, the replay ring slot, the eval flag slot) lives in a device-resident
-``OisStepCtl`` block (include/ois_b200.h) that a single-thread kernel at the end of the captured step advances.
+``OisStepCtl`` block (include/ois_b200.h) that the last CTA of the env kernel to finish advances to the next step.
 The host mirrors (``agent._act_calls``, ``task._launches``, ``memory.memory_index`` / ``filled``) are advanced
 arithmetically per replay, so eager calls and graph replays can be interleaved and produce the same stream of results
 as eager calls alone (tests/test_rollout_graph_gpu.py checks bit-equality).
@@ -32,8 +32,11 @@ class RolloutGraph:
     """``host_io=False``: device-resident loop — ``step()`` returns the (fixed) device tensors
     ``(next_states, rewards[N,1], terminated[N,1])`` without synchronising.
     ``host_io=True``: the observations of each step arrive in the pinned host tensor ``h_states`` (the caller fills it
-    before ``step()``), and the step's results are returned in pinned host tensors after ONE packed device->host copy
-    and a synchronise — the host-in-the-loop shape ``bench.py`` times as ``e2e``."""
+    before ``step()``), and the step's results are returned in pinned host tensors after a synchronise — the
+    host-in-the-loop shape ``bench.py`` times as ``e2e``.  The two kernels access the pinned buffers in place (zero-copy:
+    the actor kernel loads its rows of ``h_states`` over PCIe, the env kernel stores obs | rew | reset straight to host
+    memory), so the graph is two kernel nodes; every byte still crosses the bus every step, but without the copy-engine
+    round trips.  ``host_io="copy"`` keeps explicit copy nodes instead (H2D of the observations, ONE packed D2H)."""
 
     def __init__(self, env, agent, timestep: int, timesteps: int, host_io: bool = False):
         task = env.task
@@ -72,7 +75,7 @@ class RolloutGraph:
         """Host -> device copy of the block for the NEXT step, from the host mirrors (so eager steps may have run)."""
         a, t, m = self.agent, self.task, self.memory
         c = L.StepCtl()
-        c.step = 0
+        c.step, c.self_advance, c.ticket = 0, 1, 0
         c.env_philox_offset, c.act_philox_offset = t._launches, a._act_calls
         c.replay_row, c.replay_rows = m.memory_index, m.memory_size
         c.flag_slot = t._launches % 3
@@ -94,16 +97,20 @@ class RolloutGraph:
     def _issue(self):
         """The launches of one step, on the current stream (eagerly once to warm up, then under capture)."""
         ctl = self._ctl.data_ptr()
-        if self.host_io:
+        n = self.task.num_envs
+        if self.host_io == "copy":
             self._d_states.copy_(self.h_states, non_blocking=True)
-            states = self._d_states
-        else:
-            states = self.states
-        self.agent.act(states, self.timestep, self.timesteps, _ctl=ctl, _out=self._actions)
-        self.task.step(self._actions, True, _ctl=ctl)
-        L.check(L.lib().ois_step_ctl_advance(ctl, L.current_stream()))
-        if self.host_io:
+            self.agent.act(self._d_states, self.timestep, self.timesteps, _ctl=ctl, _out=self._actions)
+            self.task.step(self._actions, True, _ctl=ctl)
             self._h_pack.copy_(self.task._out_pack, non_blocking=True)
+        elif self.host_io:
+            hp = self._h_pack.data_ptr()                 # pinned memory: the same address is valid on the device (UVA)
+            self.agent.act(self.h_states, self.timestep, self.timesteps, _ctl=ctl, _out=self._actions,
+                           _states_ptr=self.h_states.data_ptr())
+            self.task.step(self._actions, True, _ctl=ctl, _host_out=(hp, hp + n * 24, hp + n * 28))
+        else:
+            self.agent.act(self.states, self.timestep, self.timesteps, _ctl=ctl, _out=self._actions)
+            self.task.step(self._actions, True, _ctl=ctl)
 
     def _host_state(self):
         t, a, m = self.task, self.agent, self.memory
@@ -134,7 +141,6 @@ class RolloutGraph:
         m.advance()
         t.obs_clipped = t._obs_clipped[0]
         self.env._obs = t.obs_clipped
-        self.kernel_launches += 1             # the ctl-advance kernel
         self.timestep += 1
         self._mirror = (t._launches, a._act_calls, m.memory_index, self.timestep)
 

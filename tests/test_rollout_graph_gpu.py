@@ -119,15 +119,17 @@ def test_graph_replay_interleaves_with_eager_steps_and_updates():
     assert_worlds_equal(wa, wb)
 
 
-def test_graph_replay_with_host_buffers():
-    """host_io: observations in through pinned memory, (obs | rew | reset) out with one packed copy."""
+@pytest.mark.parametrize("mode", [True, "copy"], ids=["zero-copy", "copy-nodes"])
+def test_graph_replay_with_host_buffers(mode):
+    """host_io: observations in through pinned host memory, (obs | rew | reset) out to pinned host memory — read and
+    written in place by the kernels (zero-copy) or through an H2D and ONE packed D2H copy node."""
     import torch
 
     from options_in_simulation_b200.rollout import RolloutGraph
 
     wa = make_world("KAMMA_medium", 4096, "bf16")
     wb = make_world("KAMMA_medium", 4096, "bf16")
-    g = RolloutGraph(wb["env"], wb["agent"], timestep=1000, timesteps=T_TOTAL, host_io=True)
+    g = RolloutGraph(wb["env"], wb["agent"], timestep=1000, timesteps=T_TOTAL, host_io=mode)
     g.h_states.copy_(wb["obs"])
     for k in range(8):
         oa, ra, da = eager_step(wa, 1000 + k)

@@ -40,7 +40,8 @@ extern "C" {
 
 enum { OIS_BLEND_LINEAR = 0, OIS_BLEND_SWITCH = 1 };          /* KA_DDPG_1D.py:633 | KAMMA_medium.py:632-636 */
 enum { OIS_GAMMA_CONST = 0, OIS_GAMMA_DECAY = 1 };            /* KAMMA_medium.py:627-628 */
-enum { OIS_CMD_RAND = 0, OIS_CMD_GV = 1, OIS_CMD_EVAL = 2 };  /* KAMMA_medium.py:569-575 | KAMMA_curr1.py:577-599 | KAMMA_eval.py:545-550 */
+enum { OIS_CMD_RAND = 0, OIS_CMD_GV = 1, OIS_CMD_EVAL = 2, OIS_CMD_BD = 3 };
+/* KAMMA_medium.py:569-575 | KAMMA_curr1.py:577-599 (box, "gv") | KAMMA_eval.py:545-550 | KAMMA_curr2.py:601-641 (bimodal, "bd") */
 enum { OIS_RELABEL_NONE = 0, OIS_RELABEL_EXECUTED = 1 };      /* base_KA.py | base_KA_DDPG.py:212 */
 
 typedef struct OisEnvParams {
@@ -114,7 +115,9 @@ typedef struct OisEnvIO {
   /* inputs */
   const float* actions;         /* [N,act_dim] */
   const float* rand_mask;       /* [N] uniforms of KAMMA_medium.py:633, or NULL -> in-kernel Philox */
-  const float* reset_uniforms;  /* [N,8] draws of reset_idx in reference order, or NULL -> Philox */
+  const float* reset_uniforms;  /* [N,8] draws of reset_idx in reference order, or NULL -> Philox.  Column 6 is the uniform of
+                                   sample_velocity_command (OIS_CMD_BD: the mode choice `rand < 0.5`), column 7 is unused
+                                   except for OIS_CMD_BD, where it holds the STANDARD NORMAL behind torch.normal */
   uint64_t philox_seed, philox_offset;
   /* outputs */
   float* obs;                   /* [N,6] in/out (raw obs_buf): read as the previous observation when replay_states != NULL */

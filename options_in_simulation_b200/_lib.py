@@ -17,7 +17,7 @@ OIS_EP_STATS_LEN = 24
 OIS_COMP0_LEN = 32
 BLEND_LINEAR, BLEND_SWITCH = 0, 1
 GAMMA_CONST, GAMMA_DECAY = 0, 1
-CMD_RAND, CMD_GV, CMD_EVAL = 0, 1, 2
+CMD_RAND, CMD_GV, CMD_EVAL, CMD_BD = 0, 1, 2, 3
 RELABEL_NONE, RELABEL_EXECUTED = 0, 1
 ACT_NONE, ACT_SIGMOID, ACT_TANH = 0, 1, 2
 PRECISION_FP32, PRECISION_BF16 = 0, 1

@@ -43,6 +43,18 @@ SCRIPTS = {
     ("kamma", "4d", "fifo", "gv", "rlil"): dict(
         script="train/train_kamma_4d_fifo_gv_RLIL.py", variant="KAMMA_curr1", memory=("fifo", 10_000), ou=0.05,
         T_e=5e5, random_timesteps=80, timesteps=600_000, checkpoint_interval=500_000),
+    ("kamma", "4d", "fifo", "bd", "rlil"): dict(
+        script="train/train_kamma_4d_fifo_bd_RLIL.py", variant="KAMMA_curr2", memory=("fifo", 10_000), ou=0.05,
+        T_e=5e5, random_timesteps=80, timesteps=600_000, checkpoint_interval=500_000),
+    ("kamma", "4d", "nofifo", "bd", "rlil"): dict(
+        script="train/train_kamma_4d_nofifo_bd_RLIL.py", variant="KAMMA_curr2", memory=("random", 1_000_000), ou=0.1,
+        T_e=5e5, random_timesteps=80, timesteps=500_000, checkpoint_interval=500_000),
+    ("kamma", "4d", "nofifo", "gv", "rlil"): dict(
+        script="train/train_kamma_4d_nofifo_gv_RLIL.py", variant="KAMMA_curr1", memory=("random", 1_000_000), ou=0.1,
+        T_e=5e5, random_timesteps=80, timesteps=500_000, checkpoint_interval=500_000),
+    ("kamma", "4d", "nofifo", "random", "il"): dict(
+        script="train/train_kamma_4d_nofifo_random_IL.py", variant="KAMMA_g1d_g21", memory=("random", 1_000_000), ou=0.05,
+        T_e=4e5, random_timesteps=80, timesteps=600_000, checkpoint_interval=400_000),
 }
 EVAL = {("kamma", "4d"): dict(script="eval/eval_kamma_4d.py", variant="KAMMA_eval", timesteps=50_000, output="tanh")}
 

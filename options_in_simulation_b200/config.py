@@ -37,6 +37,7 @@ VARIANTS = {
     "KAMMA_medium": EnvVariant("KAMMA_medium", 4, L.BLEND_SWITCH, _D, 1.0, _D, 1.0, 1, L.CMD_RAND, 500000.0),
     "KAMMA": EnvVariant("KAMMA", 4, L.BLEND_SWITCH, _D, 1.0, _D, 1.0, 1, L.CMD_RAND, 400000.0),
     "KAMMA_curr1": EnvVariant("KAMMA_curr1", 4, L.BLEND_SWITCH, _D, 1.0, _D, 1.0, 1, L.CMD_GV, 500000.0),
+    "KAMMA_curr2": EnvVariant("KAMMA_curr2", 4, L.BLEND_SWITCH, _D, 1.0, _D, 1.0, 1, L.CMD_BD, 500000.0),
     "KAMMA_g1d_g21": EnvVariant("KAMMA_g1d_g21", 4, L.BLEND_SWITCH, _D, 1.0, _K, 1.0, 1, L.CMD_RAND, 500000.0),
     "KAMMA_g11_g21": EnvVariant("KAMMA_g11_g21", 4, L.BLEND_SWITCH, _K, 1.0, _K, 1.0, 1, L.CMD_RAND, 500000.0),
     "KAMMA_eval": EnvVariant("KAMMA_eval", 4, L.BLEND_SWITCH, _K, 0.0, _K, 0.0, 1, L.CMD_EVAL, 50000.0, eval_sums=True),

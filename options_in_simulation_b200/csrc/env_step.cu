@@ -144,7 +144,7 @@ __device__ __forceinline__ float warp_sum(float v) {
 
 // reset_idx draws in reference order: pos x, pos y, angle, cmd x, cmd y, heading, loop x  (KAMMA_medium.py:424-456,571)
 struct ResetDraws {
-  float u[7];
+  float u[8];   // [7] is a standard normal, used by OIS_CMD_BD only
 };
 
 __device__ __forceinline__ void apply_reset(const OisEnvParams& p, const ResetDraws& d, int64_t sim_after, Skid& s,
@@ -173,6 +173,14 @@ __device__ __forceinline__ void apply_reset(const OisEnvParams& p, const ResetDr
     const float xmin = sub(c, mul((float)((double)c - (double)p.x_lo), factor));
     const float xmax = add(c, mul((float)((double)p.x_hi - (double)c), factor));
     x = add(mul(sub(xmax, xmin), d.u[6]), xmin);
+  } else if (p.command_mode == OIS_CMD_BD) {       // KAMMA_curr2.py:601-641 (bimodal "grid" sampling), per-env progress
+    // two modes that drift from the centre of the range to its ends; rand < 0.5 picks the mode, torch.normal(mean, 0.05)
+    // = randn * std + mean draws around it (the omega draws that follow are discarded by the reference: omega = 0)
+    const float progress = fminf(1.0f, dvd((float)sim_after, p.max_sim_steps));
+    const double c = ((double)p.x_lo + (double)p.x_hi) / 2.0;
+    const float left = sub((float)c, mul(progress, (float)(c - (double)p.x_lo)));
+    const float right = add((float)c, mul(progress, (float)((double)p.x_hi - c)));
+    x = add(mul(d.u[7], 0.05f), d.u[6] < 0.5f ? left : right);
   } else {                                          // KAMMA_eval.py:545-550
     const float progress = clipf(dvd((float)sim_after, p.max_sim_steps), 0.0f, 1.0f);
     x = add(1.0f, mul(progress, 1.0f));
@@ -186,6 +194,8 @@ __device__ __forceinline__ ResetDraws philox_reset_draws(uint64_t seed, uint64_t
   const uint4 second = Philox(seed)((uint64_t)env, offset * 4 + 1);
   d.u[0] = u01(first.y); d.u[1] = u01(first.z); d.u[2] = u01(first.w);
   d.u[3] = u01(second.x); d.u[4] = u01(second.y); d.u[5] = u01(second.z); d.u[6] = u01(second.w);
+  const uint4 third = Philox(seed)((uint64_t)env, offset * 4 + 2);   // resets are rare: drawn whether or not BD needs it
+  d.u[7] = normal2(third.x, third.y).x;
   return d;
 }
 
@@ -472,7 +482,7 @@ env_step_kernel(const __grid_constant__ OisEnvParams p, const __grid_constant__ 
       if (io.reset_uniforms) {
         const float4 ua = __ldcs(reinterpret_cast<const float4*>(io.reset_uniforms + 8 * i));
         const float4 ub = __ldcs(reinterpret_cast<const float4*>(io.reset_uniforms + 8 * i + 4));
-        d.u[0] = ua.x; d.u[1] = ua.y; d.u[2] = ua.z; d.u[3] = ua.w; d.u[4] = ub.x; d.u[5] = ub.y; d.u[6] = ub.z;
+        d.u[0] = ua.x; d.u[1] = ua.y; d.u[2] = ua.z; d.u[3] = ua.w; d.u[4] = ub.x; d.u[5] = ub.y; d.u[6] = ub.z; d.u[7] = ub.w;
       } else {   // resets are rare: the first Philox block is recomputed here rather than held across the physics
         d = philox_reset_draws(io.philox_seed, env_philox_offset(io), i, Philox(io.philox_seed)((uint64_t)i, env_philox_offset(io) * 4));
       }
@@ -592,7 +602,7 @@ reset_idx_kernel(const __grid_constant__ OisEnvParams p, const __grid_constant__
     const int64_t i = ids[t];
     ResetDraws d;
     if (uniforms) {
-      for (int k = 0; k < 7; ++k) d.u[k] = uniforms[8 * i + k];
+      for (int k = 0; k < 8; ++k) d.u[k] = uniforms[8 * i + k];
     } else {
       d = philox_reset_draws(seed, offset, i, Philox(seed)((uint64_t)i, offset * 4));
     }

@@ -52,7 +52,7 @@ class EnvVariant:
     gamma1: str             # "decay" | "one" | "zero"  (action assist)
     gamma2: str             # "decay" | "one" | "zero"  (reward assist)
     guiding: str            # "pre" clip (KA_DDPG_1D.py:642) | "post" clip (KAMMA_medium.py:656)
-    command: str            # "rand" | "gv" (KAMMA_curr1.py:577-599) | "eval" (KAMMA_eval.py:545-550)
+    command: str            # "rand" | "gv" (KAMMA_curr1.py:577-599) | "bd" (KAMMA_curr2.py:601-641) | "eval" (KAMMA_eval.py:545-550)
     max_sim_steps: float
     eval_sums: bool = False
     action_low: float = 0.0
@@ -65,6 +65,7 @@ VARIANTS = {
     "KAMMA_medium": EnvVariant("KAMMA_medium", 4, "switch", "decay", "decay", "post", "rand", 500000.0),
     "KAMMA": EnvVariant("KAMMA", 4, "switch", "decay", "decay", "post", "rand", 400000.0),
     "KAMMA_curr1": EnvVariant("KAMMA_curr1", 4, "switch", "decay", "decay", "post", "gv", 500000.0),
+    "KAMMA_curr2": EnvVariant("KAMMA_curr2", 4, "switch", "decay", "decay", "post", "bd", 500000.0),
     "KAMMA_g1d_g21": EnvVariant("KAMMA_g1d_g21", 4, "switch", "decay", "one", "post", "rand", 500000.0),
     "KAMMA_g11_g21": EnvVariant("KAMMA_g11_g21", 4, "switch", "one", "one", "post", "rand", 500000.0),
     "KAMMA_eval": EnvVariant("KAMMA_eval", 4, "switch", "zero", "zero", "post", "eval", 50000.0, eval_sums=True),
@@ -331,6 +332,15 @@ class EnvOracle:
             x_min = F(c) - F(c - lo) * factor
             x_max = F(c) + F(hi - c) * factor
             x = (x_max - x_min) * u[:, 6] + x_min
+        elif v.command == "bd":      # KAMMA_curr2.py:601-641 (per-env generalisation of an N=1-only formula)
+            # u[:, 6] is the uniform of `torch.rand(1) < 0.5`, u[:, 7] the standard normal behind torch.normal(mean, 0.05)
+            # (= randn * std + mean); the omega draws that follow are discarded by the reference (omega = 0.0)
+            progress = np.minimum(F(1.0), s.sim_steps[ids].astype(F) / F(v.max_sim_steps))
+            lo, hi = p.x_range
+            c = (lo + hi) / 2.0
+            left = F(c) - progress * F(c - lo)
+            right = F(c) + progress * F(hi - c)
+            x = u[:, 7] * F(0.05) + np.where(u[:, 6] < F(0.5), left, right).astype(F)
         elif v.command == "eval":    # KAMMA_eval.py:545-550
             progress = np.clip(s.sim_steps[ids].astype(F) / F(v.max_sim_steps), F(0.0), F(1.0))
             x = F(1.0) + progress * F(1.0)

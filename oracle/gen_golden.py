@@ -115,8 +115,8 @@ def run_env_case(name: str, n: int, steps: int, *, physics: bool, seed: int, for
     init_u = rng.random((n, 8)).astype(F)
     runner = RefRunner(name, n, physics=physics, init_uniforms=init_u)
     s0 = synth_state(variant, n, rng, physics=physics)
-    if name == "KAMMA_curr1":
-        assert n == 1, "the reference's gv sampler is N=1 only (KAMMA_curr1.py:579)"
+    if name in ("KAMMA_curr1", "KAMMA_curr2"):
+        assert n == 1, "the reference's gv / bd samplers are N=1 only (KAMMA_curr1.py:579, KAMMA_curr2.py:603)"
     load_state_into_reference(runner, variant, s0)
     if force_gamma is not None:     # KA-DDPG 1d/2d: gamma is a frozen attribute (KA_DDPG_1D.py:192,629)
         runner.task.gamma_assist = torch.full((n,), float(force_gamma))
@@ -135,6 +135,8 @@ def run_env_case(name: str, n: int, steps: int, *, physics: bool, seed: int, for
         rm = rng.random(n).astype(F)
         # put some uniforms exactly around gamma to exercise the rand < gamma compare
         ru = rng.random((n, 8)).astype(F)
+        if variant.command == "bd":     # column 7 is the standard normal behind torch.normal (KAMMA_curr2.py:617-619)
+            ru[:, 7] = rng.standard_normal(n).astype(F)
         obs_r, rew_r, reset_r, extras_r = runner.step(act, rand_mask=rm if variant.blend == "switch" else None,
                                                       reset_uniforms=ru)
         obs_o, rew_o, reset_o = oracle.step(act, rm, ru)
@@ -207,16 +209,21 @@ ENV_CASES = [
     ("kamma_curr1_n1_a", "KAMMA_curr1", 1, 6, False, None),
     ("kamma_curr1_n1_b", "KAMMA_curr1", 1, 6, True, None),
     ("kamma_g1d_g21_nophys", "KAMMA_g1d_g21", 32, 3, False, None),
+    ("kamma_curr2_n1_a", "KAMMA_curr2", 1, 6, False, None),        # appended: the seed of a case is 1234 + its index
+    ("kamma_curr2_n1_b", "KAMMA_curr2", 1, 6, True, None),
 ]
 
 
 def main():
     os.makedirs(GOLDEN, exist_ok=True)
+    only = set(sys.argv[1:])            # optional: file tags to (re)generate; default all
     print("env cases (reference vs oracle restatement):")
     for i, (tag, name, n, steps, physics, fg) in enumerate(ENV_CASES):
+        if only and tag not in only:
+            continue
         rec = run_env_case(name, n, steps, physics=physics, seed=1234 + i, force_gamma=fg)
         np.savez_compressed(os.path.join(GOLDEN, f"env_{tag}.npz"), **rec)
-    if os.path.exists(os.path.join(ROOT, 'oracle', 'gen_golden_agent.py')):
+    if not only and os.path.exists(os.path.join(ROOT, 'oracle', 'gen_golden_agent.py')):
         from oracle import gen_golden_agent
 
         gen_golden_agent.main()

@@ -215,11 +215,33 @@ class RefRunner:
                 return rm.clone()
 
             torch.rand = fake_rand
+        orig_normal = torch.normal
+        bimodal = getattr(self.task, "gridsampling", False)     # KAMMA_curr2.py:601-641 draws inside reset_idx
+        calls = {"rand": 0, "normal": 0}
+
+        def reset_rand(*size, **kw):
+            # per reset env: `torch.rand(1) < 0.5` for x (supplied column 6), then once more for the discarded omega
+            assert tuple(size) == (1,), size
+            k = calls["rand"]
+            calls["rand"] += 1
+            env = self._ids[k // 2]
+            return self._uniforms[env, 6].view(1).clone() if k % 2 == 0 else torch.full((1,), 0.75)
+
+        def reset_normal(mean, std, **kw):
+            # torch.normal(mean, std) == randn * std + mean; the standard normal is supplied column 7 (x draw only)
+            k = calls["normal"]
+            calls["normal"] += 1
+            env = self._ids[k // 2]
+            z = self._uniforms[env, 7] if k % 2 == 0 else torch.tensor(0.0)
+            return (z * std + mean).to(torch.float32)
+
         try:
             with contextlib.redirect_stdout(io.StringIO()):     # KAMMA_eval prints every step
                 self.task.pre_physics_step(torch.as_tensor(self.np.asarray(actions, dtype=self.np.float32)))
                 torch.rand = orig_rand
+                if bimodal:
+                    torch.rand, torch.normal = reset_rand, reset_normal
                 out = self.task.post_physics_step()
         finally:
-            torch.rand = orig_rand
+            torch.rand, torch.normal = orig_rand, orig_normal
         return out

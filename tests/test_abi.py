@@ -62,3 +62,16 @@ def test_sass_is_sm100a(built_lib):
 
     out = subprocess.run(["cuobjdump", "-lelf", LIB_PATH], capture_output=True, text=True).stdout
     assert "sm_100a" in out and "sm_90" not in out and "sm_80" not in out
+
+
+def test_abi_version_is_stated_consistently(built_lib):
+    """include/ois_b200.h, the ctypes loader, __graft_entry__.build() and INTEGRATION.md must agree."""
+    import re
+
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    ver = int(re.search(r"#define OIS_ABI_VERSION (\d+)", open(os.path.join(root, "include", "ois_b200.h")).read()).group(1))
+    assert built_lib.ois_abi_version() == ver
+    for rel in ("__graft_entry__.py", "INTEGRATION.md", os.path.join("options_in_simulation_b200", "_lib.py")):
+        text = open(os.path.join(root, rel)).read()
+        found = re.findall(r"ois_abi_version\(\) [!=]= (\d+)", text)
+        assert found and all(int(v) == ver for v in found), (rel, found)

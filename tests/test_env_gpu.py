@@ -72,7 +72,7 @@ def test_env_kernel_matches_reference_golden(fname):
 
 
 @pytest.mark.parametrize("name,n", [("KAMMA_medium", 4096), ("KA_DDPG_2D", 4096), ("KA_DDPG_1D", 64),
-                                     ("KAMMA_eval", 8192), ("KAMMA_curr1", 16384), ("KAMMA_medium", 4097),
+                                     ("KAMMA_eval", 8192), ("KAMMA_curr1", 16384), ("KAMMA_curr2", 4096), ("KAMMA_medium", 4097),
                                      ("KAMMA_medium", 1)])
 def test_env_kernel_matches_oracle_at_bench_sizes(name, n):
     """Seeded synthetic state, 6 closed-loop steps, physics on: CUDA fp32 vs numpy oracle

@@ -57,7 +57,7 @@ def test_env_oracle_matches_reference_vectors(fname):
 
 def test_golden_covers_all_blend_and_command_modes():
     seen = {str(np.load(os.path.join(GOLDEN, f))["variant"]) for f in golden_files()}
-    assert {"KAMMA_medium", "KAMMA_eval", "KAMMA_curr1", "KA_DDPG_1D", "KA_DDPG_2D", "KA_DDPG_4D"} <= seen
+    assert {"KAMMA_medium", "KAMMA_eval", "KAMMA_curr1", "KAMMA_curr2", "KA_DDPG_1D", "KA_DDPG_2D", "KA_DDPG_4D"} <= seen
 
 
 def test_dynamics_twin_float32_tracks_float64():

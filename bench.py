@@ -242,6 +242,19 @@ def device_timed(world, steps, warmup, flush):
     return sum(a.elapsed_time(b) for a, b in ev) / steps, world.launches() - l0
 
 
+def host_issue_timed(world, steps=300):
+    """Host time to ISSUE one call-by-call step (no synchronisation inside the loop; 2 launches per step, so the
+    driver's launch queue never fills): when this approaches ms_per_step the loop is host-bound."""
+    torch = world.torch
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        world.step()
+    dt = time.perf_counter() - t0
+    torch.cuda.synchronize()
+    return 1e3 * dt / steps
+
+
 def kernel_split(world, steps, flush):
     """Per-kernel-group durations (act vs env) with events between the two launches."""
     torch = world.torch
@@ -259,7 +272,7 @@ def kernel_split(world, steps, flush):
         acts.append((e[0], e[1]))
         envs.append((e[1], e[2]))
     torch.cuda.synchronize()
-    f = lambda L: sum(a.elapsed_time(b) for a, b in L) / len(L)
+    f = lambda L: sorted(a.elapsed_time(b) for a, b in L)[len(L) // 2]      # median: the first iterations warm up
     return f(acts), f(envs)
 
 
@@ -423,7 +436,7 @@ def main():
             dist.barrier()
         torch.cuda.synchronize()
 
-    sampler = ClockSampler(local)
+    sampler = ClockSampler(local) if rank == 0 else None     # one nvidia-smi poller per job, not one per rank
     barrier()
     if rank == 0:
         sampler.start()
@@ -436,12 +449,26 @@ def main():
     barrier()
     e2e_copy_ms, _, _ = e2e_graph_timed(world, min(args.steps, 200), 5, mode="copy")
     barrier()
-    graph_ms = graph_device_timed(world, min(args.steps, 200), 5, flush)
+    graph_ms = graph_device_timed(world, args.steps, 5, flush)
     barrier()
+    host_ms = host_issue_timed(world)
+    barrier()
+    per_rank = [[ms, graph_ms, host_ms]]
     if world_size > 1:
+        mine = torch.tensor(per_rank[0], device=device, dtype=torch.float64)
+        allr = [torch.empty_like(mine) for _ in range(world_size)]
+        dist.all_gather(allr, mine)
+        per_rank = [a.tolist() for a in allr]
         t = torch.tensor([ms, e2e_ms, e2e_eager_ms, graph_ms, e2e_copy_ms], device=device, dtype=torch.float64)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         ms, e2e_ms, e2e_eager_ms, graph_ms, e2e_copy_ms = t.tolist()
+    # the same device-resident step issued two ways, both timed over EXACTLY args.steps steps, max over ranks: call by
+    # call (2 launches per step from Python) and as one graph launch per step; the headline is the faster of the two
+    # (with several ranks sharing a host the call-by-call loop becomes host-bound on the slowest rank)
+    call_ms = ms
+    issue = "call-by-call (agent.act + env.step)"
+    if graph_ms < ms:
+        ms, issue, launches = graph_ms, "rollout.RolloutGraph replay (one graph launch per step)", 2 * args.steps
     value = world_size * n * 1e3 / ms
     e2e_value = world_size * n * 1e3 / e2e_ms
 
@@ -453,7 +480,7 @@ def main():
         "config": {"workload": wl["name"], "envs_per_gpu": n, "variant": wl["variant"], "act_dim": wl["act_dim"],
                    "replay": "fused append, rank-local shard", "rng": "in-kernel Philox",
                    "l2": "flushed between timed steps (256 MiB memset outside the event brackets)",
-                   "parallelism": f"env/replay shards x{world_size}, no data-path collective"},
+                   "parallelism": f"env/replay shards x{world_size}, no data-path collective", "issue": issue},
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                 "ms_per_step": e2e_ms,
                 "path": "rollout.RolloutGraph(host_io=True): one CUDA-graph launch per step = actor kernel reading the "
@@ -463,9 +490,10 @@ def main():
                 "copy_nodes_ms_per_step": e2e_copy_ms,
                 "call_by_call_ms_per_step": e2e_eager_ms,
                 "call_by_call_value": world_size * n * 1e3 / e2e_eager_ms},
-        "graph_replay": {"ms_per_step": graph_ms, "value": world_size * n * 1e3 / graph_ms,
-                         "note": "the device-resident step replayed through rollout.RolloutGraph (2 kernels per replay); "
-                                 "`value` itself is the call-by-call path"},
+        "issue_paths": {"call_by_call_ms_per_step": call_ms, "graph_replay_ms_per_step": graph_ms,
+                        "host_issue_ms_per_step": max(r[2] for r in per_rank),
+                        "per_rank_ms": [[round(x, 5) for x in r] for r in per_rank],
+                        "note": "max over ranks; per_rank_ms = [call-by-call, graph replay, host issue time] per rank"},
         "gpu_launches": launches, "clocks": clocks,
     }
 

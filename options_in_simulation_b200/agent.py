@@ -521,7 +521,7 @@ class DDPG:
                 self._noise_stats.copy_(torch.tensor([-math.inf, math.inf, 0.0]))
                 io.noise_stats = self._noise_stats.data_ptr()
         L.check(L.lib().ois_agent_act(self._handle, L.ptr(self.policy.flat), self._scaler_ref(), C.byref(io), n,
-                                      L.current_stream()))
+                                      L.current_stream(self.device.index)))
         self._act_calls += 1
         self.kernel_launches += self._act_launches(random_phase, noise is not None)
         if track and noise is not None and not random_phase:   # ddpg.py:258-266
@@ -539,7 +539,7 @@ class DDPG:
         if random_phase:
             return 1
         if self._mixed_precision:
-            return 1 + (1 if has_noise else 0)
+            return 1          # scaler, MLP, OU noise and clamp are ONE tensor-core kernel (csrc/mlp_tc.cu)
         return (1 if self._state_preprocessor is not None else 0) + 4 + (1 if has_noise else 0)
 
     def record_transition(self, states, actions, rewards, next_states, terminated, truncated, infos, timestep, timesteps):

@@ -39,6 +39,7 @@ class Memory:
         self.kernel_launches = 0
         self._out = None
         self._supplied_indexes = collections.deque()
+        self.generation = 0             # bumped whenever a tensor is (re)created: cached device addresses go stale
 
     def __len__(self) -> int:   # skrl Memory.__len__
         return self.memory_size * self.num_envs if self.filled else self.memory_index * self.num_envs + self.env_index
@@ -51,6 +52,7 @@ class Memory:
             t.fill_(float("nan"))   # skrl fills float tensors with NaN
         self.tensors[name] = t
         self.tensors_view[name] = t.view(-1, size)
+        self.generation += 1
         return True
 
     def get_tensor_by_name(self, name: str, keepdim: bool = True):

@@ -150,6 +150,37 @@ def time_cpu_port(wl, n, budget_s=12.0, min_steps=3, max_steps=200):
     return n * k / dt, k, dt
 
 
+def time_cpu_parts(wl, n, reps=20):
+    """the CPU port timed piece by piece on the same workload — env step only, actor only, one DDPG
+    update (B = 512) — so that each GPU number has its own CPU number beside it (ms per call, all host threads)."""
+    import numpy as np
+    import torch
+
+    from oracle.agent_oracle import synth_transitions
+
+    port = CpuPort(wl, n)
+    port.step()
+    A = wl["act_dim"]
+    z = port.rng.standard_normal((n, A), dtype=np.float32)
+    acts = port.agent.act(port.obs, 1000, 600000, normals=z).numpy()
+    rm, ru = port.rng.random(n, dtype=np.float32), port.rng.random((n, 8), dtype=np.float32)
+
+    def timed(fn, k):
+        fn()
+        t0 = time.perf_counter()
+        for _ in range(k):
+            fn()
+        return 1e3 * (time.perf_counter() - t0) / k
+
+    env_ms = timed(lambda: port.env.step(acts, rm, ru), reps)
+    act_ms = timed(lambda: port.agent.act(port.obs, 1000, 600000, normals=z), reps)
+    batch = synth_transitions(512, 6, A, torch.Generator().manual_seed(3))
+    upd_ms = timed(lambda: port.agent.update(**batch), reps)
+    return {"env_step_ms": env_ms, "act_ms": act_ms, "update_ms": upd_ms,
+            "train_step_ms": env_ms + act_ms + 2 * upd_ms, "envs": n, "batch": 512,
+            "note": "CPU port (oracle/), ms per call; train_step = env + act + 2 updates (reference cadence)"}
+
+
 def run_reference(args, wl, n):
     """Reference arm: the CPU implementation on the box's host cores (rank 0 only)."""
     if int(os.environ.get("RANK", "0")) != 0:
@@ -540,7 +571,8 @@ def main():
         if not args.no_extras:
             v, k, dt = time_cpu_port(wl, n)
             out["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": os.cpu_count() or 1, "kind": "port",
-                                   "sample": f"{k} steps x {n} envs in {dt:.1f} s (numpy env oracle + CPU-torch actor, oracle/)"}
+                                   "sample": f"{k} steps x {n} envs in {dt:.1f} s (numpy env oracle + CPU-torch actor, oracle/)",
+                                   "parts": time_cpu_parts(wl, n)}
         print(json.dumps(out), flush=True)
     if world_size > 1:
         dist.barrier()

@@ -25,7 +25,7 @@
 namespace ois {
 namespace tcu {
 
-constexpr int kThreads = 192;
+constexpr int kThreads = 320;   // warp 0 producer, warp 1 MMA issuer, warps 2-9 epilogue (two per TMEM lane quadrant)
 constexpr int kStages = 3;
 constexpr int kHalfStage = 32768;
 constexpr int kStageBytes = 2 * kHalfStage;           // A (128 x 128 bf16) + B (<= 128 x 128 bf16)
@@ -161,7 +161,8 @@ tc_gemm_kernel(const __grid_constant__ Group g) {
       __syncwarp();
     }
   } else {
-    // ===================================================== epilogue: one warp per TMEM lane quadrant
+    // ===================================================== epilogue: two warps per TMEM lane quadrant, each takes half of
+    // the tile's 16-column chunks (the epilogue is the serial tail of every launch of the update's dependent chain)
     // (parameter fields are copied to registers once: the inline-PTX wrappers carry memory clobbers, which would
     //  otherwise force a re-load of every P.field after each of them)
     const int epi = P.epi, Ncols = P.N, ld = P.ld, m_valid = P.m_valid, n_valid = P.n_valid, transposed = P.transposed;
@@ -172,6 +173,7 @@ tc_gemm_kernel(const __grid_constant__ Group g) {
     uint8_t* const x_out = P.x_out;
     float* const out_f32 = P.out_f32;
     const int quad = warp & 3;
+    const int half = (warp - 2) >> 2;       // chunks [4 * half, 4 * half + 4)
     const int m = quad * 32 + lane;
     const int gm = tm * 128 + m;
     const int n0 = tn * tile_n;
@@ -181,23 +183,27 @@ tc_gemm_kernel(const __grid_constant__ Group g) {
     const int et = threadIdx.x - 64;
     if (epi == EPI_HIDDEN || epi == EPI_OUT)
       if (et < tile_n) s_bias[et] = (n0 + et < n_valid || epi == EPI_HIDDEN) ? bias[n0 + et] : 0.f;
-    uint4 hreg[16];
+    uint4 hreg[8];
     if (epi == EPI_DGRAD) {
       const uint4* hp = reinterpret_cast<const uint4*>(hsrc + chunk_off(gm, n0 >> 3, Ncols >> 3, 128));
 #pragma unroll
-      for (int c = 0; c < 16; ++c) hreg[c] = (c * 8 < tile_n) ? hp[c * 128] : make_uint4(0, 0, 0, 0);
+      for (int c = 0; c < 8; ++c) hreg[c] = ((half * 8 + c) * 8 < tile_n) ? hp[(half * 8 + c) * 128] : make_uint4(0, 0, 0, 0);
     }
-    asm volatile("bar.sync 1, 128;" ::: "memory");      // the four epilogue warps only: s_bias is complete
+    asm volatile("bar.sync 1, 256;" ::: "memory");      // the eight epilogue warps only: s_bias is complete
     ptx::mbar_wait(d_full, 0);
     ptx::tc_fence_after();
     TCU_STAMP(tr && warp == 2, 8);
+    uint32_t v4[4][16];                     // all of this warp's accumulator columns in flight at once, ONE wait
 #pragma unroll
-    for (int c = 0; c < 8; ++c) {
+    for (int cc = 0; cc < 4; ++cc)
+      if ((half * 4 + cc) * 16 < tile_n) ptx::tmem_ld16(t_lane + (half * 4 + cc) * 16, v4[cc]);
+    ptx::tmem_ld_wait();
+#pragma unroll
+    for (int cc = 0; cc < 4; ++cc) {
+      const int c = half * 4 + cc;
       const int c0 = c * 16;
       if (c0 >= tile_n) break;
-      uint32_t v[16];
-      ptx::tmem_ld16(t_lane + c0, v);
-      ptx::tmem_ld_wait();
+      uint32_t (&v)[16] = v4[cc];
       const int n = n0 + c0;
       if (epi == EPI_HIDDEN || epi == EPI_DGRAD) {
         float x[16];
@@ -211,7 +217,7 @@ tc_gemm_kernel(const __grid_constant__ Group g) {
             x[j] = z > 0.f ? z : ez - 1.0f;
           }
         } else {
-          const uint4 h0 = hreg[2 * c], h1 = hreg[2 * c + 1];
+          const uint4 h0 = hreg[2 * cc], h1 = hreg[2 * cc + 1];
           const uint32_t hw[8] = {h0.x, h0.y, h0.z, h0.w, h1.x, h1.y, h1.z, h1.w};
 #pragma unroll
           for (int j = 0; j < 8; ++j) {

@@ -127,11 +127,20 @@ tc_gemm_kernel(const __grid_constant__ Group g) {
         uint8_t* sb = sa + kHalfStage;
         const uint8_t* ga = P.a_mn ? P.a + ((size_t)(s * P.a_c8 + tm * 16) * P.a_rb) * 16
                                    : P.a + ((size_t)(tm * P.a_c8 + s * (k_stage >> 3)) * P.a_rb) * 16;
-        const uint8_t* gb = P.b_mn ? P.b + ((size_t)(s * P.b_c8 + tn * (tile_n >> 3)) * P.b_rb) * 16
-                                   : P.b + ((size_t)(tn * P.b_c8 + s * (k_stage >> 3)) * P.b_rb) * 16;
         ptx::mbar_expect_tx(&full[slot], a_bytes + b_bytes);
         ptx::bulk_g2s(sa, ga, a_bytes, &full[slot]);
-        ptx::bulk_g2s(sb, gb, b_bytes, &full[slot]);
+        if (P.b_mn || P.b_rb == tile_n) {
+          const uint8_t* gb = P.b_mn ? P.b + ((size_t)(s * P.b_c8 + tn * (tile_n >> 3)) * P.b_rb) * 16
+                                     : P.b + ((size_t)(tn * P.b_c8 + s * (k_stage >> 3)) * P.b_rb) * 16;
+          ptx::bulk_g2s(sb, gb, b_bytes, &full[slot]);
+        } else {
+          // K-major B whose stored row block (128) is wider than the tile: the tile's rows are a contiguous run inside
+          // every column chunk of the block, so the stage is one copy per chunk (tile_n * 16 bytes each)
+          const int row0 = tn * tile_n;
+          const uint32_t piece = (uint32_t)tile_n * 16u;
+          for (int j = 0; j < (k_stage >> 3); ++j)
+            ptx::bulk_g2s(sb + j * piece, P.b + chunk_off(row0, s * (k_stage >> 3) + j, P.b_c8, P.b_rb), piece, &full[slot]);
+        }
       }
     }
   } else if (warp == 1) {
@@ -173,7 +182,7 @@ tc_gemm_kernel(const __grid_constant__ Group g) {
     uint8_t* const x_out = P.x_out;
     float* const out_f32 = P.out_f32;
     const int quad = warp & 3;
-    const int half = (warp - 2) >> 2;       // chunks [4 * half, 4 * half + 4)
+    const int half = (warp - 2) >> 2;       // takes the 16-column chunks c with (c & 1) == half
     const int m = quad * 32 + lane;
     const int gm = tm * 128 + m;
     const int n0 = tn * tile_n;
@@ -187,7 +196,10 @@ tc_gemm_kernel(const __grid_constant__ Group g) {
     if (epi == EPI_DGRAD) {
       const uint4* hp = reinterpret_cast<const uint4*>(hsrc + chunk_off(gm, n0 >> 3, Ncols >> 3, 128));
 #pragma unroll
-      for (int c = 0; c < 8; ++c) hreg[c] = ((half * 8 + c) * 8 < tile_n) ? hp[(half * 8 + c) * 128] : make_uint4(0, 0, 0, 0);
+      for (int c = 0; c < 8; ++c) {       // 8-column chunk pairs (2c', 2c'+1) of the 16-column chunks c' = 2 * (c >> 1) + half
+        const int k8 = (2 * (c >> 1) + half) * 2 + (c & 1);
+        hreg[c] = (k8 * 8 < tile_n) ? hp[k8 * 128] : make_uint4(0, 0, 0, 0);
+      }
     }
     asm volatile("bar.sync 1, 256;" ::: "memory");      // the eight epilogue warps only: s_bias is complete
     ptx::mbar_wait(d_full, 0);
@@ -196,11 +208,11 @@ tc_gemm_kernel(const __grid_constant__ Group g) {
     uint32_t v4[4][16];                     // all of this warp's accumulator columns in flight at once, ONE wait
 #pragma unroll
     for (int cc = 0; cc < 4; ++cc)
-      if ((half * 4 + cc) * 16 < tile_n) ptx::tmem_ld16(t_lane + (half * 4 + cc) * 16, v4[cc]);
+      if ((2 * cc + half) * 16 < tile_n) ptx::tmem_ld16(t_lane + (2 * cc + half) * 16, v4[cc]);
     ptx::tmem_ld_wait();
 #pragma unroll
     for (int cc = 0; cc < 4; ++cc) {
-      const int c = half * 4 + cc;
+      const int c = 2 * cc + half;
       const int c0 = c * 16;
       if (c0 >= tile_n) break;
       uint32_t (&v)[16] = v4[cc];
@@ -377,7 +389,7 @@ static int validate(const Problem& p) {
   OIS_CHECK_ARG(p.M % 128 == 0 && p.N % p.tile_n == 0 && p.K % k_stage == 0 && p.K % 16 == 0, "bad GEMM extents");
   OIS_CHECK_ARG(p.tile_n % 16 == 0 && p.tile_n >= 16 && p.tile_n <= 128, "bad tile_n");
   OIS_CHECK_ARG(p.a_mn ? p.a_rb == k_stage : p.a_rb == 128, "A operand row block does not match its use");
-  OIS_CHECK_ARG(p.b_mn ? p.b_rb == k_stage : p.b_rb == p.tile_n, "B operand row block does not match its use");
+  OIS_CHECK_ARG(p.b_mn ? p.b_rb == k_stage : p.b_rb % p.tile_n == 0, "B operand row block does not match its use");
   return OIS_OK;
 }
 
@@ -392,9 +404,21 @@ int launch_group(Group& g, cudaStream_t s) {
   return OIS_OK;
 }
 
+// Column width of the output tiles of the 512- and 128-wide problems.  Narrow tiles cut the B bytes, the MMA work and the
+// epilogue of every CTA and multiply the CTAs per launch (B = 512 never fills 148 SMs): measured per update on B200
+// 159.7 us (128), 155.6 us (64), 149.3 us (32).  OIS_TCU_TILE_N overrides the default for experiments.
+static int wide_tile_n() {
+  static const int v = [] {
+    const char* e = getenv("OIS_TCU_TILE_N");
+    const int t = e ? atoi(e) : 32;
+    return (t == 128 || t == 64 || t == 32) ? t : 32;
+  }();
+  return v;
+}
+
 static Problem base_problem() {
   Problem p = {};
-  p.tile_n = 128;
+  p.tile_n = wide_tile_n();
   p.m_valid = p.n_valid = 1 << 30;
   return p;
 }
@@ -408,7 +432,7 @@ static Problem fwd_problem(const OisMlpShape& sh, const float* P32, const uint8_
   Problem p = base_problem();
   p.a = in; p.a_c8 = kin[l] / 8; p.a_rb = 128; p.a_mn = 0;
   p.b = img + wo[l]; p.b_c8 = kin[l] / 8; p.b_rb = l == 3 ? 16 : 128; p.b_mn = 0;
-  p.M = B; p.N = nout[l]; p.K = kin[l]; p.tile_n = l == 3 ? 16 : 128;
+  p.M = B; p.N = nout[l]; p.K = kin[l]; p.tile_n = l == 3 ? 16 : wide_tile_n();
   p.bias = P32 + o.b[l];
   if (l < 3) { p.epi = EPI_HIDDEN; p.out_bf16 = out_bf16; }
   else { p.epi = EPI_OUT; p.out_f32 = y; p.ld = sh.out_dim; p.n_valid = sh.out_dim; p.m_valid = B; p.out_act = sh.out_act; p.x_out = x_out; p.x_col = x_col; }
@@ -483,7 +507,7 @@ static int backward(const OisMlpShape& sh, const uint8_t* img, float* G, const N
       Problem p = base_problem();
       p.a = ds[i]; p.a_c8 = Mw[i] / 8; p.a_rb = 128; p.a_mn = 1;
       p.b = xs[i]; p.b_c8 = Nw[i] / 8; p.b_rb = 128; p.b_mn = 1;
-      p.M = Mw[i]; p.N = Nw[i]; p.K = B; p.tile_n = Nw[i] == 16 ? 16 : 128;
+      p.M = Mw[i]; p.N = Nw[i]; p.K = B; p.tile_n = Nw[i] == 16 ? 16 : wide_tile_n();
       p.epi = EPI_F32; p.out_f32 = G + go[i]; p.ld = nv[i]; p.m_valid = Mw[i]; p.n_valid = nv[i];
       g.p[g.count++] = p;
     }

@@ -45,7 +45,9 @@ def debug_gemm(a_store, a_rb, b_store, b_rb, M, N, K, tile_n, mode, transposed=F
 
 
 @pytest.mark.parametrize("M,N,K,tile_n", [(512, 512, 512, 128), (512, 128, 512, 128), (128, 512, 128, 128), (512, 512, 16, 128),
-                                          (512, 16, 128, 16), (128, 16, 512, 16), (256, 256, 384, 128)])
+                                          (512, 16, 128, 16), (128, 16, 512, 16), (256, 256, 384, 128),
+                                          (512, 512, 512, 64), (512, 128, 512, 64), (128, 512, 128, 64), (512, 512, 16, 64),
+                                          (256, 256, 384, 64), (512, 512, 512, 32)])
 @pytest.mark.parametrize("mode", [0, 1, 2, 3])
 def test_tc_gemm_orientations(M, N, K, tile_n, mode):
     import torch
@@ -56,7 +58,9 @@ def test_tc_gemm_orientations(M, N, K, tile_n, mode):
     B = torch.randn(N, K, generator=g).to(torch.bfloat16).float()
     ref = A @ B.T
     a_store, a_rb = (A.T.contiguous(), k_stage) if mode & 1 else (A, 128)        # stored [K, M]: contraction over rows
-    b_store, b_rb = (B.T.contiguous(), k_stage) if mode & 2 else (B, tile_n)
+    # K-major B: stored in 128-row blocks (as the weight images are) when the tile is narrower than 128 -> the kernel's
+    # one-copy-per-column-chunk path; otherwise row block == tile
+    b_store, b_rb = (B.T.contiguous(), k_stage) if mode & 2 else (B, 128 if tile_n in (32, 64) and N % 128 == 0 else tile_n)
     if a_store.shape[1] % 8 or b_store.shape[1] % 8:
         pytest.skip("stored matrix needs a multiple of 8 columns")
     out = debug_gemm(a_store, a_rb, b_store, b_rb, M, N, K, tile_n, mode)

@@ -28,6 +28,15 @@ import torch
 from . import _lib as L
 
 
+def _device_synchronize():
+    """cudaDeviceSynchronize without the Python layers of torch.cuda.synchronize (this call is on the per-step path)."""
+    fn = getattr(torch._C, "_cuda_synchronize", None)
+    if fn is None:
+        torch.cuda.synchronize()
+    else:
+        fn()
+
+
 class RolloutGraph:
     """``host_io=False``: device-resident loop — ``step()`` returns the (fixed) device tensors
     ``(next_states, rewards[N,1], terminated[N,1])`` without synchronising.
@@ -53,6 +62,7 @@ class RolloutGraph:
         self.host_io = host_io
         self.kernel_launches = 0
         dev, n, A = task.device, task.num_envs, task.num_actions
+        self._dev_index = dev.index
         self._ctl = torch.zeros(C.sizeof(L.StepCtl), dtype=torch.uint8, device=dev)
         self._actions = torch.empty(n, A, dtype=torch.float32, device=dev)
         # the state the captured actor launch reads: the env's own clamped-observation buffer (device loop) or the
@@ -162,12 +172,12 @@ class RolloutGraph:
             self._warm = True
         else:
             # the bf16 image of the actor weights follows DDPG._update; a no-op when nothing changed
-            L.check(L.lib().ois_agent_sync_weights(a._handle, L.ptr(a.policy.flat), L.current_stream()))
+            L.check(L.lib().ois_agent_sync_weights(a._handle, L.ptr(a.policy.flat), L.current_stream(self._dev_index)))
             if self._graph is None:
                 self._capture()
             self._graph.replay()
         self._advance_host()
         if self.host_io:
-            torch.cuda.current_stream().synchronize()
+            _device_synchronize()     # the host consumes this step's results: one sync per step is the point of host_io
             return self.h_next_states, self.h_rewards, self.h_terminated
         return t.obs_clipped, t.rew_buf.view(-1, 1), t.reset_buf.view(-1, 1)

@@ -82,7 +82,7 @@ class ClockSampler:
     def start(self):
         try:
             self.proc = subprocess.Popen(["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}",
-                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                          "--format=csv,noheader,nounits", "-lms", "50"],
                                          stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             threading.Thread(target=self._read, daemon=True).start()
         except OSError:
@@ -473,7 +473,6 @@ def main():
         sampler.start()
     ms, launches = device_timed(world, args.steps, args.warmup, flush)
     barrier()
-    clocks = sampler.stop() if rank == 0 else None
     e2e_eager_ms, _, _ = e2e_timed(world, min(args.steps, 200), 5)
     barrier()
     e2e_ms, h2d, d2h = e2e_graph_timed(world, min(args.steps, 200), 5)
@@ -484,6 +483,7 @@ def main():
     barrier()
     host_ms = host_issue_timed(world)
     barrier()
+    clocks = sampler.stop() if rank == 0 else None      # sampled across ALL the timed legs above
     per_rank = [[ms, graph_ms, host_ms]]
     if world_size > 1:
         mine = torch.tensor(per_rank[0], device=device, dtype=torch.float64)

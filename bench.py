@@ -554,17 +554,19 @@ def main():
             scale = []
             del world
             torch.cuda.empty_cache()
-            for big in (65536, 1048576):
+            # 16 384 = envs per GPU of BASELINE.json configs[3] (128 row tiles: still one wave of the 148 SMs)
+            for big in (16384, 65536, 1048576):
                 w = World(wl, big, args.precision, device, seed=99)
-                a_ms, e_ms = kernel_split(w, 20, None)
+                small = big * 335 < (96 << 20)          # state + replay rows fit in L2: flush between steps, as at 4096
+                a_ms, e_ms = kernel_split(w, 20, flush if small else None)
                 for _ in range(3):
                     w.step()
-                m, _ = device_timed(w, 20, 3, None)
+                m, _ = device_timed(w, 20, 3, flush if small else None)
                 scale.append({"envs": big, "value": big * 1e3 / m, "ms_per_step": m, "act_ms": a_ms, "env_ms": e_ms,
                               "env_traffic": NCU_TRAFFIC.get(("env", big)), "act_traffic": NCU_TRAFFIC.get(("actor", big)),
                               "env_hbm_frac": (ENV_BYTES[wl["variant"]] + REPLAY_BYTES) * big / (e_ms * 1e-3) / 1e9 / hbm_peak,
                               "act_tensor_frac": ACTOR_FLOP[wl["act_dim"]] * big / (a_ms * 1e-3) / 1e12 / tc_peak,
-                              "l2": "state exceeds L2" if big >= 1048576 else "L2-resident"})
+                              "l2": "flushed between steps" if small else "state exceeds L2 (no flush needed)"})
                 del w
                 torch.cuda.empty_cache()
             out["at_scale"] = scale

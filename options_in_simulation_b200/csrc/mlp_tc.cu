@@ -229,13 +229,26 @@ tc_actor_kernel(const __grid_constant__ TcActArgs args) {
   if (warp >= 2 && warp < 2 + kEpiWarps) {   // biases: fp32, straight from the master parameters
     const int64_t b0 = (int64_t)kH0 * args.in_dim, w1 = b0 + kH0, b1 = w1 + (int64_t)kH1 * kH0, w2 = b1 + kH1;
     const int64_t b2 = w2 + (int64_t)kH2 * kH1, w3 = b2 + kH2, b3 = w3 + (int64_t)args.out_dim * kH2;
-    for (int i = threadIdx.x - 64; i < kH0 + kH1 + kH2 + kOutPad; i += kEpiWarps * 32) {
-      float v;
-      if (i < kH0) v = args.params[b0 + i];
-      else if (i < kH0 + kH1) v = args.params[b1 + i - kH0];
-      else if (i < kH0 + kH1 + kH2) v = args.params[b2 + i - kH0 - kH1];
-      else v = (i - kH0 - kH1 - kH2) < args.out_dim ? args.params[b3 + i - kH0 - kH1 - kH2] : 0.f;
-      s_bias[i] = v;
+    // all of a thread's loads are issued before any is consumed: the set-up is on the critical path whenever the kernel
+    // is not overlapping a predecessor (first kernel of a graph replay, cold start), and five dependent global-memory
+    // round trips were most of its 3 us
+    constexpr int kBiasTotal = kH0 + kH1 + kH2 + kOutPad;
+    constexpr int kBiasIters = (kBiasTotal + kEpiWarps * 32 - 1) / (kEpiWarps * 32);
+    float bv[kBiasIters];
+#pragma unroll
+    for (int k = 0; k < kBiasIters; ++k) {
+      const int i = threadIdx.x - 64 + k * kEpiWarps * 32;
+      float v = 0.f;
+      if (i < kH0) v = __ldg(args.params + b0 + i);
+      else if (i < kH0 + kH1) v = __ldg(args.params + b1 + i - kH0);
+      else if (i < kH0 + kH1 + kH2) v = __ldg(args.params + b2 + i - kH0 - kH1);
+      else if (i < kBiasTotal && (i - kH0 - kH1 - kH2) < args.out_dim) v = __ldg(args.params + b3 + i - kH0 - kH1 - kH2);
+      bv[k] = v;
+    }
+#pragma unroll
+    for (int k = 0; k < kBiasIters; ++k) {
+      const int i = threadIdx.x - 64 + k * kEpiWarps * 32;
+      if (i < kBiasTotal) s_bias[i] = bv[k];
     }
     if (threadIdx.x - 64 < 2 * kInPad) {   // RunningStandardScaler constants: mean.float(), sqrt(var.float()) + eps
       const int c = (threadIdx.x - 64) & (kInPad - 1);

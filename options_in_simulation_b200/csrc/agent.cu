@@ -40,6 +40,20 @@ __global__ void scaler_apply_kernel(const float* __restrict__ x, float* __restri
   y[row * ldy + c] = fminf(fmaxf(v, -5.0f), 5.0f);
 }
 
+// skrl RunningStandardScaler._parallel_variance for one column: merge a batch (mean, unbiased variance, B rows) into the
+// running (mu, vr, cur).  Explicitly rounded operations (no compiler-chosen FMA contraction), so that every caller —
+// scaler_train_block and the fused batch preparation of the tensor-core update — produces the same bits.
+__device__ __forceinline__ void scaler_merge(double& mu, double& vr, double& cur, double in_mean, double in_var, int B) {
+  const double n = (double)B;
+  const double tot = __dadd_rn(cur, n);
+  const double delta = __dsub_rn(in_mean, mu);
+  const double cross = __ddiv_rn(__dmul_rn(__dmul_rn(__dmul_rn(delta, delta), cur), n), tot);
+  const double M2 = __dadd_rn(__dadd_rn(__dmul_rn(vr, cur), __dmul_rn(in_var, n)), cross);
+  mu = __dadd_rn(mu, __ddiv_rn(__dmul_rn(delta, n), tot));
+  vr = __ddiv_rn(M2, tot);
+  cur = tot;
+}
+
 // RunningStandardScaler(x, train=True) on a [B, dim] batch, one CTA of 256 threads: batch mean / unbiased variance
 // (torch.mean / torch.var are float32 results; we accumulate in fp64 and round once), parallel-variance merge into
 // the fp64 running statistics, then standardise with the UPDATED statistics.  All columns are swept together (one
@@ -80,7 +94,7 @@ __device__ void scaler_train_block(const float* __restrict__ x, float* __restric
   for (int r = t; r < B; r += 256) {
 #pragma unroll
     for (int c = 0; c < 16; ++c)
-      if (c < dim) { const double d = (double)x[(size_t)r * dim + c] - s_bmean[c]; a[c] += d * d; }
+      if (c < dim) { const double d = (double)x[(size_t)r * dim + c] - s_bmean[c]; a[c] = __fma_rn(d, d, a[c]); }
   }
 #pragma unroll
   for (int c = 0; c < 16; ++c) {
@@ -95,12 +109,8 @@ __device__ void scaler_train_block(const float* __restrict__ x, float* __restric
     for (int w = 0; w < 8; ++w) m2 += s_sum[w][t];
     const double in_mean = (double)(float)s_bmean[t];                      // torch.mean -> float32
     const double in_var = (double)(float)(m2 / (double)(B - 1));           // torch.var (unbiased) -> float32
-    const double cur = count[0];
-    const double tot = cur + (double)B;
-    const double delta = in_mean - mean[t];
-    const double M2 = var[t] * cur + in_var * (double)B + delta * delta * cur * (double)B / tot;
-    const double nm = mean[t] + delta * (double)B / tot;
-    const double nv = M2 / tot;
+    double nm = mean[t], nv = var[t], cur = count[0];
+    scaler_merge(nm, nv, cur, in_mean, in_var, B);
     mean[t] = nm;
     var[t] = nv;
     s_mu[t] = (float)nm;
@@ -284,25 +294,96 @@ polyak_pair_kernel(const __grid_constant__ PolyakPair a, float tau) {
   if (a.img[k]) tcu_img_store(a.img[k], i, v, a.in_dim[k], a.out_dim[k]);
 }
 
-// the tensor-core update's batch preparation in ONE CTA: ddpg.py:381-382 (scaler, train=True, on states then on
-// next_states — sequentially dependent through the running statistics), then the bf16 network inputs:
+// the tensor-core update's batch preparation in ONE CTA of 512 threads: ddpg.py:381-382 (scaler, train=True, on states
+// then on next_states), then the bf16 network inputs:
 //   x_critic  = [scaled states, sampled actions]   (critic input; its first D columns are also the actor's input)
 //   x_scratch = [scaled next_states, 0]            (target actor input; the target actions land in columns D.. later)
-__global__ void __launch_bounds__(256)
+// The two scaler updates depend on each other only through the parallel-variance MERGE into the running statistics;
+// the batch mean and the batch variance of each tensor do not.  So threads 0-255 reduce `states` and threads 256-511
+// reduce `next_states` at the same time — each half with exactly the summation order of scaler_train_block (rows
+// strided by 256 per thread, xor-shuffle tree, the eight warp totals in warp order), which keeps the statistics
+// bit-identical to the fp32 path's — one thread per column then does the two merges back to back, and both tensors
+// are standardised together.  Half the dependent stages of two scaler_train_block calls (23 us -> see DESIGN.md 3.1).
+__global__ void __launch_bounds__(512)
 tcu_batch_prep_kernel(const float* __restrict__ states, const float* __restrict__ next_states,
                       const float* __restrict__ actions, float* __restrict__ sn, float* __restrict__ s2n, int B, int D, int A,
                       double* __restrict__ mean, double* __restrict__ var, double* __restrict__ count,
                       uint8_t* __restrict__ x_critic, uint8_t* __restrict__ x_scratch) {
+  __shared__ double s_sum[2][8][16];
+  __shared__ double s_bmean[2][16];
+  __shared__ float s_mu[2][16], s_sd[2][16];
   pdl_wait();
   if (threadIdx.x == 0) pdl_trigger();
+  const int t = threadIdx.x, half = t >> 8, tt = t & 255, lane = t & 31, wp = tt >> 5;
+  const float* __restrict__ x = half ? next_states : states;
+  float* __restrict__ y = half ? s2n : sn;
   if (mean) {
-    scaler_train_block(states, sn, B, D, mean, var, count, D);
-    scaler_train_block(next_states, s2n, B, D, mean, var, count, D);
-  } else {
-    for (int i = threadIdx.x; i < B * D; i += 256) { sn[i] = states[i]; s2n[i] = next_states[i]; }
+    double a[16];
+    // pass 1: batch mean
+#pragma unroll
+    for (int c = 0; c < 16; ++c) a[c] = 0.0;
+    for (int r = tt; r < B; r += 256) {
+#pragma unroll
+      for (int c = 0; c < 16; ++c)
+        if (c < D) a[c] += (double)x[(size_t)r * D + c];
+    }
+#pragma unroll
+    for (int c = 0; c < 16; ++c) {
+      if (c < D) {
+        for (int o = 16; o > 0; o >>= 1) a[c] += __shfl_xor_sync(0xffffffffu, a[c], o);
+        if (lane == 0) s_sum[half][wp][c] = a[c];
+      }
+    }
     __syncthreads();
+    if (tt < D) {
+      double m = 0.0;
+      for (int w = 0; w < 8; ++w) m += s_sum[half][w][tt];
+      s_bmean[half][tt] = m / (double)B;
+    }
+    __syncthreads();
+    // pass 2: centred sum of squares
+#pragma unroll
+    for (int c = 0; c < 16; ++c) a[c] = 0.0;
+    for (int r = tt; r < B; r += 256) {
+#pragma unroll
+      for (int c = 0; c < 16; ++c)
+        if (c < D) { const double d = (double)x[(size_t)r * D + c] - s_bmean[half][c]; a[c] = __fma_rn(d, d, a[c]); }
+    }
+#pragma unroll
+    for (int c = 0; c < 16; ++c) {
+      if (c < D) {
+        for (int o = 16; o > 0; o >>= 1) a[c] += __shfl_xor_sync(0xffffffffu, a[c], o);
+        if (lane == 0) s_sum[half][wp][c] = a[c];
+      }
+    }
+    __syncthreads();
+    if (t < D) {   // the two merges of skrl's _parallel_variance, in the reference's order: states, then next_states
+      double mu = mean[t], vr = var[t], cur = count[0];
+#pragma unroll
+      for (int h = 0; h < 2; ++h) {
+        double m2 = 0.0;
+        for (int w = 0; w < 8; ++w) m2 += s_sum[h][w][t];
+        const double in_mean = (double)(float)s_bmean[h][t];                  // torch.mean -> float32
+        const double in_var = (double)(float)(m2 / (double)(B - 1));           // torch.var (unbiased) -> float32
+        scaler_merge(mu, vr, cur, in_mean, in_var, B);
+        s_mu[h][t] = (float)mu;
+        s_sd[h][t] = sqrtf((float)vr);
+      }
+      mean[t] = mu;
+      var[t] = vr;
+    }
+    __syncthreads();
+    if (t == 0) count[0] += 2.0 * (double)B;   // every reader of count[0] is past the barrier above
+    for (int i = tt; i < B * D; i += 256) {
+      const int r = i / D, c = i - r * D;
+      const float v = __fdiv_rn(__fsub_rn(x[i], s_mu[half][c]), __fadd_rn(s_sd[half][c], 1e-8f));
+      y[i] = fminf(fmaxf(v, -5.0f), 5.0f);
+    }
+  } else {
+    for (int i = tt; i < B * D; i += 256) y[i] = x[i];
   }
-  for (int i = threadIdx.x; i < B * 2; i += 256) {
+  __syncthreads();
+  for (int i = threadIdx.x; i < B * 2; i += 512) {
     const int r = i >> 1, c8 = i & 1;
     uint16_t vc[8], vs[8];
 #pragma unroll
@@ -573,7 +654,7 @@ extern "C" int ois_ddpg_update_phase(OisAgent* a, const OisScaler* scaler, const
       // ddpg.py:381-382 scaler(train=True) on states, then next_states; bf16 inputs of the critic and the target actor
       uint8_t* x_critic = tcu_x_buffer(a, TCU_ACTS_CRITIC);
       uint8_t* x_scratch = tcu_x_buffer(a, TCU_ACTS_SCRATCH);
-      OIS_CHECK_CUDA(launch_pdl(tcu_batch_prep_kernel, 1, 256, 0, s, io->states, io->next_states, io->actions, a->u_sn, a->u_s2n, B,
+      OIS_CHECK_CUDA(launch_pdl(tcu_batch_prep_kernel, 1, 512, 0, s, io->states, io->next_states, io->actions, a->u_sn, a->u_s2n, B,
                                 D, A, has_scaler ? scaler->running_mean : (double*)nullptr,
                                 has_scaler ? scaler->running_variance : (double*)nullptr,
                                 has_scaler ? scaler->current_count : (double*)nullptr, x_critic, x_scratch));

@@ -254,9 +254,17 @@ adam_kernel(float* __restrict__ p, float* __restrict__ m, float* __restrict__ v,
   pdl_wait();
   if (threadIdx.x == 0) pdl_trigger();
   if (threadIdx.x == 0) {
-    const double t = (double)(step_dev ? step_dev[0] : step_host);
-    s_step_size = (float)(lr / (1.0 - pow(beta1, t)));
-    s_bc2_sqrt = (float)sqrt(1.0 - pow(beta2, t));
+    // beta ** step by repeated squaring (<= 2 log2(step) double multiplications, relative error ~1e-15): every CTA pays
+    // this latency before its elementwise work, and the library pow() of a double was ~2 us of this kernel's ~6
+    const int64_t t = step_dev ? step_dev[0] : step_host;
+    double p1 = 1.0, p2 = 1.0, x1 = beta1, x2 = beta2;
+    for (int64_t e = t; e > 0; e >>= 1) {
+      if (e & 1) { p1 = __dmul_rn(p1, x1); p2 = __dmul_rn(p2, x2); }
+      x1 = __dmul_rn(x1, x1);
+      x2 = __dmul_rn(x2, x2);
+    }
+    s_step_size = (float)(lr / (1.0 - p1));
+    s_bc2_sqrt = (float)sqrt(1.0 - p2);
   }
   __syncthreads();
   const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;

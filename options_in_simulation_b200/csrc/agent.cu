@@ -244,6 +244,37 @@ __global__ void out_act_grad_kernel(const float* __restrict__ da, int ldda, int 
   dz[i] = act == OIS_ACT_SIGMOID ? g * v * (1.f - v) : act == OIS_ACT_TANH ? g * (1.f - v * v) : g;
 }
 
+// step_size = lr / (1 - beta1 ** step), sqrt(1 - beta2 ** step) of torch.optim.Adam, in double.  beta ** step by repeated
+// squaring (<= 2 log2(step) double multiplications, relative error ~1e-15): every CTA pays this latency before its
+// elementwise work, and the library pow() of a double was ~2 us of the Adam kernel's ~6.
+__device__ __forceinline__ void adam_bias_corrections(int64_t t, double lr, double beta1, double beta2, float& step_size,
+                                                      float& bc2_sqrt) {
+  double p1 = 1.0, p2 = 1.0, x1 = beta1, x2 = beta2;
+  for (int64_t e = t; e > 0; e >>= 1) {
+    if (e & 1) { p1 = __dmul_rn(p1, x1); p2 = __dmul_rn(p2, x2); }
+    x1 = __dmul_rn(x1, x1);
+    x2 = __dmul_rn(x2, x2);
+  }
+  step_size = (float)(lr / (1.0 - p1));
+  bc2_sqrt = (float)sqrt(1.0 - p2);
+}
+
+// one element of the single-tensor Adam step; returns the new parameter
+__device__ __forceinline__ float adam_element(float* __restrict__ p, float* __restrict__ m, float* __restrict__ v,
+                                              const float* __restrict__ g, int64_t i, float grad_scale, double beta1,
+                                              double beta2, float eps, float step_size, float bc2_sqrt) {
+  const float w1 = (float)(1.0 - beta1), b2 = (float)beta2, w2 = (float)(1.0 - beta2);
+  const float gi = g[i] * grad_scale;
+  const float mi = m[i] + w1 * (gi - m[i]);            // exp_avg.lerp_(grad, 1 - beta1)
+  const float vi = v[i] * b2 + w2 * gi * gi;           // exp_avg_sq.mul_(beta2).addcmul_(grad, grad, 1 - beta2)
+  const float denom = sqrtf(vi) / bc2_sqrt + eps;
+  m[i] = mi;
+  v[i] = vi;
+  const float pn = p[i] - step_size * (mi / denom);    // param.addcdiv_(exp_avg, denom, value=-step_size)
+  p[i] = pn;
+  return pn;
+}
+
 // torch.optim.Adam (single-tensor formulas), flat buffers; g is scaled by grad_scale (1/world_size) first.
 // The step count may live on the device (CUDA-graph replay): bias corrections are then computed here.
 __global__ void __launch_bounds__(256)
@@ -253,31 +284,11 @@ adam_kernel(float* __restrict__ p, float* __restrict__ m, float* __restrict__ v,
   __shared__ float s_step_size, s_bc2_sqrt;
   pdl_wait();
   if (threadIdx.x == 0) pdl_trigger();
-  if (threadIdx.x == 0) {
-    // beta ** step by repeated squaring (<= 2 log2(step) double multiplications, relative error ~1e-15): every CTA pays
-    // this latency before its elementwise work, and the library pow() of a double was ~2 us of this kernel's ~6
-    const int64_t t = step_dev ? step_dev[0] : step_host;
-    double p1 = 1.0, p2 = 1.0, x1 = beta1, x2 = beta2;
-    for (int64_t e = t; e > 0; e >>= 1) {
-      if (e & 1) { p1 = __dmul_rn(p1, x1); p2 = __dmul_rn(p2, x2); }
-      x1 = __dmul_rn(x1, x1);
-      x2 = __dmul_rn(x2, x2);
-    }
-    s_step_size = (float)(lr / (1.0 - p1));
-    s_bc2_sqrt = (float)sqrt(1.0 - p2);
-  }
+  if (threadIdx.x == 0) adam_bias_corrections(step_dev ? step_dev[0] : step_host, lr, beta1, beta2, s_step_size, s_bc2_sqrt);
   __syncthreads();
   const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
-  const float w1 = (float)(1.0 - beta1), b2 = (float)beta2, w2 = (float)(1.0 - beta2);
-  const float gi = g[i] * grad_scale;
-  const float mi = m[i] + w1 * (gi - m[i]);            // exp_avg.lerp_(grad, 1 - beta1)
-  const float vi = v[i] * b2 + w2 * gi * gi;           // exp_avg_sq.mul_(beta2).addcmul_(grad, grad, 1 - beta2)
-  const float denom = sqrtf(vi) / s_bc2_sqrt + eps;
-  m[i] = mi;
-  v[i] = vi;
-  const float pn = p[i] - s_step_size * (mi / denom);  // param.addcdiv_(exp_avg, denom, value=-step_size)
-  p[i] = pn;
+  const float pn = adam_element(p, m, v, g, i, grad_scale, beta1, beta2, eps, s_step_size, s_bc2_sqrt);
   if (img) tcu_img_store(img, i, pn, in_dim, out_dim);  // keep the bf16 tensor-core image current (update_tc.cu)
 }
 
@@ -289,17 +300,43 @@ struct PolyakPair {
   uint8_t* img[2];
   int in_dim[2], out_dim[2];
 };
+// Phase 2 of the tensor-core update in ONE launch: ddpg.py:438 Adam step of the actor and ddpg.py:443-444 polyak of both
+// target networks.  Element i < n[0]: the actor's Adam step, then its target's polyak with the parameter just computed
+// (the same value the separate polyak launch would have read back); element n[0] + j: the critic target's polyak (the
+// critic was stepped in phase 1).  Same formulas as adam_kernel / polyak_kernel; the bf16 images are kept current.
+struct AdamPolyak {
+  PolyakPair pp;            // pt / p / n / img / dims of (actor, critic); p[0] is the actor being stepped
+  float *m, *v;
+  const float* g;
+  uint8_t* actor_img;
+  float grad_scale, eps;
+  double lr, beta1, beta2;
+  int64_t step_host;
+  const int64_t* step_dev;
+};
 __global__ void __launch_bounds__(256)
-polyak_pair_kernel(const __grid_constant__ PolyakPair a, float tau) {
+adam_polyak_kernel(const __grid_constant__ AdamPolyak a, float tau) {
+  __shared__ float s_step_size, s_bc2_sqrt;
   pdl_wait();
   if (threadIdx.x == 0) pdl_trigger();
+  if (threadIdx.x == 0)
+    adam_bias_corrections(a.step_dev ? a.step_dev[0] : a.step_host, a.lr, a.beta1, a.beta2, s_step_size, s_bc2_sqrt);
+  __syncthreads();
   int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  int k = 0;
-  if (i >= a.n[0]) { i -= a.n[0]; k = 1; }
-  if (i >= a.n[k]) return;
-  const float v = __fadd_rn(__fmul_rn(a.pt[k][i], 1.0f - tau), __fmul_rn(tau, a.p[k][i]));
-  a.pt[k][i] = v;
-  if (a.img[k]) tcu_img_store(a.img[k], i, v, a.in_dim[k], a.out_dim[k]);
+  if (i < a.pp.n[0]) {
+    float* p = const_cast<float*>(a.pp.p[0]);
+    const float pn = adam_element(p, a.m, a.v, a.g, i, a.grad_scale, a.beta1, a.beta2, a.eps, s_step_size, s_bc2_sqrt);
+    if (a.actor_img) tcu_img_store(a.actor_img, i, pn, a.pp.in_dim[0], a.pp.out_dim[0]);
+    const float t = __fadd_rn(__fmul_rn(a.pp.pt[0][i], 1.0f - tau), __fmul_rn(tau, pn));
+    a.pp.pt[0][i] = t;
+    if (a.pp.img[0]) tcu_img_store(a.pp.img[0], i, t, a.pp.in_dim[0], a.pp.out_dim[0]);
+    return;
+  }
+  i -= a.pp.n[0];
+  if (i >= a.pp.n[1]) return;
+  const float t = __fadd_rn(__fmul_rn(a.pp.pt[1][i], 1.0f - tau), __fmul_rn(tau, a.pp.p[1][i]));
+  a.pp.pt[1][i] = t;
+  if (a.pp.img[1]) tcu_img_store(a.pp.img[1], i, t, a.pp.in_dim[1], a.pp.out_dim[1]);
 }
 
 // the tensor-core update's batch preparation in ONE CTA of 512 threads: ddpg.py:381-382 (scaler, train=True, on states
@@ -761,17 +798,23 @@ extern "C" int ois_ddpg_update_phase(OisAgent* a, const OisScaler* scaler, const
   }
   // phase 2: ddpg.py:438 actor optimizer step, :443-444 polyak
   uint8_t* aimg = tc ? tcu_image_if_valid(a, TCU_ACTOR, io->actor) : nullptr;
-  if (int e = adam_step(io->actor, io->actor_m, io->actor_v, io->actor_grad, oa.total, grad_scale, io->actor_lr, io->beta1,
-                        io->beta2, io->adam_eps, io->adam_step, io->adam_step_dev, aimg, a->actor, s)) return e;
+  if (!tc)
+    if (int e = adam_step(io->actor, io->actor_m, io->actor_v, io->actor_grad, oa.total, grad_scale, io->actor_lr, io->beta1,
+                          io->beta2, io->adam_eps, io->adam_step, io->adam_step_dev, aimg, a->actor, s)) return e;
   if (tc) {
-    PolyakPair pp;
+    AdamPolyak ap;
+    PolyakPair& pp = ap.pp;
     pp.pt[0] = io->actor_target; pp.p[0] = io->actor; pp.n[0] = oa.total;
     pp.pt[1] = io->critic_target; pp.p[1] = io->critic; pp.n[1] = oc.total;
     pp.img[0] = tcu_image_if_valid(a, TCU_ACTOR_T, io->actor_target);
     pp.img[1] = tcu_image_if_valid(a, TCU_CRITIC_T, io->critic_target);
     pp.in_dim[0] = a->actor.in_dim; pp.out_dim[0] = a->actor.out_dim;
     pp.in_dim[1] = a->critic.in_dim; pp.out_dim[1] = a->critic.out_dim;
-    OIS_CHECK_CUDA(launch_pdl(polyak_pair_kernel, eg(oa.total + oc.total, 256), 256, 0, s, pp, io->polyak));
+    ap.m = io->actor_m; ap.v = io->actor_v; ap.g = io->actor_grad; ap.actor_img = aimg;
+    ap.grad_scale = grad_scale; ap.eps = (float)io->adam_eps;
+    ap.lr = io->actor_lr; ap.beta1 = io->beta1; ap.beta2 = io->beta2;
+    ap.step_host = io->adam_step; ap.step_dev = io->adam_step_dev;
+    OIS_CHECK_CUDA(launch_pdl(adam_polyak_kernel, eg(oa.total + oc.total, 256), 256, 0, s, ap, io->polyak));
     tc_invalidate_weights(a);                       // the inference kernel's own stream image is rebuilt by the next act
     if (!aimg) tcu_invalidate(a, TCU_ACTOR);
     if (!pp.img[0]) tcu_invalidate(a, TCU_ACTOR_T);

@@ -343,6 +343,7 @@ adam_polyak_kernel(const __grid_constant__ AdamPolyak a, float tau) {
 // then on next_states), then the bf16 network inputs:
 //   x_critic  = [scaled states, sampled actions]   (critic input; its first D columns are also the actor's input)
 //   x_scratch = [scaled next_states, 0]            (target actor input; the target actions land in columns D.. later)
+//   x_policy  = [scaled states, 0]                 (policy-loss critic input; the actor's actions land in columns D..)
 // The two scaler updates depend on each other only through the parallel-variance MERGE into the running statistics;
 // the batch mean and the batch variance of each tensor do not.  So threads 0-255 reduce `states` and threads 256-511
 // reduce `next_states` at the same time — each half with exactly the summation order of scaler_train_block (rows
@@ -353,7 +354,7 @@ __global__ void __launch_bounds__(512)
 tcu_batch_prep_kernel(const float* __restrict__ states, const float* __restrict__ next_states,
                       const float* __restrict__ actions, float* __restrict__ sn, float* __restrict__ s2n, int B, int D, int A,
                       double* __restrict__ mean, double* __restrict__ var, double* __restrict__ count,
-                      uint8_t* __restrict__ x_critic, uint8_t* __restrict__ x_scratch) {
+                      uint8_t* __restrict__ x_critic, uint8_t* __restrict__ x_scratch, uint8_t* __restrict__ x_policy) {
   __shared__ double s_sum[2][8][16];
   __shared__ double s_bmean[2][16];
   __shared__ float s_mu[2][16], s_sd[2][16];
@@ -430,7 +431,7 @@ tcu_batch_prep_kernel(const float* __restrict__ states, const float* __restrict_
   __syncthreads();
   for (int i = threadIdx.x; i < B * 2; i += 512) {
     const int r = i >> 1, c8 = i & 1;
-    uint16_t vc[8], vs[8];
+    uint16_t vc[8], vs[8], vp[8];
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
       const int c = c8 * 8 + j;
@@ -438,6 +439,7 @@ tcu_batch_prep_kernel(const float* __restrict__ states, const float* __restrict_
       const float xs = c < D ? s2n[(size_t)r * D + c] : 0.f;
       vc[j] = tcu_bf16_bits(xc);
       vs[j] = tcu_bf16_bits(xs);
+      vp[j] = c < D ? vc[j] : (uint16_t)0;
     }
     auto pk = [](const uint16_t* v) {
       return make_uint4((uint32_t)v[0] | ((uint32_t)v[1] << 16), (uint32_t)v[2] | ((uint32_t)v[3] << 16),
@@ -445,6 +447,7 @@ tcu_batch_prep_kernel(const float* __restrict__ states, const float* __restrict_
     };
     *reinterpret_cast<uint4*>(x_critic + tcu_chunk_off(r, c8, 2, 128)) = pk(vc);
     *reinterpret_cast<uint4*>(x_scratch + tcu_chunk_off(r, c8, 2, 128)) = pk(vs);
+    *reinterpret_cast<uint4*>(x_policy + tcu_chunk_off(r, c8, 2, 128)) = pk(vp);
   }
 }
 
@@ -699,10 +702,11 @@ extern "C" int ois_ddpg_update_phase(OisAgent* a, const OisScaler* scaler, const
       // ddpg.py:381-382 scaler(train=True) on states, then next_states; bf16 inputs of the critic and the target actor
       uint8_t* x_critic = tcu_x_buffer(a, TCU_ACTS_CRITIC);
       uint8_t* x_scratch = tcu_x_buffer(a, TCU_ACTS_SCRATCH);
+      uint8_t* x_policy = tcu_x_buffer(a, TCU_ACTS_POLICY);
       OIS_CHECK_CUDA(launch_pdl(tcu_batch_prep_kernel, 1, 512, 0, s, io->states, io->next_states, io->actions, a->u_sn, a->u_s2n, B,
                                 D, A, has_scaler ? scaler->running_mean : (double*)nullptr,
                                 has_scaler ? scaler->running_variance : (double*)nullptr,
-                                has_scaler ? scaler->current_count : (double*)nullptr, x_critic, x_scratch));
+                                has_scaler ? scaler->current_count : (double*)nullptr, x_critic, x_scratch, x_policy));
       // ddpg.py:385-386 target actor on next_states and ddpg.py:399 critic on (states, actions) are independent: they
       // advance layer by layer in the same grouped launches; the target actions land in the scratch input's columns D..
       {
@@ -712,12 +716,16 @@ extern "C" int ois_ddpg_update_phase(OisAgent* a, const OisScaler* scaler, const
         uint8_t* xo[2] = {x_scratch, nullptr};
         if (int e = tcu_forward(a, 2, nets, P32, acts, y, xo, D, s)) return e;
       }
-      // ddpg.py:387-396 target critic on (next_states, target actions)
+      // ddpg.py:387-396 target critic on (next_states, target actions).  The actor's forward of ddpg.py:420 rides in the
+      // same four launches: it reads only the scaled states and the actor's weights, neither of which the critic's
+      // optimizer step (ddpg.py:416, phase 1) touches, so hoisting it above that step changes no value.  Its fp32
+      // actions reuse u_a (the target actions there were consumed in bf16 form) and its bf16 actions land in x_policy
       {
-        const int nets[1] = {TCU_CRITIC_T}, acts[1] = {TCU_ACTS_SCRATCH};
-        const float* P32[1] = {io->critic_target};
-        float* y[1] = {a->u_q2};
-        if (int e = tcu_forward(a, 1, nets, P32, acts, y, nullptr, 0, s)) return e;
+        const int nets[2] = {TCU_CRITIC_T, TCU_ACTOR}, acts[2] = {TCU_ACTS_SCRATCH, TCU_ACTS_ACTOR};
+        const float* P32[2] = {io->critic_target, io->actor};
+        float* y[2] = {a->u_q2, a->u_a};
+        uint8_t* xo[2] = {nullptr, x_policy};
+        if (int e = tcu_forward(a, 2, nets, P32, acts, y, xo, D, s)) return e;
       }
       // TD target + MSE + d(loss)/dq as the backward's bf16 input (ddpg.py:391-407)
       OIS_CHECK_CUDA(launch_pdl(critic_loss_kernel, 1, 256, 0, s, (const float*)a->u_q, a->u_y, a->u_dq, B, io->stats, io->rewards,
@@ -757,18 +765,11 @@ extern "C" int ois_ddpg_update_phase(OisAgent* a, const OisScaler* scaler, const
     if (int e = adam_step(io->critic, io->critic_m, io->critic_v, io->critic_grad, oc.total, grad_scale, io->critic_lr,
                           io->beta1, io->beta2, io->adam_eps, io->adam_step, io->adam_step_dev, cimg, a->critic, s)) return e;
     if (tc) {
-      // ddpg.py:420-423 policy loss through the updated critic.  The actor reads the first D columns of the critic's
-      // input buffer (its image has zero weights beyond them) and writes its action into columns D.. of the same buffer
-      uint8_t* x_critic = tcu_x_buffer(a, TCU_ACTS_CRITIC);
+      // ddpg.py:420-423 policy loss through the updated critic; the actor's forward already ran in phase 0 (its actions
+      // are in x_policy's columns D.. and in u_a), so only the critic's forward on (states, actor actions) is left.
+      // TCU_ACTS_POLICY shares the hidden-activation buffers of TCU_ACTS_CRITIC, which phase 0's backward is done with
       {
-        const int nets[1] = {TCU_ACTOR}, acts[1] = {TCU_ACTS_ACTOR};   // its input buffer IS the critic's (update_tc.cu)
-        const float* P32[1] = {io->actor};
-        float* y[1] = {a->u_a};
-        uint8_t* xo[1] = {x_critic};
-        if (int e = tcu_forward(a, 1, nets, P32, acts, y, xo, D, s)) return e;
-      }
-      {
-        const int nets[1] = {TCU_CRITIC}, acts[1] = {TCU_ACTS_CRITIC};
+        const int nets[1] = {TCU_CRITIC}, acts[1] = {TCU_ACTS_POLICY};
         const float* P32[1] = {io->critic};
         float* y[1] = {a->u_q};
         if (int e = tcu_forward(a, 1, nets, P32, acts, y, nullptr, 0, s)) return e;

@@ -532,7 +532,8 @@ struct State {
   uint8_t* img[4] = {nullptr, nullptr, nullptr, nullptr};      // TCU_ACTOR, TCU_ACTOR_T, TCU_CRITIC, TCU_CRITIC_T
   const float* packed_from[4] = {nullptr, nullptr, nullptr, nullptr};
   bool valid[4] = {false, false, false, false};
-  NetActs acts[3];             // TCU_ACTS_ACTOR, TCU_ACTS_CRITIC (saved for the backward), TCU_ACTS_SCRATCH (targets)
+  NetActs acts[4];             // TCU_ACTS_ACTOR, TCU_ACTS_CRITIC (saved for the backward), TCU_ACTS_SCRATCH (targets),
+                               // TCU_ACTS_POLICY (own input buffer, hidden buffers shared with TCU_ACTS_CRITIC)
   uint8_t *dz, *d2, *d1, *d0;
 };
 
@@ -552,7 +553,7 @@ int tcu_init(OisAgent* a) {
   const size_t B = (size_t)a->batch;
   const size_t wide = B * 512 * 2, mid = B * 128 * 2, thin = B * 16 * 2;
   const size_t acts = thin + 2 * wide + mid;
-  const size_t total = 4 * kImgBytes + 3 * acts + (thin + mid + 2 * wide);
+  const size_t total = 4 * kImgBytes + 3 * acts + thin + (thin + mid + 2 * wide);
   cudaError_t e = cudaMalloc(&st->slab, total);
   if (e != cudaSuccess) {
     delete st;
@@ -568,10 +569,17 @@ int tcu_init(OisAgent* a) {
   }
   uint8_t* p = st->slab;
   for (int i = 0; i < 4; ++i) { st->img[i] = p; p += kImgBytes; }
-  for (NetActs& n : st->acts) { n.x = p; p += thin; n.h0 = p; p += wide; n.h1 = p; p += wide; n.h2 = p; p += mid; }
-  // the actor reads the first in_dim columns of the CRITIC's input buffer (its image has zero weights beyond them) and
-  // its action is written into the following columns of the same buffer: one buffer, no concatenation kernel
+  for (int i = 0; i < 3; ++i) {
+    NetActs& n = st->acts[i];
+    n.x = p; p += thin; n.h0 = p; p += wide; n.h1 = p; p += wide; n.h2 = p; p += mid;
+  }
+  // the actor reads the first in_dim columns of the CRITIC's input buffer (its image has zero weights beyond them):
+  // one buffer, no concatenation kernel.  Its action goes into columns in_dim.. of the POLICY set's input, whose
+  // first columns hold the same scaled states; that set reuses the critic's hidden buffers (the two critic passes of
+  // an update are sequential: ddpg.py:399-407, then :420-429)
   st->acts[TCU_ACTS_ACTOR].x = st->acts[TCU_ACTS_CRITIC].x;
+  st->acts[TCU_ACTS_POLICY] = st->acts[TCU_ACTS_CRITIC];
+  st->acts[TCU_ACTS_POLICY].x = p; p += thin;
   st->dz = p; p += thin; st->d2 = p; p += mid; st->d1 = p; p += wide; st->d0 = p; p += wide;
   a->tcu = st;
   return OIS_OK;

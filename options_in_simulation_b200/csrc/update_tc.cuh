@@ -41,7 +41,7 @@ __device__ inline void tcu_img_store(uint8_t* img, int64_t i, float v, int in_di
 #endif
 
 enum { TCU_ACTOR = 0, TCU_ACTOR_T = 1, TCU_CRITIC = 2, TCU_CRITIC_T = 3 };        // weight images
-enum { TCU_ACTS_ACTOR = 0, TCU_ACTS_CRITIC = 1, TCU_ACTS_SCRATCH = 2, TCU_DZ = 3 };  // activation sets / pack targets
+enum { TCU_ACTS_ACTOR = 0, TCU_ACTS_CRITIC = 1, TCU_ACTS_SCRATCH = 2, TCU_ACTS_POLICY = 3, TCU_DZ = 4 };  // activation sets / pack targets
 
 int tcu_init(OisAgent* a);
 void tcu_free(OisAgent* a);

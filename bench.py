@@ -32,11 +32,42 @@ import json
 import os
 import subprocess
 import sys
-import threading
 import time
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
+
+
+def host_cores():
+    """Host threads the CPU legs may use: the affinity mask, capped by the cgroup CPU quota when there is one
+    (more OpenMP threads than the quota allows makes the spin-waiting workers starve each other)."""
+    try:
+        n = len(os.sched_getaffinity(0)) or 1
+    except AttributeError:
+        n = os.cpu_count() or 1
+    for path in ("/sys/fs/cgroup/cpu.max", "/sys/fs/cgroup/cpu/cpu.cfs_quota_us"):
+        try:
+            with open(path) as f:
+                parts = f.read().split()
+            if path.endswith("cpu.max"):
+                quota, period = parts[0], float(parts[1])
+            else:
+                quota = parts[0]
+                with open("/sys/fs/cgroup/cpu/cpu.cfs_period_us") as f:
+                    period = float(f.read().split()[0])
+            if quota not in ("max", "-1") and period > 0:
+                n = max(1, min(n, int(float(quota) / period)))
+            break
+        except (OSError, ValueError, IndexError):
+            continue
+    return n
+
+
+# torchrun exports OMP_NUM_THREADS=1 to every rank unless the caller set it; the CPU legs (cpu_baseline, --impl
+# reference) run on rank 0 alone and are meant to use all the host cores, so rank 0 undoes that default before torch
+# (and its OpenMP runtime) is imported.  The GPU path does no host math and is unaffected.
+if "TORCHELASTIC_RUN_ID" in os.environ and os.environ.get("RANK", "0") == "0" and os.environ.get("OMP_NUM_THREADS") == "1":
+    os.environ["OMP_NUM_THREADS"] = str(host_cores())
 
 METRIC = "env-steps/s (dyn+obs+reward+act)"
 UNIT = "env-steps/s"
@@ -77,26 +108,33 @@ class ClockSampler:
          "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
 
     def __init__(self, index: int):
-        self.index, self.rows, self.proc = index, [], None
+        self.index, self.rows, self.proc, self.out = index, [], None, None
 
     def start(self):
+        # nvidia-smi writes straight into a temporary file that is parsed after the timed legs: no reader thread in
+        # this process competing with the launch loop for the interpreter lock
+        import tempfile
+
         try:
+            self.out = tempfile.TemporaryFile(mode="w+")
             self.proc = subprocess.Popen(["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}",
                                           "--format=csv,noheader,nounits", "-lms", "50"],
-                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
-            threading.Thread(target=self._read, daemon=True).start()
+                                         stdout=self.out, stderr=subprocess.DEVNULL)
         except OSError:
             self.proc = None
-
-    def _read(self):
-        for line in self.proc.stdout:
-            self.rows.append([c.strip() for c in line.split(",")])
 
     def stop(self):
         if self.proc is None:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
         time.sleep(0.15)
         self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except subprocess.TimeoutExpired:
+            self.proc.kill()
+        self.out.seek(0)
+        self.rows = [[c.strip() for c in line.split(",")] for line in self.out if line.strip()]
+        self.out.close()
         sm = sorted(int(r[0]) for r in self.rows if r and r[0].isdigit())
         mx = [int(r[1]) for r in self.rows if len(r) > 1 and r[1].isdigit()]
         names = ("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap")
@@ -118,7 +156,7 @@ class CpuPort:
         from oracle.gen_golden import synth_state
 
         self.np, self.torch = np, torch
-        torch.set_num_threads(os.cpu_count() or 1)
+        torch.set_num_threads(host_cores())
         torch.manual_seed(seed)
         v = VARIANTS[wl["variant"]]
         self.rng = np.random.default_rng(seed)
@@ -194,7 +232,7 @@ def run_reference(args, wl, n):
         port.step()
     dt = time.perf_counter() - t0
     v = n * steps / dt
-    cores = os.cpu_count() or 1
+    cores = host_cores()
     sample = f"{steps} steps x {n} envs (single host process; the CPU path does not shard across GPUs)"
     print(json.dumps({
         "impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": steps,
@@ -570,9 +608,9 @@ def main():
                 del w
                 torch.cuda.empty_cache()
             out["at_scale"] = scale
-        if not args.no_extras:
+        if not args.no_extras and world_size == 1:   # the CPU baseline is a 1-GPU-run item: rank 0 at N = 1 only
             v, k, dt = time_cpu_port(wl, n)
-            out["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": os.cpu_count() or 1, "kind": "port",
+            out["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": host_cores(), "kind": "port",
                                    "sample": f"{k} steps x {n} envs in {dt:.1f} s (numpy env oracle + CPU-torch actor, oracle/)",
                                    "parts": time_cpu_parts(wl, n)}
         print(json.dumps(out), flush=True)

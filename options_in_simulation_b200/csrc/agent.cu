@@ -730,7 +730,7 @@ extern "C" int ois_ddpg_update_phase(OisAgent* a, const OisScaler* scaler, const
       // TD target + MSE + d(loss)/dq as the backward's bf16 input (ddpg.py:391-407)
       OIS_CHECK_CUDA(launch_pdl(critic_loss_kernel, 1, 256, 0, s, (const float*)a->u_q, a->u_y, a->u_dq, B, io->stats, io->rewards,
                                 io->terminated, io->truncated, (const float*)a->u_q2, io->discount, tcu_x_buffer(a, TCU_DZ)));
-      return tcu_backward(a, TCU_CRITIC, io->critic_grad, TCU_ACTS_CRITIC, nullptr, s);
+      return tcu_backward(a, TCU_CRITIC, io->critic_grad, TCU_ACTS_CRITIC, nullptr, false, s);
     }
     // ddpg.py:381-382  scaler(train=True) on states, then on next_states
     if (has_scaler) {
@@ -774,12 +774,12 @@ extern "C" int ois_ddpg_update_phase(OisAgent* a, const OisScaler* scaler, const
         float* y[1] = {a->u_q};
         if (int e = tcu_forward(a, 1, nets, P32, acts, y, nullptr, 0, s)) return e;
       }
-      OIS_CHECK_CUDA(launch_pdl(policy_loss_kernel, 1, 256, 0, s, (const float*)a->u_q, a->u_dq, B, io->stats, tcu_x_buffer(a, TCU_DZ)));
       // data gradient only through the critic (its parameter gradients from this pass are discarded by the reference
-      // at the next critic_optimizer.zero_grad(), ddpg.py:406), then through the output activation and the actor
-      if (int e = tcu_backward(a, TCU_CRITIC, nullptr, TCU_ACTS_CRITIC, a->u_dx, s)) return e;
-      if (int e = tcu_pack_x(a, TCU_DZ, a->u_dx, CI, D, A, nullptr, 0, 0, a->u_a, a->actor.out_act, s)) return e;
-      return tcu_backward(a, TCU_ACTOR, io->actor_grad, TCU_ACTS_ACTOR, nullptr, s);
+      // at the next critic_optimizer.zero_grad(), ddpg.py:406), starting from the constant d(-mean q)/dq = -1/B, then
+      // through the output activation (the same launch writes the policy-loss statistics) and the actor
+      if (int e = tcu_backward(a, TCU_CRITIC, nullptr, TCU_ACTS_CRITIC, a->u_dx, true, s)) return e;
+      if (int e = tcu_pack_x(a, TCU_DZ, a->u_dx, CI, D, A, nullptr, 0, 0, a->u_a, a->actor.out_act, a->u_q, io->stats, s)) return e;
+      return tcu_backward(a, TCU_ACTOR, io->actor_grad, TCU_ACTS_ACTOR, nullptr, false, s);
     }
     // ddpg.py:420-429  policy loss through the (updated) critic
     if (int e = mlp_forward_fp32(a->actor, io->actor, a->u_sn, D, a->ah0, a->ah1, a->ah2, a->u_a, B, s)) return e;

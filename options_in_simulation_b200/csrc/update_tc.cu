@@ -312,9 +312,35 @@ pack_weights_kernel(const float* __restrict__ P, uint8_t* __restrict__ img, int 
 // src2 may carry a per-element factor: out_act_grad (d(pre-activation) = d(action) * act'(a)) is folded in here
 __global__ void __launch_bounds__(256)
 pack_rows_kernel(const float* __restrict__ s1, int ld1, int col1, int w1, const float* __restrict__ s2, int ld2, int w2,
-                 const float* __restrict__ act_out, int act, uint8_t* __restrict__ dst, int B) {
+                 const float* __restrict__ act_out, int act, uint8_t* __restrict__ dst, int B,
+                 const float* __restrict__ q, float* __restrict__ stats) {
+  __shared__ float s_sum[8], s_max[8], s_min[8];
   pdl_wait();
   if (threadIdx.x == 0) pdl_trigger();
+  if (q && blockIdx.x == 0) {
+    // ddpg.py:423 policy loss = -mean(Q(s, pi(s))) and the Q statistics, in policy_loss_kernel's summation order
+    // (agent.cu).  They ride here because nothing on the gradient chain needs them: d(loss)/dq is the constant -1/B
+    const int t = threadIdx.x, lane = t & 31, wp = t >> 5;
+    float a = 0.f, mx = -INFINITY, mn = INFINITY;
+    for (int k = t; k < B; k += 256) {
+      a += q[k];
+      mx = fmaxf(mx, q[k]);
+      mn = fminf(mn, q[k]);
+    }
+    for (int o = 16; o > 0; o >>= 1) {
+      a += __shfl_xor_sync(0xffffffffu, a, o);
+      mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+      mn = fminf(mn, __shfl_xor_sync(0xffffffffu, mn, o));
+    }
+    if (lane == 0) { s_sum[wp] = a; s_max[wp] = mx; s_min[wp] = mn; }
+    __syncthreads();
+    if (t == 0 && stats) {
+      float A = 0.f, MX = -INFINITY, MN = INFINITY;
+      for (int w = 0; w < 8; ++w) { A += s_sum[w]; MX = fmaxf(MX, s_max[w]); MN = fminf(MN, s_min[w]); }
+      stats[1] = -A / (float)B;
+      stats[2] = MX; stats[3] = MN; stats[4] = A / (float)B;
+    }
+  }
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= B * 2) return;
   const int r = i >> 1, c8 = i & 1;
@@ -336,6 +362,14 @@ pack_rows_kernel(const float* __restrict__ s1, int ld1, int col1, int w1, const 
   }
   *reinterpret_cast<uint4*>(dst + chunk_off(r, c8, 2, 128)) =
       make_uint4(ptx::pack_bf16(v[0], v[1]), ptx::pack_bf16(v[2], v[3]), ptx::pack_bf16(v[4], v[5]), ptx::pack_bf16(v[6], v[7]));
+}
+
+// d(policy loss)/dq = -1/B for every sample (ddpg.py:423): the critic's dz input of the policy pass never changes
+__global__ void fill_policy_dz_kernel(uint8_t* __restrict__ dz, int B) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= B) return;
+  *reinterpret_cast<uint4*>(dz + chunk_off(i, 0, 2, 128)) = make_uint4(ptx::pack_bf16(-1.0f / (float)B, 0.f), 0u, 0u, 0u);
+  *reinterpret_cast<uint4*>(dz + chunk_off(i, 1, 2, 128)) = make_uint4(0u, 0u, 0u, 0u);
 }
 
 // bias gradients: db[n] = sum over the batch rows of the (bf16, tile-blocked) pre-activation gradients of the four
@@ -535,6 +569,7 @@ struct State {
   NetActs acts[4];             // TCU_ACTS_ACTOR, TCU_ACTS_CRITIC (saved for the backward), TCU_ACTS_SCRATCH (targets),
                                // TCU_ACTS_POLICY (own input buffer, hidden buffers shared with TCU_ACTS_CRITIC)
   uint8_t *dz, *d2, *d1, *d0;
+  uint8_t* dz_policy;          // constant: -1/B in column 0 (the policy loss's gradient w.r.t. q)
 };
 
 }  // namespace tcu
@@ -553,7 +588,7 @@ int tcu_init(OisAgent* a) {
   const size_t B = (size_t)a->batch;
   const size_t wide = B * 512 * 2, mid = B * 128 * 2, thin = B * 16 * 2;
   const size_t acts = thin + 2 * wide + mid;
-  const size_t total = 4 * kImgBytes + 3 * acts + thin + (thin + mid + 2 * wide);
+  const size_t total = 4 * kImgBytes + 3 * acts + thin + (thin + mid + 2 * wide) + thin;
   cudaError_t e = cudaMalloc(&st->slab, total);
   if (e != cudaSuccess) {
     delete st;
@@ -581,6 +616,16 @@ int tcu_init(OisAgent* a) {
   st->acts[TCU_ACTS_POLICY] = st->acts[TCU_ACTS_CRITIC];
   st->acts[TCU_ACTS_POLICY].x = p; p += thin;
   st->dz = p; p += thin; st->d2 = p; p += mid; st->d1 = p; p += wide; st->d0 = p; p += wide;
+  st->dz_policy = p; p += thin;
+  fill_policy_dz_kernel<<<(a->batch + 255) / 256, 256>>>(st->dz_policy, a->batch);
+  e = cudaGetLastError();
+  if (e == cudaSuccess) e = cudaDeviceSynchronize();
+  if (e != cudaSuccess) {
+    cudaFree(st->slab);
+    delete st;
+    set_error("tcu_init: fill_policy_dz_kernel -> %s", cudaGetErrorString(e));
+    return OIS_ERR_CUDA;
+  }
   a->tcu = st;
   return OIS_OK;
 }
@@ -626,11 +671,11 @@ uint8_t* tcu_x_buffer(OisAgent* a, int which) {
 }
 
 int tcu_pack_x(OisAgent* a, int dst, const float* s1, int ld1, int col1, int w1, const float* s2, int ld2, int w2,
-               const float* act_out, int act, cudaStream_t s) {
+               const float* act_out, int act, const float* q, float* stats, cudaStream_t s) {
   State* st = (State*)a->tcu;
   OIS_CHECK_ARG(st && w1 + w2 <= 16, "bad pack request");
   uint8_t* out = dst == TCU_DZ ? st->dz : st->acts[dst].x;
-  OIS_CHECK_CUDA(launch_pdl(pack_rows_kernel, (a->batch * 2 + 255) / 256, 256, 0, s, s1, ld1, col1, w1, s2, ld2, w2, act_out, act, out, a->batch));
+  OIS_CHECK_CUDA(launch_pdl(pack_rows_kernel, (a->batch * 2 + 255) / 256, 256, 0, s, s1, ld1, col1, w1, s2, ld2, w2, act_out, act, out, a->batch, q, stats));
   return OIS_OK;
 }
 
@@ -650,10 +695,11 @@ int tcu_forward(OisAgent* a, int count, const int* nets, const float* const* P32
   return forward(count, sh, P32, img, na, y, x_out, x_col, a->batch, s);
 }
 
-int tcu_backward(OisAgent* a, int net, float* G, int acts, float* dx, cudaStream_t s) {
+int tcu_backward(OisAgent* a, int net, float* G, int acts, float* dx, bool policy_dz, cudaStream_t s) {
   State* st = (State*)a->tcu;
   OIS_CHECK_ARG(st && st->valid[net], "backward needs the weight image its forward used");
-  return backward(shape_of(a, net), st->img[net], G, st->acts[acts], st->dz, st->d2, st->d1, st->d0, dx, a->batch, s);
+  return backward(shape_of(a, net), st->img[net], G, st->acts[acts], policy_dz ? st->dz_policy : st->dz, st->d2, st->d1,
+                  st->d0, dx, a->batch, s);
 }
 
 // diagnostics hook for tests (deliberately not declared in include/ois_b200.h): C = op(A) op(B) on the tensor cores

@@ -54,9 +54,10 @@ uint8_t* tcu_image_if_valid(OisAgent* a, int net, const float* P32);
 // the bf16 input buffer of activation set `acts` (tile-blocked [B, 16]) / the dz buffer for TCU_DZ
 uint8_t* tcu_x_buffer(OisAgent* a, int which);
 // [B, w1] (columns col1.. of s1) ++ [B, w2] -> the bf16 input of activation set `dst` (or the dz buffer for TCU_DZ);
-// with act_out the first block is multiplied by the output activation's derivative at act_out
+// with act_out the first block is multiplied by the output activation's derivative at act_out; with q the same launch
+// also writes the policy-loss statistics of ddpg.py:423 (stats[1..4] = loss, max q, min q, mean q)
 int tcu_pack_x(OisAgent* a, int dst, const float* s1, int ld1, int col1, int w1, const float* s2, int ld2, int w2,
-               const float* act_out, int act, cudaStream_t s);
+               const float* act_out, int act, const float* q, float* stats, cudaStream_t s);
 // y_i = mlp_i(x_i) for up to two independent networks, layer by layer in grouped launches; hidden activations of set
 // acts[i] are kept (bf16) for the backward
 // x_out[i] (nullable): the outputs are ALSO written, as bf16, into columns x_col.. of that tile-blocked [B, 16] buffer
@@ -64,7 +65,8 @@ int tcu_pack_x(OisAgent* a, int dst, const float* s1, int ld1, int col1, int w1,
 int tcu_forward(OisAgent* a, int count, const int* nets, const float* const* P32, const int* acts, float* const* y,
                 uint8_t* const* x_out, int x_col, cudaStream_t s);
 // backward of network `net` from the dz buffer through activation set `acts`; G: flat fp32 parameter gradients
-// (nullable), dx: [B, in_dim] fp32 input gradient (nullable)
-int tcu_backward(OisAgent* a, int net, float* G, int acts, float* dx, cudaStream_t s);
+// (nullable), dx: [B, in_dim] fp32 input gradient (nullable); policy_dz: start from the constant -1/B gradient of the
+// policy loss instead of the dz buffer
+int tcu_backward(OisAgent* a, int net, float* G, int acts, float* dx, bool policy_dz, cudaStream_t s);
 
 }  // namespace ois

@@ -76,9 +76,9 @@ REPLAY_BYTES = 70
 ACTOR_FLOP = {4: 662528, 2: 662016, 1: 661760}                             # 2 * MACs, SURVEY.md §8(d)
 UPDATE_FLOP = 6645248 * 512                                                # SURVEY.md §8 row A11, B = 512
 # dram__bytes_read.sum + dram__bytes_write.sum per launch, from the committed `ncu --set full` captures
-# (profiles/r01b_ncu_full_summary.txt; kamma_4d): {(kernel, envs): bytes}
-NCU_TRAFFIC = {("env", 4096): 652032, ("actor", 4096): 924672, ("env", 1048576): 159505664 + 233138688,
-               ("actor", 1048576): 42704896 + 218112}
+# (profiles/r01g_ncu_full_summary.txt; kamma_4d): {(kernel, envs): bytes}
+NCU_TRAFFIC = {("env", 4096): 659968, ("actor", 4096): 923648, ("env", 1048576): 159438592 + 233006336,
+               ("actor", 1048576): 42703616 + 468480}
 WORKLOADS = {
     "kamma_4d": dict(variant="KAMMA_medium", act_dim=4, envs=4096, ou=0.05, T_e=5e5, memory_total=1_000_000,
                      name="KAMMA-4d nofifo random RLIL (BASELINE.json configs[2])"),

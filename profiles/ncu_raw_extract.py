@@ -14,6 +14,9 @@ WANT = [
     ("dram__bytes_write.sum", "dram write"),
     ("gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed", "dram % of peak"),
     ("lts__t_bytes.sum", "L2 bytes"),
+    ("lts__t_sectors.sum", "L2 sectors"),
+    ("l1tex__t_sectors_pipe_lsu_mem_global_op_ld.sum", "global load sectors"),
+    ("l1tex__t_requests_pipe_lsu_mem_global_op_ld.sum", "global load requests"),
     ("sm__throughput.avg.pct_of_peak_sustained_elapsed", "sm throughput %"),
     ("sm__warps_active.avg.pct_of_peak_sustained_active", "warps active %"),
     ("smsp__inst_executed.sum", "warp instructions"),

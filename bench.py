@@ -20,6 +20,14 @@ timed on the host cores — a reported baseline, not the target), ``at_scale`` (
 whose state exceeds L2, where the kernels reach their bandwidth / tensor limits) and ``update`` (DDPG._update
 at the reference cadence, reported separately: it is not part of the metric).
 
+At N > 1 the line also carries the data-parallel update (BASELINE.json configs[2] "with NCCL gradient all-reduce"):
+``update.ms_per_update`` with the gradients exchanged inside the Adam kernels over NVLink peer memory (csrc/comm.cuh),
+the same with NCCL all-reduces captured in the update graph, and without any exchange (``collective`` = the difference),
+``train_*`` at the reference cadence, and an assertion that all ranks hold bit-identical weights afterwards.
+
+``--workload`` selects the other BASELINE.json configs (kaddpg_1d, kaddpg_2d, kamma_gv_fifo, kamma_eval_sweep); the
+default, kamma_4d, is the headline.
+
 ``--impl reference`` times the CPU implementation of the same step: the reference is pure Python on Isaac
 Sim + skrl and cannot travel to (or run on) the GPU box, so this arm runs the pinned CPU port
 (oracle/env_oracle.py + oracle/agent_oracle.py: numpy / torch restatements, verified against the reference's
@@ -75,16 +83,59 @@ ENV_BYTES = {"KAMMA_medium": 265, "KA_DDPG_2D": 253, "KA_DDPG_1D": 249}   # SURV
 REPLAY_BYTES = 70
 ACTOR_FLOP = {4: 662528, 2: 662016, 1: 661760}                             # 2 * MACs, SURVEY.md §8(d)
 UPDATE_FLOP = 6645248 * 512                                                # SURVEY.md §8 row A11, B = 512
-# dram__bytes_read.sum + dram__bytes_write.sum per launch, from the committed `ncu --set full` captures
-# (profiles/r01g_ncu_full_summary.txt; kamma_4d): {(kernel, envs): bytes}
-NCU_TRAFFIC = {("env", 4096): 659968, ("actor", 4096): 923648, ("env", 1048576): 159438592 + 233006336,
-               ("actor", 1048576): 42703616 + 468480}
 WORKLOADS = {
-    "kamma_4d": dict(variant="KAMMA_medium", act_dim=4, envs=4096, ou=0.05, T_e=5e5, memory_total=1_000_000,
+    "kamma_4d": dict(variant="KAMMA_medium", act_dim=4, envs=4096, ou=0.05, T_e=5e5, memory_total=1_000_000, memory="random",
                      name="KAMMA-4d nofifo random RLIL (BASELINE.json configs[2])"),
-    "kaddpg_2d": dict(variant="KA_DDPG_2D", act_dim=2, envs=4096, ou=0.3, T_e=7e5, memory_total=35_000,
+    "kaddpg_2d": dict(variant="KA_DDPG_2D", act_dim=2, envs=4096, ou=0.3, T_e=7e5, memory_total=35_000, memory="fifo",
                       name="KA-DDPG-2d nofifo random RLIL (BASELINE.json configs[1])"),
+    # train/train_kaddpg_1d_nofifo_random_RLIL.py:209,269 (FIFOMemory(35_000), OU base scale 0.5), 64 envs
+    "kaddpg_1d": dict(variant="KA_DDPG_1D", act_dim=1, envs=64, ou=0.5, T_e=7e5, memory_total=35_000, memory="fifo",
+                      name="KA-DDPG-1d nofifo random RLIL (BASELINE.json configs[0])"),
+    # train/train_kamma_4d_fifo_gv_RLIL.py:208 FIFOMemory(10_000) + the gv command curriculum of KAMMA_curr1.py:577-599.
+    # BASELINE.json calls this the "observation-history FIFO path"; the reference has no observation history (obs dim is
+    # 6 in every variant) — its FIFO is the replay ring, which is what runs here
+    "kamma_gv_fifo": dict(variant="KAMMA_curr1", act_dim=4, envs=16384, ou=0.05, T_e=5e5, memory_total=10_000, memory="fifo",
+                          name="KAMMA-4d fifo gv RLIL (BASELINE.json configs[3])"),
+    # eval/eval_kamma_4d.py:175-234 + KAMMA_eval.py:545-550: 65 536 envs over 8 GPUs = 8192 per GPU
+    "kamma_eval_sweep": dict(variant="KAMMA_eval", act_dim=4, envs=8192, ou=None, T_e=5e5, memory_total=16_384, memory="random",
+                             name="KAMMA-4d eval rollout, TE-vs-speed sweep (BASELINE.json configs[4])"),
 }
+ENV_BYTES.update({"KAMMA_curr1": 265, "KAMMA_eval": 265 + 24})    # eval: three more sums, SURVEY.md 8(d)
+
+
+def ncu_traffic():
+    """{(kernel, envs): dram bytes per launch} from the latest committed `ncu --set full` capture, read from
+    profiles/ncu_traffic.json (written by profiles/ncu_summary.py next to the capture it came from).  The capture's L2
+    condition is stated there: ncu replays each launch on a cold, flushed cache (--cache-control all, the default)."""
+    try:
+        d = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json")))
+    except (OSError, ValueError):
+        return {}, None
+    return {(e["kernel"], int(e["envs"])): int(e["bytes"]) for e in d.get("entries", [])}, d.get("source")
+
+
+def workload_config(wl, n, world_size):
+    """The `config` object of the JSON line: identical in the GPU arm and in the reference arm."""
+    return {"workload": wl["name"], "envs_per_gpu": n, "variant": wl["variant"], "act_dim": wl["act_dim"],
+            "replay": "fused append, rank-local shard", "rng": "in-kernel Philox (GPU arm) / numpy PCG64 (CPU arm)",
+            "l2": "GPU arm: flushed between timed steps (256 MiB memset outside the event brackets); CPU arm: n/a",
+            "parallelism": f"env/replay shards x{world_size}; rollout: no data-path collective; update: critic + actor "
+                           "gradient all-reduce (ddpg.py:409-410,431-432)"}
+
+
+def pin_to_cores(local_rank, local_world):
+    """One slice of the affinity mask per rank (8 ranks on one host otherwise migrate and share cores with each other's
+    pollers: SCALE_r01's e2e efficiency of 0.52 at N = 8 was two ranks whose host issue time doubled)."""
+    try:
+        cores = sorted(os.sched_getaffinity(0))
+    except AttributeError:
+        return None
+    per = len(cores) // max(1, local_world)
+    if local_world <= 1 or per < 2:
+        return None
+    mine = cores[local_rank * per:(local_rank + 1) * per]
+    os.sched_setaffinity(0, mine)
+    return mine
 
 
 def parse():
@@ -97,6 +148,7 @@ def parse():
     ap.add_argument("--envs", type=int, default=0, help="envs per GPU (default: the workload's 4096)")
     ap.add_argument("--precision", default="bf16", choices=["bf16", "fp32"])
     ap.add_argument("--no-extras", action="store_true", help="skip at_scale / update / cpu_baseline legs")
+    ap.add_argument("--sweep-steps", type=int, default=300, help="kamma_eval_sweep: eval steps per timed sweep")
     return ap.parse_args()
 
 
@@ -161,7 +213,8 @@ class CpuPort:
         v = VARIANTS[wl["variant"]]
         self.rng = np.random.default_rng(seed)
         self.env = EnvOracle(v, synth_state(v, n, self.rng, physics=True), EnvParams(physics=True))
-        self.agent = AgentOracle(6, wl["act_dim"], "sigmoid", ou=(0.15, 0.1, wl["ou"]), exploration_timesteps=wl["T_e"])
+        self.agent = AgentOracle(6, wl["act_dim"], "sigmoid", ou=(0.15, 0.1, wl["ou"]) if wl["ou"] else None,
+                                 exploration_timesteps=wl["T_e"])
         self.n, self.A = n, wl["act_dim"]
         self.obs = np.zeros((n, 6), np.float32)
         self.t = 0
@@ -224,9 +277,9 @@ def run_reference(args, wl, n):
     if int(os.environ.get("RANK", "0")) != 0:
         return
     port = CpuPort(wl, n)
-    for _ in range(max(args.warmup, 1) if args.warmup <= 3 else 3):
+    for _ in range(args.warmup):          # exactly --warmup untimed and --steps timed steps (~10 ms each at 4096 envs)
         port.step()
-    steps = min(args.steps, 50)
+    steps = args.steps
     t0 = time.perf_counter()
     for _ in range(steps):
         port.step()
@@ -236,9 +289,9 @@ def run_reference(args, wl, n):
     sample = f"{steps} steps x {n} envs (single host process; the CPU path does not shard across GPUs)"
     print(json.dumps({
         "impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": steps,
-        "warmup": min(args.warmup, 3), "ms_per_step": 1e3 * dt / steps, "higher_is_better": True, "scaling": "weak",
+        "warmup": args.warmup, "ms_per_step": 1e3 * dt / steps, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f32 (dynamics f64)", "data": "synthetic",
-        "config": {"workload": wl["name"], "envs_per_gpu": n, "l2": "n/a (host)"},
+        "config": workload_config(wl, n, args.gpus),
         "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
         "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "note": "reference = pure Python on Isaac Sim/PhysX + skrl: not runnable on this box; this is its pinned CPU port",
@@ -249,7 +302,7 @@ def run_reference(args, wl, n):
 class World:
     """task + memory + agent of one rank, wired like train/train_kamma_4d_nofifo_random_RLIL.py:94-186."""
 
-    def __init__(self, wl, n, precision, device, seed):
+    def __init__(self, wl, n, precision, device, seed, model_seed=None):
         import torch
 
         import options_in_simulation_b200 as ois
@@ -258,7 +311,7 @@ class World:
         from options_in_simulation_b200.memory import memory_size_for
 
         self.torch, self.n, self.wl = torch, n, wl
-        torch.manual_seed(seed)
+        torch.manual_seed(seed if model_seed is None else model_seed)
         cfg = script_cfg(n, seed=seed, sim_device=str(device))
         self.task = ois.TorqueDistributionTask(sim_config=cfg, variant=wl["variant"], seed=seed)
         self.env = ois.wrap_env(self.task)
@@ -266,13 +319,15 @@ class World:
         osp, asp = self.task.observation_space, self.task.action_space
         models = {"policy": A.DeterministicActor(osp, asp, dev), "target_policy": A.DeterministicActor(osp, asp, dev),
                   "critic": A.Critic(osp, asp, dev), "target_critic": A.Critic(osp, asp, dev)}
-        self.memory = ois.RandomMemory(memory_size=memory_size_for(wl["memory_total"], n), num_envs=n, device=dev,
-                                       replacement=False)
+        # capacity rule: the scripts' memory_size counts transitions at numEnvs = 1; keep the total
+        mem_cls = ois.FIFOMemory if wl["memory"] == "fifo" else ois.RandomMemory
+        steps_cap = max(memory_size_for(wl["memory_total"], n), -(-512 // n))     # never below one batch of 512
+        self.memory = mem_cls(memory_size=steps_cap, num_envs=n, device=dev, replacement=False)
         cfg_a = {"batch_size": 512, "discount_factor": 0.999, "polyak": 0.005, "actor_learning_rate": 3e-4,
                  "critic_learning_rate": 1e-3, "random_timesteps": 0, "learning_starts": 0,
                  "mixed_precision": precision == "bf16", "sampler": "device", "graph_update": True,
                  "state_preprocessor": A.RunningStandardScaler, "state_preprocessor_kwargs": {"size": osp, "device": dev},
-                 "exploration": {"noise": A.OrnsteinUhlenbeckNoise(0.15, 0.1, wl["ou"], device=dev),
+                 "exploration": {"noise": A.OrnsteinUhlenbeckNoise(0.15, 0.1, wl["ou"], device=dev) if wl["ou"] else None,
                                  "initial_scale": 1.0, "final_scale": 1e-4, "timesteps": wl["T_e"]},
                  "experiment": {"write_interval": 0, "checkpoint_interval": 0}}
         self.agent = A.DDPG(models=models, memory=self.memory, cfg=cfg_a, observation_space=osp, action_space=asp, device=dev)
@@ -391,23 +446,42 @@ def e2e_graph_timed(world, steps, warmup, mode=True):
     g = RolloutGraph(world.env, world.agent, world.t, world.T, host_io=mode)
     g.h_states.copy_(world.obs)
 
-    def one():
-        obs, rew, term = g.step()          # synchronised: results are in pinned host memory
-        g.h_states.copy_(obs)              # the host consumes them: next step's input (host memcpy, 96 KB at N = 4096)
+    if mode is True:
+        # zero-copy: step t reads its observations from the pinned pack step t-1 wrote; step() returns when the env
+        # kernel's completion word says the step's results are in host memory (no device synchronise, no host copy)
+        def one():
+            g.step()
+    else:
+        def one():
+            obs, rew, term = g.step()      # synchronised: results are in pinned host memory
+            g.h_states.copy_(obs)          # copy-node mode: the host hands them back (host memcpy, 96 KB at N = 4096)
 
-    for _ in range(warmup + 2):            # +2: the eager warm-up step and the capture
+    for _ in range(warmup + 3):            # +3: the eager warm-up step and the capture(s)
         one()
     a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     torch.cuda.synchronize()
+    t0 = time.perf_counter()
     a.record()
     for _ in range(steps):
         one()
     b.record()
     torch.cuda.synchronize()
+    wall_ms = 1e3 * (time.perf_counter() - t0) / steps
+    ms = max(a.elapsed_time(b) / steps, wall_ms) if mode is True else a.elapsed_time(b) / steps
+    pipelined_ms = None
+    if mode is True:                       # one step in flight while the host consumes the previous one
+        g.step(wait=False)
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        for _ in range(steps):
+            g.step(wait=False)
+            g.wait(lag=1)
+        g.wait()
+        pipelined_ms = 1e3 * (time.perf_counter() - t0) / steps
     world.t = g.timestep
     world.task._obs_clipped[0].copy_(g.h_next_states)     # zero-copy mode leaves the task's device-side copy untouched
     world.obs = world.task.obs_clipped
-    return a.elapsed_time(b) / steps, n * 6 * 4, n * 29
+    return ms, n * 6 * 4, n * 29, pipelined_ms
 
 
 def graph_device_timed(world, steps, warmup, flush):
@@ -466,6 +540,158 @@ def train_timed(world, flush, steps=30):
     return sum(a.elapsed_time(b) for a, b in ev) / steps
 
 
+def weights_identical_across_ranks(agent, dist, device):
+    """Bit-level check that the data-parallel update left the same parameters on every rank: per-network (sum, xor-free
+    integer checksum) gathered and compared.  Returns (ok, detail)."""
+    import torch
+
+    sums = []
+    for name in ("policy", "critic", "target_policy", "target_critic"):
+        flat = getattr(agent, name).flat
+        sums.append(flat.view(torch.int32).to(torch.int64).sum())          # exact: any differing bit changes it
+        sums.append((flat.view(torch.int32).to(torch.int64) * torch.arange(1, flat.numel() + 1, device=device)).sum())
+    mine = torch.stack(sums)
+    allr = [torch.empty_like(mine) for _ in range(dist.get_world_size())]
+    dist.all_gather(allr, mine)
+    ok = all(torch.equal(allr[0], x) for x in allr)
+    return ok, [x.tolist() for x in allr] if not ok else None
+
+
+def update_legs(world, args, flush, dist, device, world_size, rank):
+    """DDPG._update (one CUDA graph per update, B = 512) and the reference-cadence train step at this world size.
+    N > 1: the gradient exchange runs three ways — inside the Adam kernels over NVLink peer memory ("peer"), as NCCL
+    all-reduces captured in the same graph ("nccl"), and not at all ("local", for the collective's cost by difference)."""
+    torch = world.torch
+    agent = world.agent
+
+    def timed_max(fn):
+        if world_size > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+        v = fn()
+        if world_size > 1:
+            t = torch.tensor([v], device=device, dtype=torch.float64)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            v = float(t.item())
+        return v
+
+    def set_mode(mode):
+        agent._dp_exchange = mode
+        agent._graph = None              # the captured update contains (or not) the exchange: capture again
+        torch.cuda.synchronize()
+
+    out = {"batch": 512}
+    first = agent._dp_exchange           # "peer" (or "nccl" when CUDA IPC is unavailable), "none" at N = 1
+    upd_ms = timed_max(lambda: update_timed(world))
+    train_ms = timed_max(lambda: train_timed(world, flush))
+    out.update({"ms_per_update": upd_ms, "tflops": UPDATE_FLOP / (upd_ms * 1e-3) / 1e12,
+                "path": ("bf16 tcgen05 grouped GEMMs" if args.precision == "bf16" else "fp32 SIMT") + ", one CUDA graph per update",
+                "train_ms_per_step": train_ms, "train_env_steps_per_s": world_size * world.n * 1e3 / train_ms,
+                "note": "DDPG._update; train_* = one policy step + 2 updates, the reference cadence "
+                        "(base_KA_DDPG.py:265,283), max over ranks; not in the metric"})
+    if world_size == 1:
+        return out
+    ok, detail = weights_identical_across_ranks(agent, dist, device)
+    if not ok:
+        raise SystemExit(f"data-parallel update ({first}): ranks hold different weights: {detail}")
+    coll = {"exchange": first, "weights_identical_across_ranks": True, "ms_per_update": {first: upd_ms},
+            "bytes_per_update_per_rank": 4 * (agent.critic.num_params + agent.policy.num_params),
+            "reductions_per_update": 2, "in_update_graph": True}
+    if agent._exchange is not None:
+        done_c, done_a, status = agent._exchange.status()
+        coll["peer_exchanges_completed"] = [done_c, done_a]
+        coll["peer_barrier_timeouts"] = status
+        if status:
+            raise SystemExit(f"peer exchange: a barrier timed out waiting for rank {status - 1}")
+    if first == "peer":
+        set_mode("nccl")
+        coll["ms_per_update"]["nccl"] = timed_max(lambda: update_timed(world))
+        ok, detail = weights_identical_across_ranks(agent, dist, device)
+        if not ok:
+            raise SystemExit(f"data-parallel update (nccl): ranks hold different weights: {detail}")
+    set_mode("local")                    # no exchange at all: every rank applies its own gradient (timing only; last)
+    coll["ms_per_update"]["local"] = timed_max(lambda: update_timed(world))
+    coll["us_per_update"] = {k: 1e3 * (v - coll["ms_per_update"]["local"]) for k, v in coll["ms_per_update"].items() if k != "local"}
+    coll["overlap"] = ("none possible: the critic's reduced gradient feeds the critic step that the policy pass reads "
+                       "(ddpg.py:416-423); the actor forward of ddpg.py:420 is already hoisted above the exchange")
+    out["collective"] = coll
+    set_mode(first)
+    return out
+
+
+def run_eval_sweep(args, wl, n, device, rank, world_size, dist):
+    """BASELINE.json configs[4]: every rank rolls its shard of KAMMA_eval envs over the speed ramp; the per-speed-bin
+    tracking-error sums are all-reduced ONCE at the end (evaluate.tracking_error_sweep)."""
+    import torch
+
+    import options_in_simulation_b200 as ois
+    from options_in_simulation_b200 import parallel as P
+    from options_in_simulation_b200.evaluate import phase_lock, tracking_error_sweep
+
+    world = World(wl, n, args.precision, device, seed=1234 + rank, model_seed=77)    # ONE checkpoint on every rank
+    period = phase_lock(world.task)
+    steps = max(args.sweep_steps, 2 * period + 10)
+
+    def barrier():
+        if world_size > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    sampler = ClockSampler(device.index) if rank == 0 else None
+    out = None
+    for it in range(2):                  # first sweep warms up (lazy init, capture); the second is timed
+        phase_lock(world.task)
+        barrier()
+        if it == 1 and rank == 0:
+            sampler.start()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        t0 = time.perf_counter()
+        a.record()
+        out = tracking_error_sweep(world.env, world.agent, steps, skip_steps=period)
+        b.record()
+        torch.cuda.synchronize()
+        wall_ms = 1e3 * (time.perf_counter() - t0)
+        dev_ms = a.elapsed_time(b)
+    clocks = sampler.stop() if rank == 0 else None
+    # the one collective of this workload, timed on its own: two [bins] fp64 vectors
+    te = torch.zeros(10, dtype=torch.float64, device=device)
+    cnt = torch.zeros(10, dtype=torch.float64, device=device)
+    for _ in range(3):
+        P.reduce_sums(te, cnt)
+    barrier()
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a.record()
+    for _ in range(20):
+        P.reduce_sums(te, cnt)
+    b.record()
+    torch.cuda.synchronize()
+    reduce_us = 1e3 * a.elapsed_time(b) / 20
+    t = torch.tensor([dev_ms, wall_ms, reduce_us], device=device, dtype=torch.float64)
+    if world_size > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    dev_ms, wall_ms, reduce_us = t.tolist()
+    if rank != 0:
+        return
+    total = world_size * n * steps
+    log_bytes = (steps + 1) * 24 * 4
+    line = {"metric": METRIC, "value": total / (dev_ms * 1e-3), "unit": UNIT, "n_gpus": world_size, "steps": steps, "warmup": steps,
+            "ms_per_step": dev_ms / steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "bf16 (actor MLP, fp32 accumulate) + f32 (env)" if args.precision == "bf16" else "f32", "data": "synthetic",
+            "config": workload_config(wl, n, world_size),
+            "e2e": {"value": total / (wall_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": log_bytes / steps,
+                    "ms_per_step": wall_ms / steps,
+                    "path": "evaluate.tracking_error_sweep (the public call): device-resident rollout, episode statistics reduced "
+                            "into a device log by the env kernel, ONE device->host read of the log and ONE all-reduce at the end; "
+                            "wall clock around the call"},
+            "gpu_launches": world.launches(), "clocks": clocks,
+            "sweep": {"speed": [round(float(x), 3) for x in out["speed"]],
+                      "tracking_error": [round(float(x), 5) for x in out["tracking_error"]],
+                      "episodes": [int(x) for x in out["episodes"]], "episode_period_steps": period,
+                      "all_reduce_us": reduce_us, "all_reduce_bytes": 2 * 10 * 8,
+                      "note": "random-init policy: the curve is a parity artefact (tests/test_eval_sweep_gpu.py), not a control result"}}
+    print(json.dumps(line), flush=True)
+
+
 def main():
     args = parse()
     wl = WORKLOADS[args.workload]
@@ -473,6 +699,9 @@ def main():
     if args.impl == "reference":
         run_reference(args, wl, n)
         return
+
+    rank, local, world_size = int(os.environ.get("RANK", 0)), int(os.environ.get("LOCAL_RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
+    pinned = pin_to_cores(local, int(os.environ.get("LOCAL_WORLD_SIZE", world_size)))     # before any thread is created
 
     import torch
     import torch.distributed as dist
@@ -483,11 +712,16 @@ def main():
         raise SystemExit("bench.py needs a CUDA device (B200); there is no CPU fallback for the product path")
     if not os.path.exists(ois.LIB_PATH):
         raise SystemExit(f"{ois.LIB_PATH} missing: run `python -c 'import __graft_entry__ as g; g.build()'` first")
-    rank, local, world_size = int(os.environ.get("RANK", 0)), int(os.environ.get("LOCAL_RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
     torch.cuda.set_device(local)
     device = torch.device("cuda", local)
     if world_size > 1:
         dist.init_process_group("nccl", device_id=device)
+    if args.workload == "kamma_eval_sweep":
+        run_eval_sweep(args, wl, n, device, rank, world_size, dist)
+        if world_size > 1:
+            dist.barrier()
+            dist.destroy_process_group()
+        return
     peaks = {}
     try:
         peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
@@ -513,24 +747,24 @@ def main():
     barrier()
     e2e_eager_ms, _, _ = e2e_timed(world, min(args.steps, 200), 5)
     barrier()
-    e2e_ms, h2d, d2h = e2e_graph_timed(world, min(args.steps, 200), 5)
+    e2e_ms, h2d, d2h, e2e_pipe_ms = e2e_graph_timed(world, min(args.steps, 200), 5)
     barrier()
-    e2e_copy_ms, _, _ = e2e_graph_timed(world, min(args.steps, 200), 5, mode="copy")
+    e2e_copy_ms, _, _, _ = e2e_graph_timed(world, min(args.steps, 200), 5, mode="copy")
     barrier()
     graph_ms = graph_device_timed(world, args.steps, 5, flush)
     barrier()
     host_ms = host_issue_timed(world)
     barrier()
     clocks = sampler.stop() if rank == 0 else None      # sampled across ALL the timed legs above
-    per_rank = [[ms, graph_ms, host_ms]]
+    per_rank = [[ms, graph_ms, host_ms, e2e_ms]]
     if world_size > 1:
         mine = torch.tensor(per_rank[0], device=device, dtype=torch.float64)
         allr = [torch.empty_like(mine) for _ in range(world_size)]
         dist.all_gather(allr, mine)
         per_rank = [a.tolist() for a in allr]
-        t = torch.tensor([ms, e2e_ms, e2e_eager_ms, graph_ms, e2e_copy_ms], device=device, dtype=torch.float64)
+        t = torch.tensor([ms, e2e_ms, e2e_eager_ms, graph_ms, e2e_copy_ms, e2e_pipe_ms], device=device, dtype=torch.float64)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        ms, e2e_ms, e2e_eager_ms, graph_ms, e2e_copy_ms = t.tolist()
+        ms, e2e_ms, e2e_eager_ms, graph_ms, e2e_copy_ms, e2e_pipe_ms = t.tolist()
     # the same device-resident step issued two ways, both timed over EXACTLY args.steps steps, max over ranks: call by
     # call (2 launches per step from Python) and as one graph launch per step; the headline is the faster of the two
     # (with several ranks sharing a host the call-by-call loop becomes host-bound on the slowest rank)
@@ -540,37 +774,46 @@ def main():
         ms, issue, launches = graph_ms, "rollout.RolloutGraph replay (one graph launch per step)", 2 * args.steps
     value = world_size * n * 1e3 / ms
     e2e_value = world_size * n * 1e3 / e2e_ms
+    e2e_sorted = sorted(r[3] for r in per_rank)
 
     out = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world_size, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "bf16 (actor MLP, fp32 accumulate) + f32 (env)" if args.precision == "bf16" else "f32",
         "data": "synthetic",
-        "config": {"workload": wl["name"], "envs_per_gpu": n, "variant": wl["variant"], "act_dim": wl["act_dim"],
-                   "replay": "fused append, rank-local shard", "rng": "in-kernel Philox",
-                   "l2": "flushed between timed steps (256 MiB memset outside the event brackets)",
-                   "parallelism": f"env/replay shards x{world_size}, no data-path collective", "issue": issue},
+        "config": workload_config(wl, n, world_size),
+        "issue": issue,
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                 "ms_per_step": e2e_ms,
-                "path": "rollout.RolloutGraph(host_io=True): one CUDA-graph launch per step = actor kernel reading the "
-                        "observations from pinned host memory in place + env kernel (step, replay append, step-control "
-                        "advance) storing obs|rew|reset to pinned host memory in place; host sync every step; the bytes "
-                        "below cross PCIe every step as zero-copy loads / stores",
+                "path": "rollout.RolloutGraph(host_io=True): one C call per step (ois_graph_launch_wait) = CUDA-graph launch of "
+                        "the actor kernel reading the observations from pinned host memory in place + the env kernel (step, "
+                        "replay append, step-control advance) storing obs|rew|reset to pinned host memory in place, then a "
+                        "spin on the pinned completion word the env kernel's last CTA writes; the bytes below cross PCIe "
+                        "every step as zero-copy loads / stores; max(device events, host wall clock) per step, max over ranks",
+                "per_rank_ms": {"median": e2e_sorted[len(e2e_sorted) // 2], "max": e2e_sorted[-1], "min": e2e_sorted[0]},
+                "pipelined_ms_per_step": e2e_pipe_ms,
+                "pipelined_value": world_size * n * 1e3 / e2e_pipe_ms if e2e_pipe_ms else None,
+                "pipelined_note": "same path, one step in flight while the host waits for the previous one (step(wait=False) + "
+                                  "wait(lag=1)); not the headline",
                 "copy_nodes_ms_per_step": e2e_copy_ms,
                 "call_by_call_ms_per_step": e2e_eager_ms,
-                "call_by_call_value": world_size * n * 1e3 / e2e_eager_ms},
+                "call_by_call_value": world_size * n * 1e3 / e2e_eager_ms,
+                "host_cores_per_rank": len(pinned) if pinned else None},
         "issue_paths": {"call_by_call_ms_per_step": call_ms, "graph_replay_ms_per_step": graph_ms,
                         "host_issue_ms_per_step": max(r[2] for r in per_rank),
                         "per_rank_ms": [[round(x, 5) for x in r] for r in per_rank],
-                        "note": "max over ranks; per_rank_ms = [call-by-call, graph replay, host issue time] per rank"},
+                        "note": "max over ranks; per_rank_ms = [call-by-call, graph replay, host issue time, e2e] per rank"},
         "gpu_launches": launches, "clocks": clocks,
     }
 
+    traffic, traffic_src = ncu_traffic()
+    if not args.no_extras:                       # every rank takes part: at N > 1 the update contains the exchange
+        out["update"] = update_legs(world, args, flush, dist, device, world_size, rank)
     if rank == 0:
         act_ms, env_ms = kernel_split(world, min(args.steps, 100), flush)
         env_bytes = (ENV_BYTES[wl["variant"]] + REPLAY_BYTES) * n
         act_flop = ACTOR_FLOP[wl["act_dim"]] * n
-        tr = (lambda k: NCU_TRAFFIC.get((k, n)) if args.workload == "kamma_4d" else None)
+        tr = (lambda k: traffic.get((k, n)) if args.workload == "kamma_4d" else None)
         env_roof = {"kernel": "env_step_kernel", "bound": "hbm", "achieved": env_bytes / (env_ms * 1e-3) / 1e9,
                     "peak": hbm_peak, "unit": "GB/s", "traffic": tr("env"), "ms": env_ms}
         act_roof = {"kernel": "actor MLP (ois_agent_act)", "bound": "tensor", "achieved": act_flop / (act_ms * 1e-3) / 1e12,
@@ -578,17 +821,11 @@ def main():
         for r in (env_roof, act_roof):
             r["frac"] = r["achieved"] / r["peak"]
             r["peak_source"] = peak_src
+            r["traffic_source"] = traffic_src
         dom, other = (act_roof, env_roof) if act_ms >= env_ms else (env_roof, act_roof)
         out["roofline"] = dom
         out["roofline_other"] = other
         if not args.no_extras and world_size == 1:
-            upd_ms = update_timed(world)
-            train_ms = train_timed(world, flush)
-            out["update"] = {"ms_per_update": upd_ms, "batch": 512, "tflops": UPDATE_FLOP / (upd_ms * 1e-3) / 1e12,
-                             "path": "bf16 tcgen05 grouped GEMMs, one CUDA graph per update" if args.precision == "bf16" else "fp32 SIMT",
-                             "train_ms_per_step": train_ms, "train_env_steps_per_s": n * 1e3 / train_ms,
-                             "note": "DDPG._update; train_* = one policy step + 2 updates, the reference cadence "
-                                     "(base_KA_DDPG.py:265,283); not in the metric"}
             scale = []
             del world
             torch.cuda.empty_cache()
@@ -601,7 +838,7 @@ def main():
                     w.step()
                 m, _ = device_timed(w, 20, 3, flush if small else None)
                 scale.append({"envs": big, "value": big * 1e3 / m, "ms_per_step": m, "act_ms": a_ms, "env_ms": e_ms,
-                              "env_traffic": NCU_TRAFFIC.get(("env", big)), "act_traffic": NCU_TRAFFIC.get(("actor", big)),
+                              "env_traffic": traffic.get(("env", big)), "act_traffic": traffic.get(("actor", big)),
                               "env_hbm_frac": (ENV_BYTES[wl["variant"]] + REPLAY_BYTES) * big / (e_ms * 1e-3) / 1e9 / hbm_peak,
                               "act_tensor_frac": ACTOR_FLOP[wl["act_dim"]] * big / (a_ms * 1e-3) / 1e12 / tc_peak,
                               "l2": "flushed between steps" if small else "state exceeds L2 (no flush needed)"})

@@ -32,7 +32,7 @@ extern "C" {
 #define OIS_ERR_CUDA (-2)
 #define OIS_ERR_UNSUPPORTED (-3)
 
-#define OIS_ABI_VERSION 2
+#define OIS_ABI_VERSION 3
 
 /* ------------------------------------------------------------------------------------------------
  * Environment: TorqueDistributionTask (src/my_envs/KAMMA_medium.py and its variants)
@@ -149,6 +149,11 @@ typedef struct OisEnvIO {
                                    `obs` itself stays the raw obs_buf */
   const OisStepCtl* ctl;        /* nullable; when set: philox_offset and flag_slot come from it, and the replay_* pointers
                                    are the BASE of the (memory_size, N, dim) tensors, row ctl->replay_row is written */
+  uint32_t* done_flag;          /* nullable, needs ctl with self_advance: a word of PINNED HOST memory (device-visible
+                                   address).  When every store of this launch has been performed at system scope — obs /
+                                   rew / reset may themselves be pinned host buffers — the kernel's last CTA stores
+                                   (uint32_t)ctl->step (the value AFTER the advance, i.e. steps completed) there, so a host
+                                   in the loop can wait for the step with ois_host_wait instead of a device synchronise */
 } OisEnvIO;
 
 /* One policy step for all envs: pre_physics_step + decimation physics sub-steps + post_physics_step
@@ -255,6 +260,36 @@ int ois_agent_act(OisAgent* agent, const float* actor_params, const OisScaler* s
 int ois_mlp_forward(OisAgent* agent, const OisMlpShape* shape, const float* params, const float* x, float* y,
                     int64_t n_rows, void* stream);
 
+/* ------------------------------------------------------------------------------------------------
+ * Data-parallel gradient exchange over NVLink peer memory (one process per GPU, one node).
+ * Replaces the two Model.reduce_parameters calls of DDPG._update (src/my_agents/ddpg.py:409-410 critic,
+ * :431-432 actor; skrl: all_reduce(SUM) of the flat gradients, then / world_size) and the process-group
+ * set-up of src/my_agents/base.py:88-92.  Every rank owns one exchange block in its HBM that holds its two
+ * flat gradient buffers; the blocks are mapped into every peer with CUDA IPC and the Adam kernels of
+ * ois_ddpg_update_phase read all ranks' gradients in place (csrc/comm.cuh states the protocol).  No host
+ * involvement per update: the exchange is part of the captured update graph.
+ * ---------------------------------------------------------------------------------------------- */
+#define OIS_MAX_RANKS 8
+#define OIS_IPC_HANDLE_BYTES 64
+typedef struct OisComm OisComm;   /* opaque */
+
+/* Allocate this rank's exchange block (zeroed): header + critic gradient + actor gradient (flat fp32 counts). */
+int ois_comm_create(OisComm** out, int32_t rank, int32_t world, int64_t critic_params, int64_t actor_params);
+/* The block's CUDA IPC handle (OIS_IPC_HANDLE_BYTES bytes) to hand to the other ranks by any host channel. */
+int ois_comm_export(OisComm* comm, void* handle_out);
+/* Map the peers' blocks: `handles` = world x OIS_IPC_HANDLE_BYTES bytes in rank order (own entry ignored). */
+int ois_comm_connect(OisComm* comm, const void* handles, int32_t count);
+/* Same-process variant: all ranks' OisComm objects live in this process (tests; several GPUs driven by one process). */
+int ois_comm_connect_local(OisComm* comm, OisComm* const* all, int32_t count);
+/* This rank's gradient buffer inside the block: net 0 = critic, 1 = actor.  These are the buffers to pass as
+ * OisUpdateIO.critic_grad / actor_grad when OisUpdateIO.comm is set. */
+void* ois_comm_grad(OisComm* comm, int32_t net);
+/* words_host[0..1] = completed critic / actor exchanges, [2] = 0, or p + 1 when a barrier gave up waiting for rank p. */
+int ois_comm_status(OisComm* comm, uint32_t* words_host);
+/* Test hook: mark every rank as having published exchange `epoch` of `kind` in THIS rank's header (host write). */
+int ois_comm_debug_publish(OisComm* comm, int32_t kind, uint32_t epoch);
+int ois_comm_destroy(OisComm* comm);
+
 typedef struct OisUpdateIO {
   /* sampled batch (ois_replay_gather outputs) */
   const float* states; const float* actions; const float* rewards; const float* next_states;
@@ -271,6 +306,12 @@ typedef struct OisUpdateIO {
   /* outputs for logging (ddpg.py:452-461): critic_loss, policy_loss, q max/min/mean, target max/min/mean */
   float* stats;               /* [8], nullable */
   const int64_t* adam_step_dev; /* optional device-resident 1-based step counter (CUDA-graph replay); overrides adam_step */
+  OisComm* comm;              /* nullable; when set (world > 1): the Adam kernels of phases 1 and 2 first exchange the
+                                 gradients of all ranks over peer memory (sum in rank order) — critic_grad / actor_grad must
+                                 be ois_comm_grad(comm, 0 / 1) and grad_scale 1 / world */
+  int32_t batch_rows;         /* rows of the batch tensors; 0 = the handle's batch_size.  A shorter batch (the replay
+                                 memory holds fewer than batch_size transitions, which the reference trains on as is) is
+                                 served by the fp32 path only */
 } OisUpdateIO;
 
 /* DDPG._update (ddpg.py:357-444) split at the two points where skrl all-reduces gradients:
@@ -281,12 +322,23 @@ typedef struct OisUpdateIO {
 int ois_ddpg_update_phase(OisAgent* agent, const OisScaler* scaler, const OisUpdateIO* io, int32_t phase,
                           float grad_scale, void* stream);
 
+/* ------------------------------------------------------------------------------------------------
+ * Host in the loop: the trainer's loop body (src/my_trainers/base_KA_DDPG.py:175-219) is one captured CUDA graph per
+ * policy step (act -> env step -> fused record_transition).  graph_exec is a cudaGraphExec_t.
+ * ---------------------------------------------------------------------------------------------- */
+int ois_graph_launch(void* graph_exec, void* stream);
+/* Spin (no driver call) until the pinned host word has reached `expect` (wrap-safe >=), i.e. until the env kernel that
+ * was given it as OisEnvIO.done_flag has completed that many steps.  timeout_ns <= 0: wait for ever. */
+int ois_host_wait(const uint32_t* host_flag, uint32_t expect, int64_t timeout_ns);
+/* ois_graph_launch followed by ois_host_wait in one call. */
+int ois_graph_launch_wait(void* graph_exec, void* stream, const uint32_t* host_flag, uint32_t expect, int64_t timeout_ns);
+
 /* ------------------------------------------------------------------------------------------------ */
 const char* ois_last_error_string(void);
 int ois_abi_version(void);
 /* sizeof() of the ABI structs as this library was compiled, so a foreign-language mirror (ctypes, cgo ...)
  * can verify its layout: 0 OisEnvParams, 1 OisEnvState, 2 OisEnvIO, 3 OisMlpShape, 4 OisScaler, 5 OisActIO,
- * 6 OisUpdateIO; -1 for an unknown index. */
+ * 6 OisUpdateIO, 7 OisStepCtl; -1 for an unknown index. */
 int ois_struct_size(int which);
 /* name of the SASS feature set compiled in, e.g. "sm_100a tcgen05+tma" */
 const char* ois_build_info(void);

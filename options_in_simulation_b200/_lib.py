@@ -15,6 +15,8 @@ CSRC = os.path.join(_HERE, "csrc")
 
 OIS_EP_STATS_LEN = 24
 OIS_COMP0_LEN = 32
+OIS_MAX_RANKS = 8
+OIS_IPC_HANDLE_BYTES = 64
 BLEND_LINEAR, BLEND_SWITCH = 0, 1
 GAMMA_CONST, GAMMA_DECAY = 0, 1
 CMD_RAND, CMD_GV, CMD_EVAL, CMD_BD = 0, 1, 2, 3
@@ -52,7 +54,7 @@ class EnvIO(C.Structure):
         ("guiding", _p), ("ep_stats", _p), ("comp0", _p), ("any_reset_flags", _p), ("flag_slot", _i32),
         ("replay_states", _p), ("replay_actions", _p), ("replay_rewards", _p), ("replay_next_states", _p),
         ("replay_terminated", _p), ("replay_truncated", _p), ("relabel", _i32), ("clip_obs", _f),
-        ("clip_actions", _f), ("obs_clipped", _p), ("ctl", _p),
+        ("clip_actions", _f), ("obs_clipped", _p), ("ctl", _p), ("done_flag", _p),
     ]
 
 
@@ -87,7 +89,7 @@ class UpdateIO(C.Structure):
                                   "actor_m", "actor_v", "critic_m", "critic_v")] + [
         ("adam_step", _i64), ("actor_lr", _f), ("critic_lr", _f), ("beta1", _f), ("beta2", _f), ("adam_eps", _f),
         ("discount", _f), ("polyak", _f), ("actor_grad", _p), ("critic_grad", _p), ("stats", _p),
-        ("adam_step_dev", _p)]
+        ("adam_step_dev", _p), ("comm", _p), ("batch_rows", _i32)]
 
 
 # every symbol include/ois_b200.h declares: (name, restype, argtypes)
@@ -108,6 +110,17 @@ SYMBOLS = {
     "ois_mlp_forward": (C.c_int, [_p, _PP(MlpShape), _p, _p, _p, _i64, _p]),
     "ois_ddpg_update_phase": (C.c_int, [_p, _PP(Scaler), _PP(UpdateIO), _i32, _f, _p]),
     "ois_step_ctl_advance": (C.c_int, [_p, _p]),
+    "ois_graph_launch": (C.c_int, [_p, _p]),
+    "ois_host_wait": (C.c_int, [_p, C.c_uint32, _i64]),
+    "ois_graph_launch_wait": (C.c_int, [_p, _p, _p, C.c_uint32, _i64]),
+    "ois_comm_create": (C.c_int, [_PP(_p), _i32, _i32, _i64, _i64]),
+    "ois_comm_export": (C.c_int, [_p, _p]),
+    "ois_comm_connect": (C.c_int, [_p, _p, _i32]),
+    "ois_comm_connect_local": (C.c_int, [_p, _PP(_p), _i32]),
+    "ois_comm_grad": (_p, [_p, _i32]),
+    "ois_comm_status": (C.c_int, [_p, _PP(C.c_uint32)]),
+    "ois_comm_debug_publish": (C.c_int, [_p, _i32, C.c_uint32]),
+    "ois_comm_destroy": (C.c_int, [_p]),
     "ois_last_error_string": (C.c_char_p, []),
     "ois_abi_version": (C.c_int, []),
     "ois_build_info": (C.c_char_p, []),
@@ -143,7 +156,7 @@ def lib() -> C.CDLL:
             fn = getattr(handle, name)    # AttributeError if the symbol is not exported
             fn.restype = res
             fn.argtypes = args
-        if handle.ois_abi_version() != 2:
+        if handle.ois_abi_version() != 3:
             raise OisError("libois_b200.so ABI version mismatch")
         _lib = handle
     return _lib

@@ -53,7 +53,11 @@ DDPG_DEFAULT_CONFIG = {   # src/my_agents/ddpg.py:19-61
     "sampler": "host",        # "host": torch.randperm like the reference; "device": Philox/Feistel kernel (no host sync)
     "track_stats_interval": 0,  # > 0: read losses / Q stats back every that many updates (the reference does every update)
     "graph_update": False,    # capture gather + the three update phases into ONE CUDA graph and replay it (needs
-                              # sampler "device", world_size 1): ~50 launches per update become one graph launch
+                              # sampler "device"): the launches of an update become one graph launch; under torchrun the
+                              # gradient exchange is part of the graph
+    "dp_exchange": "peer",    # world_size > 1, how the two gradient reductions of ddpg.py:409-410,431-432 run:
+                              # "peer": inside the Adam kernels over NVLink peer memory (parallel.PeerExchange, csrc/comm.cuh);
+                              # "nccl": dist.all_reduce between the phases (skrl's way), also capturable
 }
 
 _LAYER_KEYS = ("net.0", "net.2", "net.4", "net.6")   # nn.Sequential indices of the Linear layers
@@ -127,8 +131,7 @@ class DeterministicMLP:
         for key, ((wo, r, c), (bo, _)) in zip(_LAYER_KEYS, self.offsets):
             self.flat[wo:wo + r * c].copy_(sd[key + ".weight"].reshape(-1).to(self.device, torch.float32))
             self.flat[bo:bo + r].copy_(sd[key + ".bias"].to(self.device, torch.float32))
-        if self._agent is not None:
-            self._agent._weights_changed()
+        self._master_changed()
 
     def set_mode(self, mode):
         self.training = mode == "train"
@@ -142,9 +145,17 @@ class DeterministicMLP:
         else:   # p.mul_(1 - polyak); p.add_(polyak * q)  — one fused pass is what the update kernel does; this
             # standalone call keeps the Model API and uses torch only for this cold path
             self.flat.mul_(1 - polyak).add_(model.flat, alpha=polyak)
+        self._master_changed()
 
     def broadcast_parameters(self, rank=0):
         P.broadcast_flat(self.flat, rank)
+        self._master_changed()
+
+    def _master_changed(self):
+        """The fp32 master was written behind the C handle's back: its cached bf16 images (tensor-core update, actor
+        stream image) and any captured update graph are stale."""
+        if self._agent is not None:
+            self._agent._weights_changed()
 
     def reduce_parameters(self, flat_grad):
         """skrl Model.reduce_parameters on the flat gradient buffer; returns the 1/world_size factor to apply."""
@@ -344,10 +355,22 @@ class DDPG:
             self._state_preprocessor = None
         self._grad_actor = torch.zeros_like(self.policy.flat)
         self._grad_critic = torch.zeros_like(self.critic.flat)
+        # world_size > 1: the gradient buffers move into this rank's peer-mapped exchange block (csrc/comm.cuh)
+        self._exchange = None
+        self._dp_exchange = c["dp_exchange"] if self.is_distributed else "none"
+        if self._dp_exchange not in ("peer", "nccl", "none"):
+            raise L.OisError("dp_exchange must be 'peer' or 'nccl'")
+        if self._dp_exchange == "peer":
+            self._exchange = P.PeerExchange.create(self.critic.num_params, self.policy.num_params, self.device)
+            if self._exchange is None:      # CUDA IPC unavailable on some rank: every rank falls back together
+                self._dp_exchange = "nccl"
+            else:
+                self._grad_critic, self._grad_actor = self._exchange.critic_grad, self._exchange.actor_grad
         self._stats = torch.zeros(8, dtype=torch.float32, device=self.device)
         self._noise_stats = torch.zeros(3, dtype=torch.float32, device=self.device)
         self._handle = None
         self._handle_rows = 0
+        self._handle_generation = 0    # bumped when the C handle is re-created: captured graphs hold pointers into it
         self._act_calls = 0
         self._updates = 0
         self._graph = None            # (torch.cuda.CUDAGraph, idx buffer) of one update, see _update_graphed
@@ -377,7 +400,12 @@ class DDPG:
         if self._handle is not None and rows <= self._handle_rows:
             return
         if self._handle is not None:
+            # a captured update graph / rollout.RolloutGraph holds raw pointers into the handle's workspaces and weight
+            # images: drop ours, and let RolloutGraph see the new generation and re-capture
+            torch.cuda.synchronize(self.device)
+            self._graph = None
             L.lib().ois_agent_destroy(self._handle)
+        self._handle_generation += 1
         rows = max(int(rows), self._batch_size)
         h = C.c_void_p()
         prec = L.PRECISION_BF16 if self._mixed_precision else L.PRECISION_FP32
@@ -612,7 +640,15 @@ class DDPG:
         io.discount, io.polyak = self._discount_factor, self._polyak
         io.actor_grad, io.critic_grad = self._grad_actor.data_ptr(), self._grad_critic.data_ptr()
         io.stats = self._stats.data_ptr()
+        io.comm = self._exchange.handle.value if (self._exchange is not None and self._dp_exchange == "peer") else None
+        io.batch_rows = int(s.shape[0])
         return io
+
+    def _reduce(self, model, grad):
+        """The gradient reduction between two phases (ddpg.py:409-410,431-432).  "peer": nothing to do here — the next
+        phase's Adam kernel exchanges the gradients itself; "nccl": skrl's all-reduce."""
+        if self._dp_exchange == "nccl":
+            model.reduce_parameters(grad)
 
     def _track_update_stats(self):
         every = self.cfg["track_stats_interval"] or (1 if self.write_interval > 0 else 0)
@@ -632,8 +668,13 @@ class DDPG:
         outside the graph: its offset and the memory length change per call), the graph holds the gather and the
         three phases; the Adam step count lives on the device (OisUpdateIO.adam_step_dev)."""
         lib, m = L.lib(), self.memory
-        if m.sampler != "device" or self.is_distributed or m._supplied_indexes:
-            raise L.OisError("graph_update needs sampler='device', world_size 1 and no supplied indexes")
+        if m.sampler != "device" or m._supplied_indexes:
+            raise L.OisError("graph_update needs sampler='device' and no supplied indexes")
+        if len(m) < self._batch_size:
+            raise L.OisError("graph_update needs len(memory) >= batch_size (raise learning_starts)")
+        scale = 1.0 / self.world_size if self.is_distributed else 1.0
+        grads = (self._grad_critic, self._grad_actor, None)
+        nets = (self.critic, self.policy, None)
         if self._graph is None:
             idx = torch.empty(self._batch_size, dtype=torch.int64, device=self.device)
             self._step_dev = torch.tensor([self.critic_optimizer.step], dtype=torch.int64, device=self.device)
@@ -645,14 +686,19 @@ class DDPG:
             # sequence is then captured — capture records, it does not execute — for every later call
             self._step_dev.add_(1)
             for ph in range(3):
-                L.check(lib.ois_ddpg_update_phase(self._handle, self._scaler_ref(), C.byref(io), ph, 1.0, L.current_stream()))
+                L.check(lib.ois_ddpg_update_phase(self._handle, self._scaler_ref(), C.byref(io), ph, scale, L.current_stream()))
+                if ph < 2:
+                    self._reduce(nets[ph], grads[ph])
             torch.cuda.synchronize()
             graph = torch.cuda.CUDAGraph()
-            with torch.cuda.graph(graph):
+            # "thread_local": the NCCL watchdog thread may query events while this thread captures (dp_exchange "nccl")
+            with torch.cuda.graph(graph, capture_error_mode="thread_local"):
                 self._step_dev.add_(1)
                 m.sample_by_index(self._tensors_names, idx)
                 for ph in range(3):
-                    L.check(lib.ois_ddpg_update_phase(self._handle, self._scaler_ref(), C.byref(io), ph, 1.0, L.current_stream()))
+                    L.check(lib.ois_ddpg_update_phase(self._handle, self._scaler_ref(), C.byref(io), ph, scale, L.current_stream()))
+                    if ph < 2:
+                        self._reduce(nets[ph], grads[ph])
             self._graph = (graph, idx, io, batch)
         else:
             graph, idx = self._graph[0], self._graph[1]
@@ -679,7 +725,11 @@ class DDPG:
                 self._track_update_stats()
             return
         for _ in range(self._gradient_steps):
+            # the reference trains on whatever randperm(len)[:batch_size] returns, i.e. on a SHORTER batch while the
+            # memory holds fewer than batch_size transitions (io.batch_rows tells the kernels; fp32 path only)
             batch = self.memory.sample(names=self._tensors_names, batch_size=self._batch_size)[0]
+            if batch[0].shape[0] < 2:
+                continue     # a 1-row batch has no variance (torch.var -> NaN in the reference); nothing sane to train on
             io = self._update_io(batch)
             self.policy_optimizer.step += 1
             self.critic_optimizer.step += 1
@@ -687,11 +737,9 @@ class DDPG:
             scale = 1.0 / self.world_size if self.is_distributed else 1.0
             stream = L.current_stream()
             L.check(lib.ois_ddpg_update_phase(self._handle, self._scaler_ref(), C.byref(io), 0, scale, stream))
-            if self.is_distributed:   # critic.reduce_parameters(), ddpg.py:409-410
-                self.critic.reduce_parameters(self._grad_critic)
+            self._reduce(self.critic, self._grad_critic)    # critic.reduce_parameters(), ddpg.py:409-410
             L.check(lib.ois_ddpg_update_phase(self._handle, self._scaler_ref(), C.byref(io), 1, scale, stream))
-            if self.is_distributed:   # policy.reduce_parameters(), ddpg.py:431-432
-                self.policy.reduce_parameters(self._grad_actor)
+            self._reduce(self.policy, self._grad_actor)     # policy.reduce_parameters(), ddpg.py:431-432
             L.check(lib.ois_ddpg_update_phase(self._handle, self._scaler_ref(), C.byref(io), 2, scale, stream))
             self._updates += 1
             self.kernel_launches += UPDATE_LAUNCHES_BF16 if self._mixed_precision else UPDATE_LAUNCHES

@@ -7,6 +7,7 @@
 #include "mlp_fp32.cuh"
 #include "explore.cuh"
 #include "update_tc.cuh"
+#include "comm.cuh"
 
 namespace ois {
 
@@ -261,10 +262,10 @@ __device__ __forceinline__ void adam_bias_corrections(int64_t t, double lr, doub
 
 // one element of the single-tensor Adam step; returns the new parameter
 __device__ __forceinline__ float adam_element(float* __restrict__ p, float* __restrict__ m, float* __restrict__ v,
-                                              const float* __restrict__ g, int64_t i, float grad_scale, double beta1,
+                                              float g_sum, int64_t i, float grad_scale, double beta1,
                                               double beta2, float eps, float step_size, float bc2_sqrt) {
   const float w1 = (float)(1.0 - beta1), b2 = (float)beta2, w2 = (float)(1.0 - beta2);
-  const float gi = g[i] * grad_scale;
+  const float gi = g_sum * grad_scale;
   const float mi = m[i] + w1 * (gi - m[i]);            // exp_avg.lerp_(grad, 1 - beta1)
   const float vi = v[i] * b2 + w2 * gi * gi;           // exp_avg_sq.mul_(beta2).addcmul_(grad, grad, 1 - beta2)
   const float denom = sqrtf(vi) / bc2_sqrt + eps;
@@ -277,19 +278,27 @@ __device__ __forceinline__ float adam_element(float* __restrict__ p, float* __re
 
 // torch.optim.Adam (single-tensor formulas), flat buffers; g is scaled by grad_scale (1/world_size) first.
 // The step count may live on the device (CUDA-graph replay): bias corrections are then computed here.
+// comm.world > 1: this launch IS the gradient all-reduce of ddpg.py:409-410 — barrier with the peers, then every element
+// is the rank-ordered sum of all ranks' gradients read in place over NVLink (comm.cuh).
 __global__ void __launch_bounds__(256)
 adam_kernel(float* __restrict__ p, float* __restrict__ m, float* __restrict__ v, const float* __restrict__ g, int64_t n,
             float grad_scale, double lr, double beta1, double beta2, float eps, int64_t step_host,
-            const int64_t* __restrict__ step_dev, uint8_t* __restrict__ img, int in_dim, int out_dim) {
+            const int64_t* __restrict__ step_dev, uint8_t* __restrict__ img, int in_dim, int out_dim,
+            const __grid_constant__ CommArgs comm) {
   __shared__ float s_step_size, s_bc2_sqrt;
   pdl_wait();
   if (threadIdx.x == 0) pdl_trigger();
   if (threadIdx.x == 0) adam_bias_corrections(step_dev ? step_dev[0] : step_host, lr, beta1, beta2, s_step_size, s_bc2_sqrt);
-  __syncthreads();
+  const bool dp = comm.world > 1;
+  if (dp) comm_barrier(comm);
+  else __syncthreads();
   const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= n) return;
-  const float pn = adam_element(p, m, v, g, i, grad_scale, beta1, beta2, eps, s_step_size, s_bc2_sqrt);
-  if (img) tcu_img_store(img, i, pn, in_dim, out_dim);  // keep the bf16 tensor-core image current (update_tc.cu)
+  if (i < n) {
+    const float gs = dp ? comm_reduced(comm, i) : g[i];
+    const float pn = adam_element(p, m, v, gs, i, grad_scale, beta1, beta2, eps, s_step_size, s_bc2_sqrt);
+    if (img) tcu_img_store(img, i, pn, in_dim, out_dim);  // keep the bf16 tensor-core image current (update_tc.cu)
+  }
+  if (dp) comm_finish(comm);
 }
 
 // both target networks in one launch, each optionally with its bf16 tensor-core image kept current
@@ -313,6 +322,7 @@ struct AdamPolyak {
   double lr, beta1, beta2;
   int64_t step_host;
   const int64_t* step_dev;
+  CommArgs comm;            // world > 1: the actor-gradient all-reduce of ddpg.py:431-432 happens here (comm.cuh)
 };
 __global__ void __launch_bounds__(256)
 adam_polyak_kernel(const __grid_constant__ AdamPolyak a, float tau) {
@@ -321,22 +331,25 @@ adam_polyak_kernel(const __grid_constant__ AdamPolyak a, float tau) {
   if (threadIdx.x == 0) pdl_trigger();
   if (threadIdx.x == 0)
     adam_bias_corrections(a.step_dev ? a.step_dev[0] : a.step_host, a.lr, a.beta1, a.beta2, s_step_size, s_bc2_sqrt);
-  __syncthreads();
+  const bool dp = a.comm.world > 1;
+  if (dp) comm_barrier(a.comm);
+  else __syncthreads();
   int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i < a.pp.n[0]) {
     float* p = const_cast<float*>(a.pp.p[0]);
-    const float pn = adam_element(p, a.m, a.v, a.g, i, a.grad_scale, a.beta1, a.beta2, a.eps, s_step_size, s_bc2_sqrt);
+    const float gs = dp ? comm_reduced(a.comm, i) : a.g[i];
+    const float pn = adam_element(p, a.m, a.v, gs, i, a.grad_scale, a.beta1, a.beta2, a.eps, s_step_size, s_bc2_sqrt);
     if (a.actor_img) tcu_img_store(a.actor_img, i, pn, a.pp.in_dim[0], a.pp.out_dim[0]);
     const float t = __fadd_rn(__fmul_rn(a.pp.pt[0][i], 1.0f - tau), __fmul_rn(tau, pn));
     a.pp.pt[0][i] = t;
     if (a.pp.img[0]) tcu_img_store(a.pp.img[0], i, t, a.pp.in_dim[0], a.pp.out_dim[0]);
-    return;
+  } else if (i - a.pp.n[0] < a.pp.n[1]) {
+    i -= a.pp.n[0];
+    const float t = __fadd_rn(__fmul_rn(a.pp.pt[1][i], 1.0f - tau), __fmul_rn(tau, a.pp.p[1][i]));
+    a.pp.pt[1][i] = t;
+    if (a.pp.img[1]) tcu_img_store(a.pp.img[1], i, t, a.pp.in_dim[1], a.pp.out_dim[1]);
   }
-  i -= a.pp.n[0];
-  if (i >= a.pp.n[1]) return;
-  const float t = __fadd_rn(__fmul_rn(a.pp.pt[1][i], 1.0f - tau), __fmul_rn(tau, a.pp.p[1][i]));
-  a.pp.pt[1][i] = t;
-  if (a.pp.img[1]) tcu_img_store(a.pp.img[1], i, t, a.pp.in_dim[1], a.pp.out_dim[1]);
+  if (dp) comm_finish(a.comm);
 }
 
 // the tensor-core update's batch preparation in ONE CTA of 512 threads: ddpg.py:381-382 (scaler, train=True, on states
@@ -529,9 +542,22 @@ static int mlp_backward_fp32(const OisMlpShape& sh, const float* P, float* G, co
 
 static int adam_step(float* p, float* m, float* v, const float* g, int64_t n, float grad_scale, double lr, double b1,
                      double b2, double eps, int64_t step, const int64_t* step_dev, uint8_t* img, const OisMlpShape& sh,
-                     cudaStream_t s) {
+                     const CommArgs& comm, cudaStream_t s) {
   OIS_CHECK_CUDA(launch_pdl(adam_kernel, eg(n, 256), 256, 0, s, p, m, v, g, n, grad_scale, lr, b1, b2, (float)eps, step,
-                            step_dev, img, (int)sh.in_dim, (int)sh.out_dim));
+                            step_dev, img, (int)sh.in_dim, (int)sh.out_dim, comm));
+  return OIS_OK;
+}
+
+// the exchange table of gradient `kind` when the caller set OisUpdateIO.comm for a world of more than one rank
+static int comm_for(const OisUpdateIO* io, int kind, const float* grad, int64_t n, CommArgs& out) {
+  out = CommArgs{};
+  const OisComm* c = io->comm;
+  if (!c || c->world <= 1) return OIS_OK;
+  OIS_CHECK_ARG(c->connected, "OisUpdateIO.comm is not connected to its peers (ois_comm_connect)");
+  OIS_CHECK_ARG(c->n[kind] == n, "OisUpdateIO.comm was created for other parameter counts");
+  OIS_CHECK_ARG((const char*)grad == (const char*)c->block + c->off_grad[kind],
+                "with OisUpdateIO.comm set the gradient buffers must be ois_comm_grad(comm, 0 / 1)");
+  out = comm_args(c, kind);
   return OIS_OK;
 }
 
@@ -687,14 +713,18 @@ extern "C" int ois_ddpg_update_phase(OisAgent* a, const OisScaler* scaler, const
   OIS_CHECK_ARG(io->actor_grad && io->critic_grad && io->actor_m && io->actor_v && io->critic_m && io->critic_v,
                 "null optimizer buffer");
   cudaStream_t s = (cudaStream_t)stream;
-  const int B = a->batch, D = a->actor.in_dim, A = a->actor.out_dim, CI = a->critic.in_dim;
+  OIS_CHECK_ARG(io->batch_rows >= 0 && io->batch_rows <= a->batch, "batch_rows exceeds the handle's batch_size");
+  const int B = io->batch_rows > 0 ? io->batch_rows : a->batch;
+  const int D = a->actor.in_dim, A = a->actor.out_dim, CI = a->critic.in_dim;
   const MlpOffsets oa = mlp_offsets(a->actor), oc = mlp_offsets(a->critic);
   const bool has_scaler = scaler && scaler->running_mean;
+  OIS_CHECK_ARG(!has_scaler || B >= 2, "the scaler's batch statistics need at least 2 rows");
   // OIS_PRECISION_BF16: every contraction below runs as a tcgen05 grouped GEMM (update_tc.cu) and the element-wise
   // pieces (fp64 scaler statistics, TD target, losses, Adam, polyak — the same arithmetic as the exact fp32 path) are
   // fused around them; every launch is a programmatic dependent launch, so prologues overlap the predecessor's tail
   const bool tc = a->precision == OIS_PRECISION_BF16;
   OIS_CHECK_ARG(!tc || a->tcu, "the bf16 tcgen05 update needs batch_size to be a multiple of 128 (use OIS_PRECISION_FP32 otherwise)");
+  OIS_CHECK_ARG(!tc || B == a->batch, "the bf16 tcgen05 update runs full batches only (batch_rows must equal batch_size)");
   if (phase == 0) {
     OIS_CHECK_ARG(io->states && io->actions && io->rewards && io->next_states && io->terminated && io->truncated,
                   "null batch tensor");
@@ -762,8 +792,10 @@ extern "C" int ois_ddpg_update_phase(OisAgent* a, const OisScaler* scaler, const
     // ddpg.py:416  critic optimizer step (bf16 path: the critic's tensor-core image is kept current by the same kernel)
     uint8_t* cimg = tc ? tcu_image_if_valid(a, TCU_CRITIC, io->critic) : nullptr;
     if (tc && !cimg) tcu_invalidate(a, TCU_CRITIC);
+    CommArgs comm;
+    if (int e = comm_for(io, 0, io->critic_grad, oc.total, comm)) return e;
     if (int e = adam_step(io->critic, io->critic_m, io->critic_v, io->critic_grad, oc.total, grad_scale, io->critic_lr,
-                          io->beta1, io->beta2, io->adam_eps, io->adam_step, io->adam_step_dev, cimg, a->critic, s)) return e;
+                          io->beta1, io->beta2, io->adam_eps, io->adam_step, io->adam_step_dev, cimg, a->critic, comm, s)) return e;
     if (tc) {
       // ddpg.py:420-423 policy loss through the updated critic; the actor's forward already ran in phase 0 (its actions
       // are in x_policy's columns D.. and in u_a), so only the critic's forward on (states, actor actions) is left.
@@ -799,9 +831,11 @@ extern "C" int ois_ddpg_update_phase(OisAgent* a, const OisScaler* scaler, const
   }
   // phase 2: ddpg.py:438 actor optimizer step, :443-444 polyak
   uint8_t* aimg = tc ? tcu_image_if_valid(a, TCU_ACTOR, io->actor) : nullptr;
+  CommArgs comm;
+  if (int e = comm_for(io, 1, io->actor_grad, oa.total, comm)) return e;
   if (!tc)
     if (int e = adam_step(io->actor, io->actor_m, io->actor_v, io->actor_grad, oa.total, grad_scale, io->actor_lr, io->beta1,
-                          io->beta2, io->adam_eps, io->adam_step, io->adam_step_dev, aimg, a->actor, s)) return e;
+                          io->beta2, io->adam_eps, io->adam_step, io->adam_step_dev, aimg, a->actor, comm, s)) return e;
   if (tc) {
     AdamPolyak ap;
     PolyakPair& pp = ap.pp;
@@ -815,6 +849,7 @@ extern "C" int ois_ddpg_update_phase(OisAgent* a, const OisScaler* scaler, const
     ap.grad_scale = grad_scale; ap.eps = (float)io->adam_eps;
     ap.lr = io->actor_lr; ap.beta1 = io->beta1; ap.beta2 = io->beta2;
     ap.step_host = io->adam_step; ap.step_dev = io->adam_step_dev;
+    ap.comm = comm;
     OIS_CHECK_CUDA(launch_pdl(adam_polyak_kernel, eg(oa.total + oc.total, 256), 256, 0, s, ap, io->polyak));
     tc_invalidate_weights(a);                       // the inference kernel's own stream image is rebuilt by the next act
     if (!aimg) tcu_invalidate(a, TCU_ACTOR);

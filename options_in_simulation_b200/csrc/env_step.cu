@@ -565,10 +565,17 @@ env_step_kernel(const __grid_constant__ OisEnvParams p, const __grid_constant__ 
     __syncthreads();
     if (threadIdx.x == 0) {
       OisStepCtl* c = const_cast<OisStepCtl*>(io.ctl);
-      __threadfence();
+      // (the barrier above orders this CTA's stores before the fence; with a host waiting on done_flag they may be stores
+      //  to pinned host memory, so the fence is a system-scope one)
+      if (io.done_flag) __threadfence_system();
+      else __threadfence();
       if (atomicAdd(&c->ticket, 1u) == gridDim.x - 1) {
         c->ticket = 0;
         step_ctl_advance(c);
+        if (io.done_flag) {     // every CTA's results are out: tell the host which step is complete
+          __threadfence_system();
+          *reinterpret_cast<volatile uint32_t*>(io.done_flag) = (uint32_t)c->step;
+        }
       }
     }
   }
@@ -659,6 +666,7 @@ extern "C" int ois_env_step(const OisEnvParams* params, const OisEnvState* state
                           io->replay_terminated && io->replay_truncated;
   OIS_CHECK_ARG(!any_replay || all_replay, "replay pointers must be all set or all null");
   OIS_CHECK_ARG(io->flag_slot >= 0 && io->flag_slot < 3, "flag_slot must be 0..2");
+  OIS_CHECK_ARG(!io->done_flag || io->ctl, "done_flag needs a step-control block (ctl) with self_advance");
   if (n_envs == 0) return OIS_OK;
   const int grid = grid_for(n_envs, kEnvThreads);
   cudaStream_t s = (cudaStream_t)stream;

@@ -299,12 +299,13 @@ class TorqueDistributionTask:
         """RLTask.reset (rl_task.py:251-253): flag every env for reset."""
         self.reset_buf.fill_(True)   # in place: the buffer is a view of _out_pack (the reference allocates a new one)
 
-    def pre_physics_step(self, actions, record: bool = True, _ctl=None, _host_out=None):
+    def pre_physics_step(self, actions, record: bool = True, _ctl=None, _host_out=None, _done_flag=None):
         """KAMMA_medium.py:596-656 — and, fused behind it, everything post_physics_step computes.
         ``record=False`` suppresses the fused replay append for this step (the wrapper's reset step).
         ``_ctl`` (rollout.RolloutGraph): device OisStepCtl the kernel takes its per-step scalars and replay row from.
         ``_host_out``: device-visible addresses (obs_clipped, rew, reset) of pinned HOST memory the kernel stores this
-        step's results to directly, in place of the task's own device buffers."""
+        step's results to directly, in place of the task's own device buffers.  ``_done_flag``: device-visible address of a
+        pinned host word that receives the completed-step count (OisEnvIO.done_flag)."""
         if self._env is not None and hasattr(self._env, "world") and not self._env.world.is_playing():
             return
         if not (actions.is_cuda and actions.dtype == torch.float32 and actions.is_contiguous()
@@ -335,6 +336,7 @@ class TorqueDistributionTask:
         io.rew, io.reset = self._io_static[0], self._io_static[1]
         io.ep_stats = io.comp0 = None
         io.ctl = _ctl
+        io.done_flag = _done_flag
         want_stats = _ctl is None and self.stats_interval > 0 and (self._launches % self.stats_interval == 0)
         if self.stats_log is not None and _ctl is None and self._stats_row < self.stats_log.shape[0]:
             want_stats = False
@@ -384,8 +386,8 @@ class TorqueDistributionTask:
         self.progress_buf += 1
         return self.obs_buf, self.rew_buf, self.reset_buf, self.extras
 
-    def step(self, actions, record: bool = True, _ctl=None, _host_out=None):
-        self.pre_physics_step(actions, record, _ctl, _host_out)
+    def step(self, actions, record: bool = True, _ctl=None, _host_out=None, _done_flag=None):
+        self.pre_physics_step(actions, record, _ctl, _host_out, _done_flag)
         return self.obs_buf, self.rew_buf, self.reset_buf, self.extras
 
     def get_observations(self):   # :825-869

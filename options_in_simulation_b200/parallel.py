@@ -6,8 +6,13 @@ skrl's DP semantics, as the reference uses them through ``Model.broadcast_parame
 broadcast from rank 0 once; each update all-reduces (SUM) ONE flat gradient buffer per network and divides by
 the world size (here the division is folded into the Adam kernel as ``grad_scale``).
 
-Nothing here touches CUDA directly, so the functions run unchanged on the ``gloo`` backend with CPU tensors
+The plain functions touch no CUDA API, so they run unchanged on the ``gloo`` backend with CPU tensors
 (tests/test_distributed_cpu.py, world_size 2) and on ``nccl`` over NVLink 5 / NVSwitch on the GPU box.
+
+``PeerExchange`` is the B200 data path of the same two reductions: every rank's flat gradient buffers live in an
+exchange block that all peers map over NVLink (CUDA IPC), and the Adam kernels read all ranks' gradients in place
+(csrc/comm.cuh) — no NCCL call, no host involvement per update, capturable in the update's CUDA graph.  The only thing
+it asks of ``torch.distributed`` is to carry the 64-byte IPC handles between the ranks once, at construction.
 """
 from __future__ import annotations
 
@@ -64,6 +69,112 @@ def all_reduce_gradients(flat_grad: torch.Tensor) -> float:
         dist.all_reduce(flat_grad, op=dist.ReduceOp.SUM)
         return 1.0 / dist.get_world_size()
     return 1.0
+
+
+class _DeviceMemory:
+    """A raw device allocation owned by the C library, exposed to torch through ``__cuda_array_interface__``."""
+
+    def __init__(self, ptr: int, count: int):
+        self.__cuda_array_interface__ = {"shape": (int(count),), "typestr": "<f4", "data": (int(ptr), False), "version": 3}
+
+
+def gather_handles(handle: bytes, world: int, group=None) -> bytes:
+    """All ranks' IPC handles concatenated in rank order (the one host-side exchange, at construction)."""
+    out = [None] * world
+    dist.all_gather_object(out, bytes(handle), group=group)
+    return b"".join(out)
+
+
+class PeerExchange:
+    """This rank's exchange block + the mappings of all peers' blocks (include/ois_b200.h: ``ois_comm_*``).
+
+    ``critic_grad`` / ``actor_grad`` are torch views of the block's two gradient buffers: the update's backward kernels
+    write them, the peers read them.  ``handle`` goes into ``OisUpdateIO.comm``."""
+
+    def __init__(self, critic_params: int, actor_params: int, device, rank: int | None = None, world: int | None = None,
+                 handles: bytes | None = None):
+        import ctypes as C
+
+        from . import _lib as L
+
+        info = distributed_info()
+        self.rank = info.rank if rank is None else int(rank)
+        self.world = info.world_size if world is None else int(world)
+        self.device = torch.device(device)
+        self._L, self._C = L, C
+        h = C.c_void_p()
+        with torch.cuda.device(self.device):
+            L.check(L.lib().ois_comm_create(C.byref(h), self.rank, self.world, int(critic_params), int(actor_params)))
+            self.handle = h
+            buf = C.create_string_buffer(L.OIS_IPC_HANDLE_BYTES)
+            if self.world > 1 and handles != b"":       # b"": the caller connects later (create())
+                if handles is None:
+                    L.check(L.lib().ois_comm_export(h, buf))
+                    handles = gather_handles(buf.raw, self.world)
+                L.check(L.lib().ois_comm_connect(h, handles, self.world))
+        lib = L.lib()
+        self.critic_grad = torch.as_tensor(_DeviceMemory(lib.ois_comm_grad(h, 0), critic_params), device=self.device)
+        self.actor_grad = torch.as_tensor(_DeviceMemory(lib.ois_comm_grad(h, 1), actor_params), device=self.device)
+
+    @classmethod
+    def create(cls, critic_params: int, actor_params: int, device):
+        """Collective constructor for the torchrun case: every rank either gets a connected exchange or — if CUDA IPC
+        is unavailable on ANY rank (container without a shared IPC namespace, no P2P path) — all of them get ``None``
+        and fall back to NCCL together.  Two agreement points, so that no rank is left waiting in a collective."""
+        import ctypes as C
+
+        from . import _lib as L
+
+        info = distributed_info()
+        dev = torch.device(device)
+
+        def all_ok(ok: bool) -> bool:
+            t = torch.tensor([1 if ok else 0], dtype=torch.int32, device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MIN)
+            return bool(t.item())
+
+        self, handle, err = None, b"\0" * L.OIS_IPC_HANDLE_BYTES, None
+        try:
+            self = cls(critic_params, actor_params, dev, info.rank, info.world_size, handles=b"")
+            buf = C.create_string_buffer(L.OIS_IPC_HANDLE_BYTES)
+            with torch.cuda.device(dev):
+                L.check(L.lib().ois_comm_export(self.handle, buf))
+            handle = buf.raw
+        except L.OisError as e:
+            err = e
+        ok = all_ok(err is None)
+        handles = gather_handles(handle, info.world_size)
+        if ok:
+            try:
+                with torch.cuda.device(dev):
+                    L.check(L.lib().ois_comm_connect(self.handle, handles, info.world_size))
+            except L.OisError as e:
+                err = e
+            ok = all_ok(err is None)
+        if not ok:
+            if info.rank == 0:
+                print(f"[ois] peer-memory gradient exchange unavailable ({err or 'on another rank'}); using NCCL", flush=True)
+            if self is not None and self.handle is not None:
+                L.lib().ois_comm_destroy(self.handle)
+                self.handle = None
+            return None
+        return self
+
+    def status(self) -> tuple[int, int, int]:
+        """(critic exchanges completed, actor exchanges completed, 0 or p + 1 if a barrier gave up waiting for rank p)."""
+        w = (self._C.c_uint32 * 3)()
+        with torch.cuda.device(self.device):
+            self._L.check(self._L.lib().ois_comm_status(self.handle, w))
+        return int(w[0]), int(w[1]), int(w[2])
+
+    def close(self) -> None:
+        if self.handle is not None:
+            torch.cuda.synchronize(self.device)
+            if dist.is_initialized() and self.world > 1:
+                dist.barrier()              # no peer may still be reading this block
+            self.critic_grad = self.actor_grad = None
+            self._L.lib().ois_comm_destroy(self.handle)
+            self.handle = None
 
 
 def reduce_sums(*tensors: torch.Tensor) -> None:

@@ -40,12 +40,20 @@ def _device_synchronize():
 class RolloutGraph:
     """``host_io=False``: device-resident loop — ``step()`` returns the (fixed) device tensors
     ``(next_states, rewards[N,1], terminated[N,1])`` without synchronising.
-    ``host_io=True``: the observations of each step arrive in the pinned host tensor ``h_states`` (the caller fills it
-    before ``step()``), and the step's results are returned in pinned host tensors after a synchronise — the
-    host-in-the-loop shape ``bench.py`` times as ``e2e``.  The two kernels access the pinned buffers in place (zero-copy:
-    the actor kernel loads its rows of ``h_states`` over PCIe, the env kernel stores obs | rew | reset straight to host
-    memory), so the graph is two kernel nodes; every byte still crosses the bus every step, but without the copy-engine
-    round trips.  ``host_io="copy"`` keeps explicit copy nodes instead (H2D of the observations, ONE packed D2H)."""
+    ``host_io=True``: the observations of each step are read from the pinned host tensor ``h_states`` and the step's
+    results are returned in pinned host tensors once the step is complete — the host-in-the-loop shape ``bench.py``
+    times as ``e2e``.  The two kernels access the pinned buffers in place (zero-copy: the actor kernel loads its rows of
+    ``h_states`` over PCIe, the env kernel stores obs | rew | reset straight to host memory), so the graph is two kernel
+    nodes; every byte still crosses the bus every step, but without the copy-engine round trips.  There are two pinned
+    result packs and two captured graphs that alternate: step t reads its observations from the pack step t-1 wrote
+    (``states = next_states``, base_KA_DDPG.py:268-275, without a host copy — the caller may still overwrite
+    ``h_states`` before ``step()``) and writes the other one, so the results of step t stay readable while step t+1
+    runs.  Completion is signalled by the env kernel itself (``OisEnvIO.done_flag``: a pinned word the last CTA
+    stores the step count to) and ``step()`` is ONE C call, ``ois_graph_launch_wait``: no cudaDeviceSynchronize.
+    ``step(wait=False)`` only launches; ``wait()`` then blocks until that step's results are in host memory (one step
+    may be in flight while the host consumes the previous one).
+    ``host_io="copy"`` keeps explicit copy nodes instead (H2D of the observations, ONE packed D2H) and a device
+    synchronise per step."""
 
     def __init__(self, env, agent, timestep: int, timesteps: int, host_io: bool = False):
         task = env.task
@@ -68,24 +76,39 @@ class RolloutGraph:
         # the state the captured actor launch reads: the env's own clamped-observation buffer (device loop) or the
         # landing buffer of the host->device copy (host loop)
         self.states = task._obs_clipped[0]
+        self._zero_copy = host_io is True
+        self._steps_done = 0             # steps issued through the step-control block (the value done_flag receives)
         if host_io:
-            self.h_states = torch.empty(n, 6, dtype=torch.float32).pin_memory()
-            self._d_states = torch.empty(n, 6, dtype=torch.float32, device=dev)
             # obs [N,6] f32 | rew [N] f32 | terminated [N] u8: the task keeps them in ONE allocation (envs.py: _out_pack)
-            self._h_pack = torch.empty(n * 29, dtype=torch.uint8).pin_memory()
-            self.h_next_states = self._h_pack[: n * 24].view(torch.float32).view(n, 6)
-            self.h_rewards = self._h_pack[n * 24: n * 28].view(torch.float32).view(n, 1)
-            self.h_terminated = self._h_pack[n * 28:].view(torch.bool).view(n, 1)
-        self._graph = None
+            packs = 2 if self._zero_copy else 1
+            self._h_packs = [torch.zeros(n * 29, dtype=torch.uint8).pin_memory() for _ in range(packs)]
+            view = lambda p: (p[: n * 24].view(torch.float32).view(n, 6), p[n * 24: n * 28].view(torch.float32).view(n, 1),
+                              p[n * 28:].view(torch.bool).view(n, 1))
+            self._h_views = [view(p) for p in self._h_packs]
+            self._cur = 0                # zero-copy: the pack whose observations the NEXT step reads
+            if self._zero_copy:
+                self._h_done = torch.zeros(16, dtype=torch.int32).pin_memory()     # [0]: steps completed (done_flag)
+            else:
+                self._h_in = torch.empty(n, 6, dtype=torch.float32).pin_memory()
+                self._d_states = torch.empty(n, 6, dtype=torch.float32, device=dev)
+            self.h_next_states, self.h_rewards, self.h_terminated = self._h_views[0]
+        self._graphs = {}                # captured step per input pack (zero-copy: 0 and 1; otherwise only 0)
+        self._graph_generation = -1      # agent._handle_generation the captured launches point into
         self._warm = False
         self._per_step = (1, 1)
+        self._wait_timeout_ns = 30_000_000_000
+
+    @property
+    def h_states(self):
+        """Pinned host buffer the next ``step()`` reads its observations from (fill or overwrite it before the call)."""
+        return self._h_views[self._cur][0] if self._zero_copy else self._h_in
 
     # ------------------------------------------------------------------ the per-step scalars
     def _write_ctl(self):
         """Host -> device copy of the block for the NEXT step, from the host mirrors (so eager steps may have run)."""
         a, t, m = self.agent, self.task, self.memory
         c = L.StepCtl()
-        c.step, c.self_advance, c.ticket = 0, 1, 0
+        c.step, c.self_advance, c.ticket = self._steps_done, 1, 0
         c.env_philox_offset, c.act_philox_offset = t._launches, a._act_calls
         c.replay_row, c.replay_rows = m.memory_index, m.memory_size
         c.flag_slot = t._launches % 3
@@ -104,20 +127,22 @@ class RolloutGraph:
         t, a, m = self.task, self.agent, self.memory
         return self._mirror != (t._launches, a._act_calls, m.memory_index, self.timestep)
 
-    def _issue(self):
-        """The launches of one step, on the current stream (eagerly once to warm up, then under capture)."""
+    def _issue(self, src: int = 0):
+        """The launches of one step, on the current stream (eagerly once to warm up, then under capture).  ``src``: the
+        pinned pack the observations are read from (zero-copy mode; the results go to the other one)."""
         ctl = self._ctl.data_ptr()
         n = self.task.num_envs
         if self.host_io == "copy":
-            self._d_states.copy_(self.h_states, non_blocking=True)
+            self._d_states.copy_(self._h_in, non_blocking=True)
             self.agent.act(self._d_states, self.timestep, self.timesteps, _ctl=ctl, _out=self._actions)
             self.task.step(self._actions, True, _ctl=ctl)
-            self._h_pack.copy_(self.task._out_pack, non_blocking=True)
+            self._h_packs[0].copy_(self.task._out_pack, non_blocking=True)
         elif self.host_io:
-            hp = self._h_pack.data_ptr()                 # pinned memory: the same address is valid on the device (UVA)
-            self.agent.act(self.h_states, self.timestep, self.timesteps, _ctl=ctl, _out=self._actions,
-                           _states_ptr=self.h_states.data_ptr())
-            self.task.step(self._actions, True, _ctl=ctl, _host_out=(hp, hp + n * 24, hp + n * 28))
+            h_in = self._h_views[src][0]                 # pinned memory: the same address is valid on the device (UVA)
+            hp = self._h_packs[1 - src].data_ptr()
+            self.agent.act(h_in, self.timestep, self.timesteps, _ctl=ctl, _out=self._actions, _states_ptr=h_in.data_ptr())
+            self.task.step(self._actions, True, _ctl=ctl, _host_out=(hp, hp + n * 24, hp + n * 28),
+                           _done_flag=self._h_done.data_ptr())
         else:
             self.agent.act(self.states, self.timestep, self.timesteps, _ctl=ctl, _out=self._actions)
             self.task.step(self._actions, True, _ctl=ctl)
@@ -130,16 +155,23 @@ class RolloutGraph:
         t, a, m = self.task, self.agent, self.memory
         t._launches, t.kernel_launches, a._act_calls, a.kernel_launches, m.memory_index, m.filled = s
 
-    def _capture(self):
+    def _capture(self, src: int = 0):
         saved = self._host_state()            # capture runs the Python bookkeeping of one step without executing it
         graph = torch.cuda.CUDAGraph()
         # "relaxed": Python's collector may run a finaliser while the step is being captured (an old agent handle or
         # graph going away -> cudaFree), which the stricter modes treat as an error; nothing captured here depends on
         # memory that such a call could touch (every buffer is held by this object, the task, the agent or the memory)
         with torch.cuda.graph(graph, capture_error_mode="relaxed"):
-            self._issue()
+            self._issue(src)
         self._set_host_state(saved)
-        self._graph = graph
+        raw = None
+        if self._zero_copy:
+            try:                      # the instantiated cudaGraphExec_t, for the one-call launch + wait in C
+                raw = int(graph.raw_cuda_graph_exec())
+            except Exception:         # a torch without the accessor: torch launches, ois_host_wait still waits
+                raw = None
+        self._graphs[src] = (graph, raw)
+        self._graph_generation = self.agent._handle_generation
 
     def _advance_host(self):
         """What one eager act + step would have done to the host mirrors."""
@@ -155,29 +187,55 @@ class RolloutGraph:
         self._mirror = (t._launches, a._act_calls, m.memory_index, self.timestep)
 
     # ------------------------------------------------------------------ public
-    def step(self):
+    def wait(self, lag: int = 0):
+        """Zero-copy mode: block (spinning on the pinned completion word, no driver call) until all but the last ``lag``
+        launched steps are complete; with lag 0 returns the last step's pinned result tensors."""
+        L.check(L.lib().ois_host_wait(self._h_done.data_ptr(), (self._steps_done - lag) & 0xFFFFFFFF, self._wait_timeout_ns))
+        return self.h_next_states, self.h_rewards, self.h_terminated
+
+    def step(self, wait: bool = True):
         """One policy step.  The first call issues the launches eagerly (lazy initialisation inside the library must
-        not happen under capture), the second captures, every later call is one graph launch."""
+        not happen under capture), the next ones capture, every later call is one graph launch."""
         a, t = self.agent, self.task
         if not self.host_io and t.obs_clipped.data_ptr() != self.states.data_ptr():
             self.states.copy_(t.obs_clipped)          # an eager step left the current observation in the other buffer
         if not self._warm or self._mirrors_moved():
             self._write_ctl()                          # (re)seed the device block from the host mirrors
+        src = self._cur if self._zero_copy else 0
+        launched_and_waited = False
         if not self._warm:
             before = self._host_state()
-            self._issue()
+            self._issue(src)
             after = self._host_state()
             self._per_step = (after[1] - before[1], after[3] - before[3])
             self._set_host_state(before)
             self._warm = True
         else:
             # the bf16 image of the actor weights follows DDPG._update; a no-op when nothing changed
-            L.check(L.lib().ois_agent_sync_weights(a._handle, L.ptr(a.policy.flat), L.current_stream(self._dev_index)))
-            if self._graph is None:
-                self._capture()
-            self._graph.replay()
+            stream = L.current_stream(self._dev_index)
+            L.check(L.lib().ois_agent_sync_weights(a._handle, L.ptr(a.policy.flat), stream))
+            if self._graph_generation != a._handle_generation:
+                self._graphs = {}      # the agent re-created its C handle: the old graphs' pointers are dead
+            if src not in self._graphs:
+                self._capture(src)
+            graph, raw = self._graphs[src]
+            if raw is None:
+                graph.replay()
+            elif wait:                 # launch + spin on the completion word: ONE C call, no device synchronise
+                L.check(L.lib().ois_graph_launch_wait(raw, stream, self._h_done.data_ptr(), (self._steps_done + 1) & 0xFFFFFFFF,
+                                                      self._wait_timeout_ns))
+                launched_and_waited = True
+            else:
+                L.check(L.lib().ois_graph_launch(raw, stream))
         self._advance_host()
+        self._steps_done += 1
+        if self._zero_copy:
+            self._cur = 1 - src
+            self.h_next_states, self.h_rewards, self.h_terminated = self._h_views[self._cur]
+            if wait and not launched_and_waited:
+                self.wait()
+            return self.h_next_states, self.h_rewards, self.h_terminated
         if self.host_io:
-            _device_synchronize()     # the host consumes this step's results: one sync per step is the point of host_io
+            _device_synchronize()     # copy-node mode: one device synchronise per step
             return self.h_next_states, self.h_rewards, self.h_terminated
         return t.obs_clipped, t.rew_buf.view(-1, 1), t.reset_buf.view(-1, 1)

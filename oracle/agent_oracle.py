@@ -108,12 +108,15 @@ class AgentOracle:
         critic_loss = Fn.mse_loss(q, y)
         self.critic_optimizer.zero_grad()
         critic_loss.backward()
+        # what critic.reduce_parameters() would all-reduce (ddpg.py:409-410): kept for the gradient-parity tests
+        self.last_critic_grad = torch.cat([p.grad.detach().reshape(-1).clone() for p in self.critic.parameters()])
         self.critic_optimizer.step()
         pa = self.policy(s)
         qp = self.critic(torch.cat([s, pa], dim=1))
         policy_loss = -qp.mean()
         self.policy_optimizer.zero_grad()
         policy_loss.backward()
+        self.last_actor_grad = torch.cat([p.grad.detach().reshape(-1).clone() for p in self.policy.parameters()])   # ddpg.py:431-432
         self.policy_optimizer.step()
         with torch.no_grad():   # Model.update_parameters(polyak)
             for net, tgt in ((self.policy, self.target_policy), (self.critic, self.target_critic)):
@@ -123,6 +126,17 @@ class AgentOracle:
         return dict(critic_loss=critic_loss.item(), policy_loss=policy_loss.item(), q_max=qp.max().item(),
                     q_min=qp.min().item(), q_mean=qp.mean().item(), y_max=y.max().item(), y_min=y.min().item(),
                     y_mean=y.mean().item())
+
+
+def adam_moments(opt: torch.optim.Adam, net: nn.Module):
+    """(exp_avg, exp_avg_sq, step) of a torch Adam flattened in parameter order (zeros before the first step)."""
+    m, v, step = [], [], 0
+    for p in net.parameters():
+        st = opt.state.get(p, {})
+        m.append(st["exp_avg"].reshape(-1) if "exp_avg" in st else torch.zeros(p.numel()))
+        v.append(st["exp_avg_sq"].reshape(-1) if "exp_avg_sq" in st else torch.zeros(p.numel()))
+        step = int(st["step"]) if "step" in st else step
+    return torch.cat(m), torch.cat(v), step
 
 
 def synth_transitions(rows: int, obs_dim: int, act_dim: int, gen: torch.Generator):

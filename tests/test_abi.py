@@ -24,7 +24,7 @@ def test_binding_table_matches_header(built_lib):
     from options_in_simulation_b200 import _lib as L
 
     assert sorted(L.SYMBOLS) == declared_symbols()
-    assert built_lib.ois_abi_version() == 2
+    assert built_lib.ois_abi_version() == 3
     assert b"sm_100a" in built_lib.ois_build_info()
 
 

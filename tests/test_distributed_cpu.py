@@ -52,6 +52,8 @@ def _worker(rank, world, port, out):
     res["bins"] = (bins.te_sum.clone(), bins.count.clone(), bins.means().clone())
     # 6. timing: max over ranks
     res["tmax"] = P.max_over_ranks(1.0 + rank, "cpu")
+    # 7. the one host-side exchange of the peer-memory gradient path: 64-byte IPC handles, concatenated in rank order
+    res["handles"] = P.gather_handles(bytes([rank + 1]) * 64, world)
     out[rank] = res
     dist.barrier()
     dist.destroy_process_group()
@@ -77,6 +79,7 @@ def test_world_size_2_gloo():
         assert te[0].item() == pytest.approx(0.6) and mean[0].item() == pytest.approx(0.3)
         assert mean[5].item() == pytest.approx(0.6) and mean[9].item() == pytest.approx(0.4)
         assert r["tmax"] == 2.0
+        assert r["handles"] == b"\x01" * 64 + b"\x02" * 64
 
 
 def test_single_process_is_identity():

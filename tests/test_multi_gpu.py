@@ -31,12 +31,18 @@ def test_ddpg_update_is_data_parallel_on_nccl():
 
 @pytest.mark.skipif(_gpus() < 2, reason="needs 2 GPUs")
 def test_bench_two_ranks_prints_one_aggregate_line():
-    r = _torchrun(2, "bench.py", "--gpus", "2", "--steps", "30", "--warmup", "5", "--no-extras", port=29519)
+    r = _torchrun(2, "bench.py", "--gpus", "2", "--steps", "30", "--warmup", "5", port=29519)
     assert r.returncode == 0, r.stderr[-4000:]
     lines = [l for l in r.stdout.splitlines() if l.startswith("{")]
     assert len(lines) == 1
     d = json.loads(lines[0])
     assert d["n_gpus"] == 2 and d["scaling"] == "weak" and d["value"] > 0 and d["e2e"]["value"] > 0
+    # the data-parallel update leg: graph-captured, gradients exchanged over peer memory and (second leg) NCCL,
+    # bit-identical weights on both ranks (bench.py exits non-zero otherwise)
+    u = d["update"]
+    assert u["ms_per_update"] > 0 and u["train_env_steps_per_s"] > 0
+    c = u["collective"]
+    assert c["weights_identical_across_ranks"] and c["in_update_graph"] and set(c["ms_per_update"]) >= {"local", c["exchange"]}
 
 
 @pytest.mark.skipif(_gpus() < 2, reason="needs 2 GPUs")

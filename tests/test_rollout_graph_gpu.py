@@ -85,7 +85,7 @@ def test_graph_replay_is_bit_identical_to_eager_steps(variant, n, precision):
         ob, rb, db = g.step()
         torch.cuda.synchronize()
         assert torch.equal(oa, ob) and torch.equal(ra, rb) and torch.equal(da, db), k
-    assert g._graph is not None
+    assert g._graphs
     assert_worlds_equal(wa, wb)
 
 

@@ -77,6 +77,23 @@ def host_cores():
 if "TORCHELASTIC_RUN_ID" in os.environ and os.environ.get("RANK", "0") == "0" and os.environ.get("OMP_NUM_THREADS") == "1":
     os.environ["OMP_NUM_THREADS"] = str(host_cores())
 
+# stdout carries exactly ONE line, the JSON: libraries that print to fd 1 (NCCL's "NCCL version ..." banner under
+# NCCL_DEBUG=VERSION, for one) are sent to stderr for the whole run, and emit() writes to the saved descriptor.
+_JSON_FD = None
+
+
+def own_stdout():
+    global _JSON_FD
+    if _JSON_FD is None:
+        sys.stdout.flush()
+        _JSON_FD = os.dup(1)
+        os.dup2(2, 1)
+
+
+def emit(obj):
+    os.write(1 if _JSON_FD is None else _JSON_FD, (json.dumps(obj) + "\n").encode())
+
+
 METRIC = "env-steps/s (dyn+obs+reward+act)"
 UNIT = "env-steps/s"
 ENV_BYTES = {"KAMMA_medium": 265, "KA_DDPG_2D": 253, "KA_DDPG_1D": 249}   # SURVEY.md §8(d), per env-step
@@ -287,7 +304,7 @@ def run_reference(args, wl, n):
     v = n * steps / dt
     cores = host_cores()
     sample = f"{steps} steps x {n} envs (single host process; the CPU path does not shard across GPUs)"
-    print(json.dumps({
+    emit({
         "impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": steps,
         "warmup": args.warmup, "ms_per_step": 1e3 * dt / steps, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f32 (dynamics f64)", "data": "synthetic",
@@ -295,7 +312,7 @@ def run_reference(args, wl, n):
         "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
         "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "note": "reference = pure Python on Isaac Sim/PhysX + skrl: not runnable on this box; this is its pinned CPU port",
-    }), flush=True)
+    })
 
 
 # ------------------------------------------------------------------------------------------------ our arm
@@ -689,11 +706,12 @@ def run_eval_sweep(args, wl, n, device, rank, world_size, dist):
                       "episodes": [int(x) for x in out["episodes"]], "episode_period_steps": period,
                       "all_reduce_us": reduce_us, "all_reduce_bytes": 2 * 10 * 8,
                       "note": "random-init policy: the curve is a parity artefact (tests/test_eval_sweep_gpu.py), not a control result"}}
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 def main():
     args = parse()
+    own_stdout()
     wl = WORKLOADS[args.workload]
     n = args.envs or wl["envs"]
     if args.impl == "reference":
@@ -850,7 +868,7 @@ def main():
             out["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": host_cores(), "kind": "port",
                                    "sample": f"{k} steps x {n} envs in {dt:.1f} s (numpy env oracle + CPU-torch actor, oracle/)",
                                    "parts": time_cpu_parts(wl, n)}
-        print(json.dumps(out), flush=True)
+        emit(out)
     if world_size > 1:
         dist.barrier()
         dist.destroy_process_group()

@@ -247,10 +247,11 @@ int ois_agent_destroy(OisAgent* agent);
  * drop cached bf16 weight images.  ois_ddpg_update_phase invalidates by itself. */
 int ois_agent_invalidate(OisAgent* agent);
 
-/* Bring the handle's cached bf16 image of the actor weights up to date with `actor_params` (a no-op when nothing
- * changed, and for fp32 handles).  ois_agent_act does this by itself; a captured CUDA graph of the rollout step cannot,
- * so its owner calls this before each replay (DDPG._update changes the weights between replays). */
-int ois_agent_sync_weights(OisAgent* agent, const float* actor_params, void* stream);
+/* Bring the bf16 image of the actor weights that ois_agent_act reads for `n_rows` envs up to date with `actor_params`
+ * (a no-op when nothing changed — after ois_ddpg_update_phase the image is already current, the Adam kernels write it
+ * element by element — and for fp32 handles).  ois_agent_act does this by itself; a captured CUDA graph of the rollout
+ * step cannot, so its owner calls this before each replay (DDPG._update changes the weights between replays). */
+int ois_agent_sync_weights(OisAgent* agent, const float* actor_params, int64_t n_rows, void* stream);
 
 /* DDPG.act (ddpg.py:215-268): scaler -> actor MLP -> OU noise -> clamp, N rows. */
 int ois_agent_act(OisAgent* agent, const float* actor_params, const OisScaler* scaler, const OisActIO* io,

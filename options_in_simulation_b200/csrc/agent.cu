@@ -327,8 +327,10 @@ struct AdamPolyak {
 __global__ void __launch_bounds__(256)
 adam_polyak_kernel(const __grid_constant__ AdamPolyak a, float tau) {
   __shared__ float s_step_size, s_bc2_sqrt;
+  // No pdl_trigger here: this is the last kernel of an update and the writer of the actor's parameters and bf16 image.
+  // Its stream successor is often the next policy step's actor kernel (mlp_tct.cu), which starts streaming that image
+  // before its own griddepcontrol.wait; without a trigger that kernel cannot start until this one has completed.
   pdl_wait();
-  if (threadIdx.x == 0) pdl_trigger();
   if (threadIdx.x == 0)
     adam_bias_corrections(a.step_dev ? a.step_dev[0] : a.step_host, a.lr, a.beta1, a.beta2, s_step_size, s_bc2_sqrt);
   const bool dp = a.comm.world > 1;
@@ -670,10 +672,10 @@ extern "C" int ois_mlp_forward(OisAgent* a, const OisMlpShape* shape, const floa
   return mlp_forward_fp32(*shape, params, x, shape->in_dim, a->h0, a->h1, a->h2, y, n_rows, (cudaStream_t)stream);
 }
 
-extern "C" int ois_agent_sync_weights(OisAgent* a, const float* actor_params, void* stream) {
+extern "C" int ois_agent_sync_weights(OisAgent* a, const float* actor_params, int64_t n_rows, void* stream) {
   OIS_CHECK_ARG(a && actor_params, "null argument");
   if (a->precision != OIS_PRECISION_BF16) return OIS_OK;   // the fp32 path reads the master weights directly
-  return tc_sync_image(a, actor_params, (cudaStream_t)stream);
+  return tc_sync_image(a, actor_params, n_rows, (cudaStream_t)stream);
 }
 
 extern "C" int ois_agent_act(OisAgent* a, const float* actor_params, const OisScaler* scaler, const OisActIO* io,

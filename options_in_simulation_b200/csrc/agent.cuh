@@ -37,7 +37,10 @@ int mlp_forward_fp32(const OisMlpShape& sh, const float* P, const float* x, int 
 int tc_agent_init(OisAgent* a, cudaStream_t s);
 void tc_agent_free(OisAgent* a);
 void tc_invalidate_weights(OisAgent* a);
-int tc_sync_image(OisAgent* a, const float* actor_params, cudaStream_t s);
+int tc_sync_image(OisAgent* a, const float* actor_params, int64_t rows, cudaStream_t s);
+// the small-tile transposed kernel (mlp_tct.cu): 64 envs per CTA, weights from the update's tile-blocked image
+int tct_actor_forward(OisAgent* a, const uint8_t* image, const float* actor_params, const OisScaler* scaler, const OisActIO* io,
+                      int64_t rows, cudaStream_t s);
 // scaler -> 4-layer MLP -> (OU noise, scale, clamp when io->ou_state) in ONE launch
 int tc_actor_forward(OisAgent* a, const float* actor_params, const OisScaler* scaler, const OisActIO* io, int64_t rows,
                      cudaStream_t s);

@@ -22,6 +22,7 @@
 #include "agent.cuh"
 #include "explore.cuh"
 #include "tc_ptx.cuh"
+#include "update_tc.cuh"
 
 namespace ois {
 
@@ -280,7 +281,7 @@ tc_actor_kernel(const __grid_constant__ TcActArgs args) {
             const int slot = n % kW2Slots;
             ptx::mbar_wait(&w2_empty[slot], ((n / kW2Slots) & 1) ^ 1);
             ptx::mbar_expect_tx(&w2_full[slot], kW2SlotBytes);
-            ptx::bulk_g2s(s_w2 + slot * kW2SlotBytes, args.image + kImgW2 + (size_t)h * kW2SlotBytes, kW2SlotBytes, &w2_full[slot]);
+            ptx::bulk_g2s(s_w2 + slot * kW2SlotBytes, args.image + tc::kImgW2 + (size_t)h * kW2SlotBytes, kW2SlotBytes, &w2_full[slot]);
           }
         }
       } else if (p == 2) {
@@ -290,13 +291,13 @@ tc_actor_kernel(const __grid_constant__ TcActArgs args) {
             const int slot = n % kW3Slots;
             ptx::mbar_wait(&w3_empty[slot], ((n / kW3Slots) & 1) ^ 1);
             ptx::mbar_expect_tx(&w3_full[slot], kStageBytes);
-            ptx::bulk_g2s(s_w3 + slot * kStageBytes, args.image + kImgW3 + (size_t)k * kStageBytes, kStageBytes, &w3_full[slot]);
+            ptx::bulk_g2s(s_w3 + slot * kStageBytes, args.image + tc::kImgW3 + (size_t)k * kStageBytes, kStageBytes, &w3_full[slot]);
           }
         }
       } else {
         ptx::mbar_expect_tx(wconst_full, kStageBytes + kLastStageBytes);
-        ptx::bulk_g2s(s_w1, args.image + kImgW1, kStageBytes, wconst_full);
-        ptx::bulk_g2s(s_w4, args.image + kImgW4, kLastStageBytes, wconst_full);
+        ptx::bulk_g2s(s_w1, args.image + tc::kImgW1, kStageBytes, wconst_full);
+        ptx::bulk_g2s(s_w4, args.image + tc::kImgW4, kLastStageBytes, wconst_full);
       }
     }
   } else if (warp == 1 || warp == kWarpA2) {
@@ -673,9 +674,22 @@ void tc_invalidate_weights(OisAgent* a) {
   if (a->tc) ((TcState*)a->tc)->valid = false;
 }
 
-// (Re)build the inference kernel's bf16 stream image if the fp32 master changed since it was packed.
-int tc_sync_image(OisAgent* a, const float* actor_params, cudaStream_t s) {
+// Which kernel serves `rows` envs: the transposed small-tile kernel (mlp_tct.cu: 64 envs per CTA, reads the update's
+// tile-blocked image) up to OIS_TCT_MAX_ROWS rows, the 128-env-row-tile kernel of this file (own stream image) beyond.
+static int64_t g_tct_max_rows = -1;     // < 0: OIS_TCT_MAX_ROWS or the default; set by ois_debug_set_tct_max_rows (tests)
+bool tc_use_transposed(const OisAgent* a, int64_t rows) {
+  static const int64_t dflt = [] {
+    const char* e = getenv("OIS_TCT_MAX_ROWS");
+    return e ? (int64_t)atoll(e) : (int64_t)32768;
+  }();
+  const int64_t max_rows = g_tct_max_rows >= 0 ? g_tct_max_rows : dflt;
+  return a->tcu != nullptr && a->actor.in_dim <= 8 && rows <= max_rows;
+}
+
+// (Re)build the bf16 weight image the inference kernel for `rows` envs reads, if the fp32 master changed since.
+int tc_sync_image(OisAgent* a, const float* actor_params, int64_t rows, cudaStream_t s) {
   using namespace tc;
+  if (tc_use_transposed(a, rows)) return tcu_image(a, TCU_ACTOR, actor_params, s);   // kept current by the update's Adam
   TcState* st = (TcState*)a->tc;
   OIS_CHECK_ARG(st, "agent was not created with OIS_PRECISION_BF16");
   if (!st->valid || st->packed_from != actor_params) {
@@ -691,7 +705,9 @@ int tc_sync_image(OisAgent* a, const float* actor_params, cudaStream_t s) {
 int tc_actor_forward(OisAgent* a, const float* actor_params, const OisScaler* scaler, const OisActIO* io, int64_t rows,
                      cudaStream_t s) {
   using namespace tc;
-  if (int e = tc_sync_image(a, actor_params, s)) return e;
+  if (int e = tc_sync_image(a, actor_params, rows, s)) return e;
+  if (tc_use_transposed(a, rows))
+    return tct_actor_forward(a, tcu_image_if_valid(a, TCU_ACTOR, actor_params), actor_params, scaler, io, rows, s);
   TcState* st = (TcState*)a->tc;
   TcActArgs args;
   args.params = actor_params;
@@ -710,6 +726,13 @@ int tc_actor_forward(OisAgent* a, const float* actor_params, const OisScaler* sc
 }
 
 }  // namespace ois
+
+// diagnostics hook for tests and profiles (deliberately not declared in include/ois_b200.h): row count up to which
+// ois_agent_act uses the transposed small-tile kernel; 0 = always the 128-env-row-tile kernel, < 0 = the default
+extern "C" int ois_debug_set_tct_max_rows(long long rows) {
+  ois::g_tct_max_rows = rows;
+  return 0;
+}
 
 // diagnostics hook for profiles/tc_trace.py (deliberately not declared in include/ois_b200.h)
 extern "C" int ois_debug_tc_trace(unsigned long long* out_host, int n) {

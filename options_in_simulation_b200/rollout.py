@@ -213,7 +213,7 @@ class RolloutGraph:
         else:
             # the bf16 image of the actor weights follows DDPG._update; a no-op when nothing changed
             stream = L.current_stream(self._dev_index)
-            L.check(L.lib().ois_agent_sync_weights(a._handle, L.ptr(a.policy.flat), stream))
+            L.check(L.lib().ois_agent_sync_weights(a._handle, L.ptr(a.policy.flat), self.task.num_envs, stream))
             if self._graph_generation != a._handle_generation:
                 self._graphs = {}      # the agent re-created its C handle: the old graphs' pointers are dead
             if src not in self._graphs:

@@ -10,6 +10,10 @@
 //     (__fmul_rn, __fadd_rn, __fdiv_rn ...), so it is bit-identical to CPU torch / the numpy oracle;
 //   * the skid-steer sub-steps (no reference code exists: PhysX) use FMA contraction and MUFU
 //     reciprocals; they are held to <= 1e-6 of the float64 twin (oracle/dynamics_twin.py).
+#include <map>
+#include <mutex>
+#include <string.h>
+#include <math.h>
 #include "ois_common.cuh"
 
 namespace ois {
@@ -20,10 +24,48 @@ __device__ __forceinline__ float sub(float a, float b) { return __fsub_rn(a, b);
 __device__ __forceinline__ float dvd(float a, float b) { return __fdiv_rn(a, b); }
 __device__ __forceinline__ float clipf(float x, float lo, float hi) { return fminf(fmaxf(x, lo), hi); }
 
-// torch.clamp(1.0 - (sim_steps.float() / max_sim_steps), min=0.0)   KAMMA_medium.py:627-628
-__device__ __forceinline__ float gamma_assist(int mode, float constant, int64_t sim_steps, float max_sim_steps) {
-  if (mode == OIS_GAMMA_DECAY) return fmaxf(sub(1.0f, dvd((float)sim_steps, max_sim_steps)), 0.0f);
-  return constant;
+// ---------------------------------------------------------------------------------------------
+// Correctly rounded division by a divisor that is constant for the launch (dt, action_scale, max_sim_steps).
+// __fdiv_rn costs 11 instructions plus a branch per quotient (MUFU.RCP, FCHK, five FFMA) and falls into a subroutine
+// for zero numerators; the kernel is issue-bound, and the step has ten such quotients per env.  With rc = RN(1/d):
+//     q0 = RN(x rc);  r = x - d q0 (exact, one FMA);  q = RN(q0 + r rc)
+// is RN(x / d) (Markstein 1990; Brisebarre, Muller & Raina 2004) for every x unless d is one of a few exceptional
+// divisors — so the HOST checks each divisor once, exhaustively over all 2^23 significands of x (the result is
+// scale-invariant), before the kernel is allowed to use it (const_div_exact below); otherwise `exact` is 0 and the
+// kernel divides with __fdiv_rn.  Zero numerators return x (IEEE: +-0 / d = +-0 for d > 0).  Not covered: infinite,
+// NaN or subnormal x — none of which a finite rollout state produces.
+// ---------------------------------------------------------------------------------------------
+struct ConstDiv {
+  float d, rc;
+  int exact;
+};
+__device__ __forceinline__ float cdiv(float x, const ConstDiv& c) {
+  if (!c.exact) return __fdiv_rn(x, c.d);
+  const float q0 = __fmul_rn(x, c.rc);
+  const float r = __fmaf_rn(-c.d, q0, x);
+  const float q = __fmaf_rn(r, c.rc, q0);
+  return x == 0.0f ? x : q;
+}
+struct EnvDerived {
+  ConstDiv dt, action_scale, max_sim_steps;
+};
+
+// Philox2x32-10 (Salmon et al. 2011, Random123): the per-step Bernoulli switch needs ONE uniform per env, and the
+// four-lane generator costs 85 instructions for it; this one costs 25.  counter = (env, step offset), key = folded seed.
+__device__ __forceinline__ uint32_t philox2x32(uint32_t c0, uint32_t c1, uint32_t key) {
+#pragma unroll
+  for (int r = 0; r < 10; ++r) {
+    const uint64_t p = (uint64_t)0xD256D193u * c0;
+    c0 = (uint32_t)(p >> 32) ^ key ^ c1;
+    c1 = (uint32_t)p;
+    key += 0x9E3779B9u;
+  }
+  return c0;
+}
+
+// torch.clamp(1.0 - (sim_steps.float() / max_sim_steps), min=0.0)   KAMMA_medium.py:627-628; `decay` is that value
+__device__ __forceinline__ float gamma_assist(int mode, float constant, float decay) {
+  return mode == OIS_GAMMA_DECAY ? decay : constant;
 }
 
 struct Skid {
@@ -48,14 +90,25 @@ __device__ __forceinline__ float2 bc(float s) { return make_float2(s, s); }
 __device__ __forceinline__ float2 neg2(float2 a) { return make_float2(-a.x, -a.y); }
 __device__ __forceinline__ float mufu_rcp(float x) { float r; asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
 __device__ __forceinline__ float mufu_rsq(float x) { float r; asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
-// 1/x for two lanes: MUFU seed + one Newton step, r <- r + r (1 - x r)
+// 1/x for two lanes: the MUFU.RCP result (<= 1 ulp) as is; OIS_ENV_RCP_NEWTON adds one Newton step r <- r + r (1 - x r)
+#ifndef OIS_ENV_RCP_NEWTON
+#define OIS_ENV_RCP_NEWTON 0
+#endif
 __device__ __forceinline__ float2 rcp2(float2 x) {
   const float2 r = make_float2(mufu_rcp(x.x), mufu_rcp(x.y));
+#if OIS_ENV_RCP_NEWTON
   return fma2(r, fma2(neg2(x), r, bc(1.0f)), r);
+#else
+  return r;
+#endif
 }
 __device__ __forceinline__ float rcp1(float x) {
   const float r = mufu_rcp(x);
+#if OIS_ENV_RCP_NEWTON
   return fmaf(r, fmaf(-x, r, 1.0f), r);
+#else
+  return r;
+#endif
 }
 
 struct AxleOut { float2 al, be, k, g, phi, kl; };
@@ -249,7 +302,7 @@ __device__ __forceinline__ int64_t replay_row_base(const OisEnvIO& io, int64_t n
 template <bool kStats, bool kEval>
 __global__ void __launch_bounds__(kEnvThreads, kEnvMinBlocks)
 env_step_kernel(const __grid_constant__ OisEnvParams p, const __grid_constant__ OisEnvState st,
-                const __grid_constant__ OisEnvIO io, const int64_t n) {
+                const __grid_constant__ OisEnvIO io, const int64_t n, const __grid_constant__ EnvDerived dv) {
   __shared__ float s_stats[OIS_EP_STATS_LEN];
   // Programmatic dependent launch: this grid may have started while its stream predecessor (normally the actor kernel)
   // was still running.  The predecessor may be another env step (tests, dynamics-only loops), so nothing is read
@@ -344,15 +397,18 @@ env_step_kernel(const __grid_constant__ OisEnvParams p, const __grid_constant__ 
     const float current_v = pv.w, current_w = tp.y;
     const float v_delta = sub(desired_v, current_v);
     const float omega_delta = sub(desired_w, current_w);
-    const float lin = mul(p.kp, mul(p.vehicle_mass, dvd(v_delta, p.dt)));
-    const float ang = mul(p.kp_omega, mul(p.vehicle_inertia, dvd(omega_delta, p.dt)));
+    const float lin = mul(p.kp, mul(p.vehicle_mass, cdiv(v_delta, dv.dt)));
+    const float ang = mul(p.kp_omega, mul(p.vehicle_inertia, cdiv(omega_delta, dv.dt)));
     const float ac_left = sub(lin, ang), ac_right = add(lin, ang);
     const float crit[4] = {ac_left, ac_left, ac_right, ac_right};
-    const float g1 = gamma_assist(p.gamma1_mode, p.gamma1_const, sim, p.max_sim_steps);
-    const float g2 = gamma_assist(p.gamma2_mode, p.gamma2_const, sim, p.max_sim_steps);
+    const float decay = fmaxf(sub(1.0f, cdiv((float)sim, dv.max_sim_steps)), 0.0f);
+    const float g1 = gamma_assist(p.gamma1_mode, p.gamma1_const, decay);
+    const float g2 = gamma_assist(p.gamma2_mode, p.gamma2_const, decay);
     float tq[4], wt[4];
     if (p.blend == OIS_BLEND_SWITCH) {          // :632-636
-      const float rm = need_mask_draw ? u01(Philox(io.philox_seed)((uint64_t)i, env_philox_offset(io) * 4).x) : __ldcs(io.rand_mask + i);
+      const float rm = need_mask_draw ? u01(philox2x32((uint32_t)i, (uint32_t)env_philox_offset(io),
+                                                       (uint32_t)io.philox_seed ^ (uint32_t)(io.philox_seed >> 32) ^ (uint32_t)(i >> 32)))
+                                      : __ldcs(io.rand_mask + i);
       const float mask = rm < g1 ? 1.0f : 0.0f;
       const float nmask = sub(1.0f, mask);
 #pragma unroll
@@ -387,7 +443,7 @@ env_step_kernel(const __grid_constant__ OisEnvParams p, const __grid_constant__ 
     }
     const float r3 = add(add(add(mul(wt[0], wt[0]), mul(wt[1], wt[1])), mul(wt[2], wt[2])), mul(wt[3], wt[3]));
     // calculate_metrics :770 — linear_acc lags a step: it uses the pre-physics projection
-    const float lin_acc = dvd(sub(current_v, tp.z), p.dt);
+    const float lin_acc = cdiv(sub(current_v, tp.z), dv.dt);
     float smooth = 0.f;
     if (kEval) {                                // KAMMA_eval.py:677-685
       float4 ot = ld_stream4(st.old_torques + 4 * i);
@@ -399,8 +455,8 @@ env_step_kernel(const __grid_constant__ OisEnvParams p, const __grid_constant__ 
     float4 replay_act = make_float4(0.f, 0.f, 0.f, 0.f);
     if (replay) {   // what record_transition stores as the action (base_KA_DDPG.py:212 relabel, or the policy's)
       if (io.relabel == OIS_RELABEL_EXECUTED)
-        replay_act = make_float4(dvd(wt[0], p.action_scale), dvd(wt[1], p.action_scale), dvd(wt[2], p.action_scale),
-                                 dvd(wt[3], p.action_scale));
+        replay_act = make_float4(cdiv(wt[0], dv.action_scale), cdiv(wt[1], dv.action_scale), cdiv(wt[2], dv.action_scale),
+                                 cdiv(wt[3], dv.action_scale));
       else replay_act = make_float4(a4[0], a4[1], a4[2], a4[3]);
       const int64_t ri = replay_row_base(io, n) + i;
       if (io.relabel == OIS_RELABEL_EXECUTED || p.act_dim == 4) st_stream4(io.replay_actions + 4 * ri, replay_act);
@@ -441,7 +497,7 @@ env_step_kernel(const __grid_constant__ OisEnvParams p, const __grid_constant__ 
     const bool reset = timeout | oob;
 
     // calculate_metrics :767-810
-    const float ang_acc = dvd(sub(s.r, tp.w), p.dt);
+    const float ang_acc = cdiv(sub(s.r, tp.w), dv.dt);
     const float prev_lin = current_v, prev_ang = s.r;
     const float r1 = add(mul(v_delta, v_delta), mul(5.0f, mul(omega_delta, omega_delta)));
     const float r2 = add(mul(lin_acc, lin_acc), mul(ang_acc, ang_acc));
@@ -639,6 +695,46 @@ static int grid_for(int64_t n, int threads) {
   return (int)blocks;
 }
 
+// Is q = RN(q0 + (x - d q0) rc), q0 = RN(x rc), rc = RN(1/d), the correctly rounded x / d for EVERY x?  The answer
+// depends only on the significands, so all 2^23 of x in [1, 2) are tried once per divisor (about 20 ms on one host core;
+// cached).  Mirrors cdiv() with the host's correctly rounded fmaf.
+static bool const_div_exact(float d) {
+  static std::mutex mu;
+  static std::map<uint32_t, bool> cache;
+  uint32_t key;
+  memcpy(&key, &d, 4);
+  std::lock_guard<std::mutex> lock(mu);
+  auto it = cache.find(key);
+  if (it != cache.end()) return it->second;
+  bool ok = d > 1e-12f && d < 1e12f;       // comfortably inside the normal range: no under- / overflow in q0, r
+  if (ok) {
+    const volatile float rcv = 1.0f / d;   // IEEE division: RN(1/d)
+    const float rc = rcv;
+    for (uint32_t m = 0; m < (1u << 23) && ok; ++m) {
+      const uint32_t bits = 0x3F800000u | m;
+      float x;
+      memcpy(&x, &bits, 4);
+      const volatile float q0v = x * rc;
+      const float q0 = q0v;
+      const float r = fmaf(-d, q0, x);
+      const float q = fmaf(r, rc, q0);
+      const volatile float refv = x / d;
+      if (q != refv) ok = false;
+    }
+  }
+  cache[key] = ok;
+  return ok;
+}
+
+static ConstDiv const_div(float d) {
+  ConstDiv c;
+  c.d = d;
+  c.exact = const_div_exact(d) ? 1 : 0;
+  const volatile float rc = 1.0f / d;
+  c.rc = rc;
+  return c;
+}
+
 static int check_state(const OisEnvParams* p, const OisEnvState* s) {
   OIS_CHECK_ARG(p && s, "null params/state");
   OIS_CHECK_ARG(p->act_dim == 1 || p->act_dim == 2 || p->act_dim == 4, "act_dim must be 1, 2 or 4");
@@ -679,11 +775,15 @@ extern "C" int ois_env_step(const OisEnvParams* params, const OisEnvState* state
     carveout_set = true;
   }
   const bool stats = io->ep_stats != nullptr, ev = params->eval_sums != 0;
+  EnvDerived dv;
+  dv.dt = const_div(params->dt);
+  dv.action_scale = const_div(params->action_scale);
+  dv.max_sim_steps = const_div(params->max_sim_steps);
   cudaError_t le;
-  if (stats && ev) le = launch_pdl(env_step_kernel<true, true>, grid, kEnvThreads, 0, s, *params, *state, *io, n_envs);
-  else if (stats) le = launch_pdl(env_step_kernel<true, false>, grid, kEnvThreads, 0, s, *params, *state, *io, n_envs);
-  else if (ev) le = launch_pdl(env_step_kernel<false, true>, grid, kEnvThreads, 0, s, *params, *state, *io, n_envs);
-  else le = launch_pdl(env_step_kernel<false, false>, grid, kEnvThreads, 0, s, *params, *state, *io, n_envs);
+  if (stats && ev) le = launch_pdl(env_step_kernel<true, true>, grid, kEnvThreads, 0, s, *params, *state, *io, n_envs, dv);
+  else if (stats) le = launch_pdl(env_step_kernel<true, false>, grid, kEnvThreads, 0, s, *params, *state, *io, n_envs, dv);
+  else if (ev) le = launch_pdl(env_step_kernel<false, true>, grid, kEnvThreads, 0, s, *params, *state, *io, n_envs, dv);
+  else le = launch_pdl(env_step_kernel<false, false>, grid, kEnvThreads, 0, s, *params, *state, *io, n_envs, dv);
   OIS_CHECK_CUDA(le);
   return OIS_OK;
 }

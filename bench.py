@@ -417,6 +417,29 @@ def kernel_split(world, steps, flush):
     return f(acts), f(envs)
 
 
+def kernels_back_to_back(world, reps=20):
+    """Average launch duration of each kernel with `reps` launches of the SAME kernel issued back to back inside one event
+    bracket (no per-launch event pair: an event pair around a single kernel adds ~6 us of front-end latency on this
+    system, profiles/micro/launch_overhead.cu).  Only used where the state exceeds L2, so no flush is needed between
+    launches; the env kernel advances its own state from launch to launch, the actor re-reads the same observations."""
+    torch = world.torch
+    actions = world.agent.act(world.obs, world.t, world.T)[0].clone()
+    for _ in range(2):
+        world.env.step(actions)
+    a, b, c = (torch.cuda.Event(enable_timing=True) for _ in range(3))
+    torch.cuda.synchronize()
+    a.record()
+    for _ in range(reps):
+        world.env.step(actions)
+    b.record()
+    for _ in range(reps):
+        world.agent.act(world.obs, world.t, world.T)
+    c.record()
+    torch.cuda.synchronize()
+    world.obs = world.task.obs_clipped
+    return b.elapsed_time(c) / reps, a.elapsed_time(b) / reps
+
+
 def e2e_timed(world, steps, warmup):
     """Host in the loop: observations come from pinned host memory, results go back to pinned host memory."""
     torch = world.torch
@@ -852,10 +875,15 @@ def main():
                 w = World(wl, big, args.precision, device, seed=99)
                 small = big * 335 < (96 << 20)          # state + replay rows fit in L2: flush between steps, as at 4096
                 a_ms, e_ms = kernel_split(w, 20, flush if small else None)
+                how = "events around every launch, L2 flushed between steps"
+                if not small:
+                    a_ms, e_ms = kernels_back_to_back(w)
+                    how = "20 launches of the same kernel back to back inside one event bracket (state exceeds L2)"
                 for _ in range(3):
                     w.step()
                 m, _ = device_timed(w, 20, 3, flush if small else None)
                 scale.append({"envs": big, "value": big * 1e3 / m, "ms_per_step": m, "act_ms": a_ms, "env_ms": e_ms,
+                              "kernel_ms_measured": how,
                               "env_traffic": traffic.get(("env", big)), "act_traffic": traffic.get(("actor", big)),
                               "env_hbm_frac": (ENV_BYTES[wl["variant"]] + REPLAY_BYTES) * big / (e_ms * 1e-3) / 1e9 / hbm_peak,
                               "act_tensor_frac": ACTOR_FLOP[wl["act_dim"]] * big / (a_ms * 1e-3) / 1e12 / tc_peak,

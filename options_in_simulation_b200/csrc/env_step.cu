@@ -79,7 +79,7 @@ struct Skid {
 // x = (+a, -a, +a, -a), y = (+b, +b, -b, -b).
 //
 // The kernel is issue-bound, not HBM-bound (profiles/r01_ncu_full_summary.txt), so the sub-step is written
-// for instruction count: the two wheels of an axle travel as one packed float2 (lane x = left, y = right)
+// for instruction count: the two wheels of a side travel as one packed float2 (lane x = front, y = rear)
 // through Blackwell's FFMA2 / FMUL2 / FADD2; reciprocals are MUFU.RCP + one Newton step (2 FMA, no IEEE
 // slow path); the slip norm uses MUFU.RSQ directly.
 // ---------------------------------------------------------------------------------------------
@@ -111,14 +111,16 @@ __device__ __forceinline__ float rcp1(float x) {
 #endif
 }
 
-struct AxleOut { float2 al, be, k, g, phi, kl; };
+struct SideOut { float2 al, be, k, g, phi, kl; };
 
-// one axle (x position xi, lateral contact speed l): the left (y=+b) and right (y=-b) wheels in the two lanes
-__device__ __forceinline__ AxleOut axle(float2 w, float2 tau, float2 nu /* -(uL, uR) */, float l, float2 R2, float2 RR2,
-                                        float2 Iwh2, float2 nc2, float2 mu2, float eps2) {
-  AxleOut o;
-  const float2 sx = fma2(R2, w, nu);                       // R w - u
-  const float2 n2 = fma2(sx, sx, bc(fmaf(l, l, eps2)));
+// one SIDE of the vehicle (lateral position y): its front (x = +a) and rear (x = -a) wheels in the two lanes.  Pairing by
+// side keeps every packed operand in the registers it already lives in — wheel speeds and torques are stored
+// (fl, rl, fr, rr), so (fl, rl) and (fr, rr) are adjacent — where pairing by axle cost a dozen register moves per sub-step.
+__device__ __forceinline__ SideOut side(float2 w, float2 tau, float nu /* -u of this side */, float2 l, float2 l2e /* l^2 + eps^2 */,
+                                        float2 R2, float2 RR2, float2 Iwh2, float2 nc2, float2 mu2) {
+  SideOut o;
+  const float2 sx = fma2(R2, w, bc(nu));                   // R w - u
+  const float2 n2 = fma2(sx, sx, l2e);
   const float2 k = mul2(make_float2(mufu_rsq(n2.x), mufu_rsq(n2.y)), mu2);
   const float2 inv = rcp2(fma2(RR2, k, Iwh2));             // 1 / (Iw/h + c + R^2 k)
   const float2 Rk = mul2(R2, k);
@@ -126,7 +128,7 @@ __device__ __forceinline__ AxleOut axle(float2 w, float2 tau, float2 nu /* -(uL,
   o.be = mul2(Rk, inv);
   o.g = mul2(mul2(k, Iwh2), inv);
   o.phi = mul2(k, fma2(R2, o.al, sx));
-  o.kl = mul2(k, bc(l));
+  o.kl = mul2(k, l);
   o.k = k;
   return o;
 }
@@ -139,27 +141,27 @@ __device__ __forceinline__ void skid_steps(Skid& s, const float tau[4], const Oi
   const float eps2 = p.slip_eps * p.slip_eps, aa = a * a, bb = b * b;
   const float wmax = p.wheel_speed_max;
   const float2 R2 = bc(R), RR2 = bc(R * R), Iwh2 = bc(Iw_h), nc2 = bc(-c), mu2 = bc(p.mu_n);
-  const float2 side = make_float2(-b, b);                  // u' - u = dvx -+ dr b  (left, right)
-  float2 wF = make_float2(s.w[0], s.w[2]), wB = make_float2(s.w[1], s.w[3]);   // front / rear axle, (left, right)
-  const float2 tF = make_float2(tau[0], tau[2]), tB = make_float2(tau[1], tau[3]);
+  float2 wL = make_float2(s.w[0], s.w[1]), wR = make_float2(s.w[2], s.w[3]);   // left / right side, (front, rear)
+  const float2 tL = make_float2(tau[0], tau[1]), tR = make_float2(tau[2], tau[3]);
   float sn, cs;
   sincosf(s.yaw, &sn, &cs);
 #pragma unroll 1
   for (int it = 0; it < p.decimation; ++it) {
     const float vx = s.vx, vy = s.vy, r = s.r;
-    const float2 nu = fma2(bc(r), make_float2(b, -b), bc(-vx));   // -(vx - r b), -(vx + r b)
-    const AxleOut F = axle(wF, tF, nu, fmaf(r, a, vy), R2, RR2, Iwh2, nc2, mu2, eps2);
-    const AxleOut B = axle(wB, tB, nu, fmaf(-r, a, vy), R2, RR2, Iwh2, nc2, mu2, eps2);
-    const float2 G = add2(F.g, B.g), K = add2(F.k, B.k), KD = add2(F.k, neg2(B.k));
-    const float2 PH = add2(F.phi, B.phi), KL = add2(F.kl, B.kl), KLD = add2(F.kl, neg2(B.kl));
-    const float gs = G.x + G.y, ks = K.x + K.y;
+    const float2 l = make_float2(fmaf(r, a, vy), fmaf(-r, a, vy));     // lateral contact speed: front, rear
+    const float2 l2e = fma2(l, l, bc(eps2));
+    const SideOut Lf = side(wL, tL, fmaf(r, b, -vx), l, l2e, R2, RR2, Iwh2, nc2, mu2);     // y = +b: u = vx - r b
+    const SideOut Rt = side(wR, tR, fmaf(-r, b, -vx), l, l2e, R2, RR2, Iwh2, nc2, mu2);    // y = -b: u = vx + r b
+    const float2 Sg = add2(Lf.g, Rt.g), Dg = add2(Lf.g, neg2(Rt.g)), Sk = add2(Lf.k, Rt.k);
+    const float2 Sph = add2(Lf.phi, Rt.phi), Dph = add2(Lf.phi, neg2(Rt.phi)), Skl = add2(Lf.kl, Rt.kl);
+    const float gs = Sg.x + Sg.y, ks = Sk.x + Sk.y;
     const float A00 = m_h + gs, A11 = m_h + ks;
     const float A22 = fmaf(bb, gs, fmaf(aa, ks, J_h));
-    const float A02 = -b * (G.x - G.y);                      // -sum y_i g_i
-    const float A12 = a * (KD.x + KD.y);                     //  sum x_i k_i
-    const float b0 = fmaf(m * r, vy, PH.x + PH.y);
-    const float b1 = -fmaf(m * r, vx, KL.x + KL.y);
-    const float b2 = -fmaf(a, KLD.x + KLD.y, b * (PH.x - PH.y));
+    const float A02 = -b * (Dg.x + Dg.y);                    // -sum y_i g_i
+    const float A12 = a * (Sk.x - Sk.y);                     //  sum x_i k_i
+    const float b0 = fmaf(m * r, vy, Sph.x + Sph.y);
+    const float b1 = -fmaf(m * r, vx, Skl.x + Skl.y);
+    const float b2 = -fmaf(a, Skl.x - Skl.y, b * (Dph.x + Dph.y));
     const float2 iA = rcp2(make_float2(A00, A11));
     const float e0 = A02 * iA.x, e1 = A12 * iA.y;
     const float s22 = fmaf(-A12, e1, fmaf(-A02, e0, A22));
@@ -169,11 +171,11 @@ __device__ __forceinline__ void skid_steps(Skid& s, const float tau[4], const Oi
     s.vx = vx + dvx;
     s.vy = vy + dvy;
     s.r = r + dr;
-    const float2 du = fma2(bc(dr), side, bc(dvx));
-    wF = add2(wF, fma2(F.be, du, F.al));
-    wB = add2(wB, fma2(B.be, du, B.al));
-    wF = make_float2(clipf(wF.x, -wmax, wmax), clipf(wF.y, -wmax, wmax));
-    wB = make_float2(clipf(wB.x, -wmax, wmax), clipf(wB.y, -wmax, wmax));
+    // u' - u = dvx -+ dr b  (left, right)
+    wL = add2(wL, fma2(Lf.be, bc(fmaf(-dr, b, dvx)), Lf.al));
+    wR = add2(wR, fma2(Rt.be, bc(fmaf(dr, b, dvx)), Rt.al));
+    wL = make_float2(clipf(wL.x, -wmax, wmax), clipf(wL.y, -wmax, wmax));
+    wR = make_float2(clipf(wR.x, -wmax, wmax), clipf(wR.y, -wmax, wmax));
     // heading: rotate (cos, sin) by d = h*r' with a Taylor pair (|d| <= 0.01 * R wmax / b = 0.3)
     const float d = h * s.r, d2 = d * d;
     const float sd = d * (1.f + d2 * (-1.f / 6.f + d2 * (1.f / 120.f + d2 * (-1.f / 5040.f + d2 * (1.f / 362880.f)))));
@@ -185,7 +187,7 @@ __device__ __forceinline__ void skid_steps(Skid& s, const float tau[4], const Oi
     s.px += h * (s.vx * cs - s.vy * sn);
     s.py += h * (s.vx * sn + s.vy * cs);
   }
-  s.w[0] = wF.x; s.w[2] = wF.y; s.w[1] = wB.x; s.w[3] = wB.y;
+  s.w[0] = wL.x; s.w[1] = wL.y; s.w[2] = wR.x; s.w[3] = wR.y;
 }
 
 // warp-level sum

@@ -871,7 +871,7 @@ def main():
             del world
             torch.cuda.empty_cache()
             # 16 384 = envs per GPU of BASELINE.json configs[3] (128 row tiles: still one wave of the 148 SMs)
-            for big in (16384, 65536, 1048576):
+            for big in (16384, 65536, 1048576, 4194304):
                 w = World(wl, big, args.precision, device, seed=99)
                 small = big * 335 < (96 << 20)          # state + replay rows fit in L2: flush between steps, as at 4096
                 a_ms, e_ms = kernel_split(w, 20, flush if small else None)

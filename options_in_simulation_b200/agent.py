@@ -791,7 +791,8 @@ class DDPG:
 # actor bwd 11 | adam + 2 polyak
 UPDATE_LAUNCHES = (2 + 4 + 2 + 4 + 1 + 2 + 4 + 1 + 11) + (1 + 4 + 2 + 4 + 1 + 4 + 1 + 11) + 3
 # on the bf16 tcgen05 path (csrc/update_tc.cu; steady state, weight images kept current by Adam / polyak):
-# batch prep + 4 grouped fwd (target actor || critic) + 4 grouped fwd (target critic || actor) + TD/loss + critic bwd
-# (3 dgrad + grouped wgrad + bias) | adam + 4 fwd (critic on the actor's actions) + critic dgrad (3 + 1) + pack (sigma' and
-# the policy-loss statistics) + actor bwd 5 | adam(actor) + both polyaks in ONE launch
-UPDATE_LAUNCHES_BF16 = (1 + 4 + 4 + 1 + 5) + (1 + 4 + 4 + 1 + 5) + 1
+# batch prep + 4 grouped fwd (target actor || critic) + 4 grouped fwd (target critic || actor) + TD / loss / first data
+# gradient + critic bwd (2 dgrad + ONE grouped launch of the weight and bias gradients) | adam + policy pass through the
+# critic (3 fwd, layer 3 emits the first data gradient; [layer 4 || dgrad]; dgrad; dx) + sigma' / actor's first data
+# gradient / policy-loss statistics + actor bwd 3 | adam(actor) + both polyaks in ONE launch
+UPDATE_LAUNCHES_BF16 = (1 + 4 + 4 + 1 + 3) + (1 + 6 + 1 + 3) + 1

@@ -201,6 +201,152 @@ critic_loss_kernel(const float* __restrict__ q, float* __restrict__ y, float* __
   }
 }
 
+__device__ __forceinline__ float bf16_lo_f(uint32_t w) { return __uint_as_float(w << 16); }
+__device__ __forceinline__ float bf16_hi_f(uint32_t w) { return __uint_as_float(w & 0xFFFF0000u); }
+__device__ __forceinline__ uint32_t pack_bf16_pair(float lo, float hi) {
+  uint32_t r;
+  asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo));
+  return r;
+}
+// eight columns of d2 = acc * elu'(h): h = the saved bf16 layer-3 activations (elu' = 1 for h > 0, else h + 1)
+__device__ __forceinline__ uint4 d2_chunk(const float (&acc)[8], const uint4 h) {
+  const uint32_t hw[4] = {h.x, h.y, h.z, h.w};
+  uint32_t o[4];
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    const float ha = bf16_lo_f(hw[j]), hb = bf16_hi_f(hw[j]);
+    o[j] = pack_bf16_pair(acc[2 * j] * (ha > 0.f ? 1.f : ha + 1.f), acc[2 * j + 1] * (hb > 0.f ? 1.f : hb + 1.f));
+  }
+  return make_uint4(o[0], o[1], o[2], o[3]);
+}
+
+// Tensor-core update, ddpg.py:391-407 in ONE launch of B / 16 CTAs: TD target, MSE loss, d(loss)/dq as the bf16 dz column
+// AND the first data gradient d2 = (dz W4) * elu'(h2) — with one output the K = 16 GEMM that produced d2 degenerates to
+// bf16(g_r) * bf16(W4[0][n]), an exact fp32 product, so this is bit-identical to that launch and removes it from the
+// dependent chain.  Thread (row, 8-column chunk); CTA 0 also reduces the loss / target statistics over the whole batch.
+__global__ void __launch_bounds__(256)
+critic_loss_tc_kernel(const float* __restrict__ q, float* __restrict__ y, float* __restrict__ dq, int B, float* __restrict__ stats,
+                      const float* __restrict__ r, const uint8_t* __restrict__ te, const uint8_t* __restrict__ tr,
+                      const float* __restrict__ q2, float discount, uint8_t* __restrict__ dz, uint8_t* __restrict__ d2,
+                      const uint8_t* __restrict__ h2, const uint8_t* __restrict__ w4) {
+  __shared__ float s_sum[8], s_ysum[8], s_ymax[8], s_ymin[8];
+  pdl_wait();
+  if (threadIdx.x == 0) pdl_trigger();
+  const int t = threadIdx.x, lane = t & 31, wp = t >> 5;
+  {
+    const int row = blockIdx.x * 16 + (t >> 4), c8 = t & 15;
+    if (row < B) {
+      const float nd = (te[row] | tr[row]) ? 0.0f : 1.0f;
+      const float yi = __fadd_rn(r[row], __fmul_rn(__fmul_rn(discount, nd), q2[row]));
+      const float g = 2.0f * (q[row] - yi) / (float)B;
+      const uint32_t gb = (uint32_t)tcu_bf16_bits(g);
+      if (c8 < 2) *reinterpret_cast<uint4*>(dz + tcu_chunk_off(row, c8, 2, 128)) = make_uint4(c8 == 0 ? gb : 0u, 0u, 0u, 0u);
+      const float gf = __uint_as_float(gb << 16);
+      const uint4 w = *reinterpret_cast<const uint4*>(w4 + c8 * 256);                    // row 0 of W4, columns 8 c8 ..
+      const uint4 h = *reinterpret_cast<const uint4*>(h2 + tcu_chunk_off(row, c8, 16, 128));
+      const float acc[8] = {gf * bf16_lo_f(w.x), gf * bf16_hi_f(w.x), gf * bf16_lo_f(w.y), gf * bf16_hi_f(w.y),
+                            gf * bf16_lo_f(w.z), gf * bf16_hi_f(w.z), gf * bf16_lo_f(w.w), gf * bf16_hi_f(w.w)};
+      *reinterpret_cast<uint4*>(d2 + tcu_chunk_off(row, c8, 16, 128)) = d2_chunk(acc, h);
+    }
+  }
+  if (blockIdx.x != 0) return;
+  float a = 0.f, ys = 0.f, ymx = -INFINITY, ymn = INFINITY;
+  for (int i = t; i < B; i += 256) {      // the same loop, order and arithmetic as critic_loss_kernel
+    const float nd = (te[i] | tr[i]) ? 0.0f : 1.0f;
+    const float yi = __fadd_rn(r[i], __fmul_rn(__fmul_rn(discount, nd), q2[i]));
+    y[i] = yi;
+    const float d = q[i] - yi;
+    a += d * d;
+    dq[i] = 2.0f * d / (float)B;
+    ys += yi;
+    ymx = fmaxf(ymx, yi);
+    ymn = fminf(ymn, yi);
+  }
+  for (int o = 16; o > 0; o >>= 1) {
+    a += __shfl_xor_sync(0xffffffffu, a, o);
+    ys += __shfl_xor_sync(0xffffffffu, ys, o);
+    ymx = fmaxf(ymx, __shfl_xor_sync(0xffffffffu, ymx, o));
+    ymn = fminf(ymn, __shfl_xor_sync(0xffffffffu, ymn, o));
+  }
+  if (lane == 0) { s_sum[wp] = a; s_ysum[wp] = ys; s_ymax[wp] = ymx; s_ymin[wp] = ymn; }
+  __syncthreads();
+  if (t == 0 && stats) {
+    float A = 0.f, Y = 0.f, MX = -INFINITY, MN = INFINITY;
+    for (int w = 0; w < 8; ++w) { A += s_sum[w]; Y += s_ysum[w]; MX = fmaxf(MX, s_ymax[w]); MN = fminf(MN, s_ymin[w]); }
+    stats[0] = A / (float)B;
+    stats[5] = MX; stats[6] = MN; stats[7] = Y / (float)B;
+  }
+}
+
+// Tensor-core update, the actor's side of ddpg.py:423-429 in ONE launch of B / 16 CTAs: dz = d(loss)/d(action) * act'(a)
+// (sigmoid' = a (1 - a), tanh' = 1 - a^2) as the bf16 [B, 16] backward input, the first data gradient
+// d2 = (dz W4) * elu'(h2) (out_dim <= 8 terms per element, accumulated in fp32 in column order) and, in CTA 0, the
+// policy-loss statistics of ddpg.py:423 (loss = -mean q, max / min / mean q) in policy_loss_kernel's summation order.
+__global__ void __launch_bounds__(256)
+actor_dz_kernel(const float* __restrict__ dx, int lddx, int col0, const float* __restrict__ act_out, int A, int act, int B,
+                uint8_t* __restrict__ dz, uint8_t* __restrict__ d2, const uint8_t* __restrict__ h2,
+                const uint8_t* __restrict__ w4, const float* __restrict__ q, float* __restrict__ stats) {
+  __shared__ float s_sum[8], s_max[8], s_min[8];
+  pdl_wait();
+  if (threadIdx.x == 0) pdl_trigger();
+  const int t = threadIdx.x, lane = t & 31, wp = t >> 5;
+  {
+    const int row = blockIdx.x * 16 + (t >> 4), c8 = t & 15;
+    if (row < B) {
+      float dzf[8];
+      uint32_t dzb[8];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        float x = 0.f;
+        if (j < A) {
+          x = dx[(size_t)row * lddx + col0 + j];
+          const float av = act_out[(size_t)row * A + j];
+          x = act == OIS_ACT_SIGMOID ? x * av * (1.f - av) : act == OIS_ACT_TANH ? x * (1.f - av * av) : x;
+        }
+        dzb[j] = (uint32_t)tcu_bf16_bits(x);
+        dzf[j] = __uint_as_float(dzb[j] << 16);
+      }
+      if (c8 == 0)
+        *reinterpret_cast<uint4*>(dz + tcu_chunk_off(row, 0, 2, 128)) =
+            make_uint4(dzb[0] | (dzb[1] << 16), dzb[2] | (dzb[3] << 16), dzb[4] | (dzb[5] << 16), dzb[6] | (dzb[7] << 16));
+      if (c8 == 1) *reinterpret_cast<uint4*>(dz + tcu_chunk_off(row, 1, 2, 128)) = make_uint4(0u, 0u, 0u, 0u);
+      float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        if (j < A) {
+          const uint4 w = *reinterpret_cast<const uint4*>(w4 + c8 * 256 + j * 16);       // row j of W4, columns 8 c8 ..
+          acc[0] = fmaf(dzf[j], bf16_lo_f(w.x), acc[0]); acc[1] = fmaf(dzf[j], bf16_hi_f(w.x), acc[1]);
+          acc[2] = fmaf(dzf[j], bf16_lo_f(w.y), acc[2]); acc[3] = fmaf(dzf[j], bf16_hi_f(w.y), acc[3]);
+          acc[4] = fmaf(dzf[j], bf16_lo_f(w.z), acc[4]); acc[5] = fmaf(dzf[j], bf16_hi_f(w.z), acc[5]);
+          acc[6] = fmaf(dzf[j], bf16_lo_f(w.w), acc[6]); acc[7] = fmaf(dzf[j], bf16_hi_f(w.w), acc[7]);
+        }
+      }
+      const uint4 h = *reinterpret_cast<const uint4*>(h2 + tcu_chunk_off(row, c8, 16, 128));
+      *reinterpret_cast<uint4*>(d2 + tcu_chunk_off(row, c8, 16, 128)) = d2_chunk(acc, h);
+    }
+  }
+  if (blockIdx.x != 0 || q == nullptr) return;
+  float a = 0.f, mx = -INFINITY, mn = INFINITY;
+  for (int k = t; k < B; k += 256) {
+    a += q[k];
+    mx = fmaxf(mx, q[k]);
+    mn = fminf(mn, q[k]);
+  }
+  for (int o = 16; o > 0; o >>= 1) {
+    a += __shfl_xor_sync(0xffffffffu, a, o);
+    mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+    mn = fminf(mn, __shfl_xor_sync(0xffffffffu, mn, o));
+  }
+  if (lane == 0) { s_sum[wp] = a; s_max[wp] = mx; s_min[wp] = mn; }
+  __syncthreads();
+  if (t == 0 && stats) {
+    float S = 0.f, MX = -INFINITY, MN = INFINITY;
+    for (int w = 0; w < 8; ++w) { S += s_sum[w]; MX = fmaxf(MX, s_max[w]); MN = fminf(MN, s_min[w]); }
+    stats[1] = -S / (float)B;
+    stats[2] = MX; stats[3] = MN; stats[4] = S / (float)B;
+  }
+}
+
 // policy loss = -mean(q_pi), dq = -1/B; also Q stats.   one CTA
 __global__ void __launch_bounds__(256)
 policy_loss_kernel(const float* __restrict__ q, float* __restrict__ dq, int B, float* __restrict__ stats,
@@ -760,9 +906,12 @@ extern "C" int ois_ddpg_update_phase(OisAgent* a, const OisScaler* scaler, const
         if (int e = tcu_forward(a, 2, nets, P32, acts, y, xo, D, s)) return e;
       }
       // TD target + MSE + d(loss)/dq as the backward's bf16 input (ddpg.py:391-407)
-      OIS_CHECK_CUDA(launch_pdl(critic_loss_kernel, 1, 256, 0, s, (const float*)a->u_q, a->u_y, a->u_dq, B, io->stats, io->rewards,
-                                io->terminated, io->truncated, (const float*)a->u_q2, io->discount, tcu_x_buffer(a, TCU_DZ)));
-      return tcu_backward(a, TCU_CRITIC, io->critic_grad, TCU_ACTS_CRITIC, nullptr, false, s);
+      // and the backward's first data gradient d2 (critic_loss_tc_kernel): the chain continues at layer 3
+      OIS_CHECK_CUDA(launch_pdl(critic_loss_tc_kernel, (B + 15) / 16, 256, 0, s, (const float*)a->u_q, a->u_y, a->u_dq, B, io->stats,
+                                io->rewards, io->terminated, io->truncated, (const float*)a->u_q2, io->discount,
+                                tcu_x_buffer(a, TCU_DZ), tcu_d2_buffer(a), tcu_h2_buffer(a, TCU_ACTS_CRITIC),
+                                tcu_w4_image(a, TCU_CRITIC)));
+      return tcu_backward(a, TCU_CRITIC, io->critic_grad, TCU_ACTS_CRITIC, nullptr, false, true, s);
     }
     // ddpg.py:381-382  scaler(train=True) on states, then on next_states
     if (has_scaler) {
@@ -802,18 +951,17 @@ extern "C" int ois_ddpg_update_phase(OisAgent* a, const OisScaler* scaler, const
       // ddpg.py:420-423 policy loss through the updated critic; the actor's forward already ran in phase 0 (its actions
       // are in x_policy's columns D.. and in u_a), so only the critic's forward on (states, actor actions) is left.
       // TCU_ACTS_POLICY shares the hidden-activation buffers of TCU_ACTS_CRITIC, which phase 0's backward is done with
-      {
-        const int nets[1] = {TCU_CRITIC}, acts[1] = {TCU_ACTS_POLICY};
-        const float* P32[1] = {io->critic};
-        float* y[1] = {a->u_q};
-        if (int e = tcu_forward(a, 1, nets, P32, acts, y, nullptr, 0, s)) return e;
-      }
-      // data gradient only through the critic (its parameter gradients from this pass are discarded by the reference
-      // at the next critic_optimizer.zero_grad(), ddpg.py:406), starting from the constant d(-mean q)/dq = -1/B, then
-      // through the output activation (the same launch writes the policy-loss statistics) and the actor
-      if (int e = tcu_backward(a, TCU_CRITIC, nullptr, TCU_ACTS_CRITIC, a->u_dx, true, s)) return e;
-      if (int e = tcu_pack_x(a, TCU_DZ, a->u_dx, CI, D, A, nullptr, 0, 0, a->u_a, a->actor.out_act, a->u_q, io->stats, s)) return e;
-      return tcu_backward(a, TCU_ACTOR, io->actor_grad, TCU_ACTS_ACTOR, nullptr, false, s);
+      // Forward and data gradient through the critic as one chain (tcu_policy_pass): the loss gradient w.r.t. q is the
+      // constant -1/B, so layer 3 of the forward already emits the first data gradient and layer 4 (q, read only by the
+      // statistics) rides in the next launch.  The critic's parameter gradients of this pass are not computed: the
+      // reference discards them at the next critic_optimizer.zero_grad() (ddpg.py:406).
+      if (int e = tcu_policy_pass(a, TCU_CRITIC, io->critic, TCU_ACTS_POLICY, a->u_q, a->u_dx, s)) return e;
+      // through the output activation into the actor: dz, the actor's first data gradient and the policy-loss statistics
+      OIS_CHECK_ARG(A <= 8, "the fused actor output gradient handles out_dim <= 8");
+      OIS_CHECK_CUDA(launch_pdl(actor_dz_kernel, (B + 15) / 16, 256, 0, s, (const float*)a->u_dx, CI, D, (const float*)a->u_a, A,
+                                a->actor.out_act, B, tcu_x_buffer(a, TCU_DZ), tcu_d2_buffer(a),
+                                tcu_h2_buffer(a, TCU_ACTS_ACTOR), tcu_w4_image(a, TCU_ACTOR), (const float*)a->u_q, io->stats));
+      return tcu_backward(a, TCU_ACTOR, io->actor_grad, TCU_ACTS_ACTOR, nullptr, false, true, s);
     }
     // ddpg.py:420-429  policy loss through the (updated) critic
     if (int e = mlp_forward_fp32(a->actor, io->actor, a->u_sn, D, a->ah0, a->ah1, a->ah2, a->u_a, B, s)) return e;

@@ -691,7 +691,8 @@ reset_idx_kernel(const __grid_constant__ OisEnvParams p, const __grid_constant__
 
 static int grid_for(int64_t n, int threads) {
   int64_t blocks = (n + threads - 1) / threads;
-  const int64_t cap = (int64_t)num_sms() * kEnvMinBlocks * 2;   // two waves of resident CTAs; grid-stride beyond
+  static const int waves = getenv("OIS_ENV_WAVES") ? atoi(getenv("OIS_ENV_WAVES")) : 8;   // measured: 2 -> 8 waves = 63.6 -> 70.3 % of HBM at 4M envs (tail balance)
+  const int64_t cap = (int64_t)num_sms() * kEnvMinBlocks * waves;   // `waves` waves of resident CTAs; grid-stride beyond
   if (blocks > cap) blocks = cap;
   if (blocks < 1) blocks = 1;
   return (int)blocks;

@@ -18,6 +18,7 @@
 // a 3-deep shared-memory ring on mbarriers; warp 0 = bulk-copy producer, warp 1 = tcgen05.mma issuer (one elected
 // lane), warps 2-5 = epilogue (tcgen05.ld -> bias / ELU / ELU' / output activation -> bf16 tile-blocked or fp32).
 #include <new>
+#include <string.h>
 #include "agent.cuh"
 #include "tc_ptx.cuh"
 #include "update_tc.cuh"
@@ -29,15 +30,17 @@ constexpr int kThreads = 320;   // warp 0 producer, warp 1 MMA issuer, warps 2-9
 constexpr int kStages = 3;
 constexpr int kHalfStage = 32768;
 constexpr int kStageBytes = 2 * kHalfStage;           // A (128 x 128 bf16) + B (<= 128 x 128 bf16)
-constexpr int kSmemBytes = kStages * kStageBytes + 128 + 512;
+constexpr int kSmemBytes = kStages * kStageBytes + 128 + 512 + 512;
 constexpr int kTmemCols = 128;
-constexpr int kMaxProblems = 8;
+constexpr int kMaxProblems = 12;
 
 enum Epi : int {
   EPI_HIDDEN = 0,   // out_bf16 = bf16(elu(acc + bias[n]))
   EPI_OUT = 1,      // out_f32[m, n] = act(acc + bias[n]), n < n_valid
   EPI_DGRAD = 2,    // out_bf16 = bf16(acc * elu'(z)), elu' recovered from the saved bf16 output h: h > 0 ? 1 : h + 1
   EPI_F32 = 3,      // out_f32[m, n] (or [n, m] when transposed) = acc, m < m_valid, n < n_valid
+  EPI_BIAS = 4,     // no GEMM: out_f32[n] = sum over the K batch rows of the bf16 matrix `a` [K, a_c8 * 8] (a bias gradient);
+                    // one CTA per 64 columns, riding in the weight-gradient launch instead of a launch of its own
 };
 
 struct Problem {
@@ -54,6 +57,12 @@ struct Problem {
   int ld, m_valid, n_valid, transposed;
   uint8_t* x_out;           // EPI_OUT: also bf16 into columns x_col.. of a tile-blocked [M, 16] buffer
   int x_col;
+  // EPI_HIDDEN with d_out != null (layer 3 of the policy-loss critic pass): the data gradient of the NEXT layer's single
+  // output, d_out[m, n] = bf16(d_coef * d_w[n] * elu'(h[m, n])), is emitted with the activation — exactly what the K = 16
+  // GEMM dz W4 would produce from dz = (d_coef, 0, ...), so that launch (and the wait for layer 4) leaves the chain
+  uint8_t* d_out;
+  const uint8_t* d_w;       // row 0 of the next layer's W in its tile-blocked image ([k chunk][16 rows][8])
+  float d_coef;
   int tile_begin;
 };
 
@@ -84,6 +93,7 @@ tc_gemm_kernel(const __grid_constant__ Group g) {
   uint64_t* d_full = empty + kStages;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(d_full + 1);
   float* s_bias = reinterpret_cast<float*>(smem + kStages * kStageBytes + 128);   // [128]
+  float* s_dw = s_bias + 128;                                                       // [128]
   const bool tr = blockIdx.x == 0 && (threadIdx.x & 31) == 0;
   TCU_STAMP(tr && threadIdx.x == 0, 0);
 
@@ -94,6 +104,39 @@ tc_gemm_kernel(const __grid_constant__ Group g) {
   const Problem P = g.p[pi];   // by value: registers, immune to the memory clobbers of the inline-PTX wrappers
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int t = blockIdx.x - P.tile_begin;
+  if (P.epi == EPI_BIAS) {
+    // ===================================================== bias gradient: warp w of CTA t sums 8-column chunk 8 t + w of `a`
+    // over the K batch rows (eight independent 16-byte loads in flight per lane; fixed summation order)
+    pdl_wait();
+    if (threadIdx.x == 0) pdl_trigger();
+    const int w = t * 8 + warp;
+    if (warp >= 8 || w >= P.a_c8) return;
+    float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    for (int r0 = 0; r0 < P.K; r0 += 256) {
+      uint4 q[8];
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        const int r = r0 + u * 32 + lane;
+        q[u] = r < P.K ? *reinterpret_cast<const uint4*>(P.a + chunk_off(r, w, P.a_c8, 128)) : make_uint4(0, 0, 0, 0);
+      }
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        const uint32_t ws[4] = {q[u].x, q[u].y, q[u].z, q[u].w};
+#pragma unroll
+        for (int j = 0; j < 4; ++j) { acc[2 * j] += bf16_lo(ws[j]); acc[2 * j + 1] += bf16_hi(ws[j]); }
+      }
+    }
+#pragma unroll
+    for (int j = 0; j < 8; ++j)
+      for (int o = 16; o > 0; o >>= 1) acc[j] += __shfl_xor_sync(0xffffffffu, acc[j], o);
+    if (lane < 8 && w * 8 + lane < P.n_valid) {
+      float sacc = acc[0];
+#pragma unroll
+      for (int j = 1; j < 8; ++j) sacc = lane == j ? acc[j] : sacc;
+      P.out_f32[w * 8 + lane] = sacc;
+    }
+    return;
+  }
   const int tile_n = P.tile_n;
   const int tiles_n = P.N / tile_n;
   const int tm = t / tiles_n, tn = t - tm * tiles_n;
@@ -192,6 +235,12 @@ tc_gemm_kernel(const __grid_constant__ Group g) {
     const int et = threadIdx.x - 64;
     if (epi == EPI_HIDDEN || epi == EPI_OUT)
       if (et < tile_n) s_bias[et] = (n0 + et < n_valid || epi == EPI_HIDDEN) ? bias[n0 + et] : 0.f;
+    uint8_t* const d_out = P.d_out;
+    if (d_out && et < tile_n) {   // d_coef * W[0][n] for this tile's columns (both factors are bf16: the product is exact)
+      const int n = n0 + et;
+      const uint32_t wb = *reinterpret_cast<const uint16_t*>(P.d_w + (n >> 3) * 256 + (n & 7) * 2);
+      s_dw[et] = P.d_coef * __uint_as_float(wb << 16);
+    }
     uint4 hreg[8];
     if (epi == EPI_DGRAD) {
       const uint4* hp = reinterpret_cast<const uint4*>(hsrc + chunk_off(gm, n0 >> 3, Ncols >> 3, 128));
@@ -239,8 +288,23 @@ tc_gemm_kernel(const __grid_constant__ Group g) {
           }
         }
         uint4* op = reinterpret_cast<uint4*>(out_bf16 + chunk_off(gm, n >> 3, Ncols >> 3, 128));
-        op[0] = make_uint4(ptx::pack_bf16(x[0], x[1]), ptx::pack_bf16(x[2], x[3]), ptx::pack_bf16(x[4], x[5]), ptx::pack_bf16(x[6], x[7]));
-        op[128] = make_uint4(ptx::pack_bf16(x[8], x[9]), ptx::pack_bf16(x[10], x[11]), ptx::pack_bf16(x[12], x[13]), ptx::pack_bf16(x[14], x[15]));
+        const uint4 o0 = make_uint4(ptx::pack_bf16(x[0], x[1]), ptx::pack_bf16(x[2], x[3]), ptx::pack_bf16(x[4], x[5]), ptx::pack_bf16(x[6], x[7]));
+        const uint4 o1 = make_uint4(ptx::pack_bf16(x[8], x[9]), ptx::pack_bf16(x[10], x[11]), ptx::pack_bf16(x[12], x[13]), ptx::pack_bf16(x[14], x[15]));
+        op[0] = o0;
+        op[128] = o1;
+        if (epi == EPI_HIDDEN && d_out) {   // next layer's data gradient from the bf16 activation just produced (see Problem::d_out)
+          const uint32_t hw[8] = {o0.x, o0.y, o0.z, o0.w, o1.x, o1.y, o1.z, o1.w};
+          float dd[16];
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            const float ha = bf16_lo(hw[j]), hb = bf16_hi(hw[j]);
+            dd[2 * j] = s_dw[c0 + 2 * j] * (ha > 0.f ? 1.f : ha + 1.f);
+            dd[2 * j + 1] = s_dw[c0 + 2 * j + 1] * (hb > 0.f ? 1.f : hb + 1.f);
+          }
+          uint4* dp = reinterpret_cast<uint4*>(d_out + chunk_off(gm, n >> 3, Ncols >> 3, 128));
+          dp[0] = make_uint4(ptx::pack_bf16(dd[0], dd[1]), ptx::pack_bf16(dd[2], dd[3]), ptx::pack_bf16(dd[4], dd[5]), ptx::pack_bf16(dd[6], dd[7]));
+          dp[128] = make_uint4(ptx::pack_bf16(dd[8], dd[9]), ptx::pack_bf16(dd[10], dd[11]), ptx::pack_bf16(dd[12], dd[13]), ptx::pack_bf16(dd[14], dd[15]));
+        }
       } else if (epi == EPI_OUT) {
         if (gm < m_valid) {
 #pragma unroll
@@ -372,53 +436,14 @@ __global__ void fill_policy_dz_kernel(uint8_t* __restrict__ dz, int B) {
   *reinterpret_cast<uint4*>(dz + chunk_off(i, 1, 2, 128)) = make_uint4(0u, 0u, 0u, 0u);
 }
 
-// bias gradients: db[n] = sum over the batch rows of the (bf16, tile-blocked) pre-activation gradients of the four
-// layers; one warp per 8-column chunk
-struct BiasGradArgs {
-  const uint8_t* d[4];
-  float* out[4];
-  int c8[4], n_valid[4];
-  int B;
-};
-__global__ void __launch_bounds__(256)
-bias_grad_kernel(const __grid_constant__ BiasGradArgs a) {
-  pdl_wait();
-  if (threadIdx.x == 0) pdl_trigger();
-  int w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-  const int lane = threadIdx.x & 31;
-  int l = 0;
-  while (l < 4 && w >= a.c8[l]) { w -= a.c8[l]; ++l; }
-  if (l == 4) return;
-  float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-  for (int r0 = 0; r0 < a.B; r0 += 256) {      // eight independent 16-byte loads in flight per lane; fixed summation order
-    uint4 q[8];
-#pragma unroll
-    for (int u = 0; u < 8; ++u) {
-      const int r = r0 + u * 32 + lane;
-      q[u] = r < a.B ? *reinterpret_cast<const uint4*>(a.d[l] + chunk_off(r, w, a.c8[l], 128)) : make_uint4(0, 0, 0, 0);
-    }
-#pragma unroll
-    for (int u = 0; u < 8; ++u) {
-      const uint32_t ws[4] = {q[u].x, q[u].y, q[u].z, q[u].w};
-#pragma unroll
-      for (int j = 0; j < 4; ++j) { acc[2 * j] += bf16_lo(ws[j]); acc[2 * j + 1] += bf16_hi(ws[j]); }
-    }
-  }
-#pragma unroll
-  for (int j = 0; j < 8; ++j)
-    for (int o = 16; o > 0; o >>= 1) acc[j] += __shfl_xor_sync(0xffffffffu, acc[j], o);
-  if (lane < 8 && w * 8 + lane < a.n_valid[l]) {
-    float s = acc[0];
-#pragma unroll
-    for (int j = 1; j < 8; ++j) s = lane == j ? acc[j] : s;
-    a.out[l][w * 8 + lane] = s;
-  }
-}
-
 // ----------------------------------------------------------------------------------------------------------
 // host side
 // ----------------------------------------------------------------------------------------------------------
 static int validate(const Problem& p) {
+  if (p.epi == EPI_BIAS) {
+    OIS_CHECK_ARG(p.a && p.out_f32 && p.a_c8 > 0 && p.K > 0, "bad bias-gradient request");
+    return OIS_OK;
+  }
   const int k_stage = p.K < 128 ? p.K : 128;
   OIS_CHECK_ARG(p.M % 128 == 0 && p.N % p.tile_n == 0 && p.K % k_stage == 0 && p.K % 16 == 0, "bad GEMM extents");
   OIS_CHECK_ARG(p.tile_n % 16 == 0 && p.tile_n >= 16 && p.tile_n <= 128, "bad tile_n");
@@ -432,7 +457,7 @@ int launch_group(Group& g, cudaStream_t s) {
   for (int i = 0; i < g.count; ++i) {
     if (int e = validate(g.p[i])) return e;
     g.p[i].tile_begin = tiles;
-    tiles += (g.p[i].M / 128) * (g.p[i].N / g.p[i].tile_n);
+    tiles += g.p[i].epi == EPI_BIAS ? (g.p[i].a_c8 + 7) / 8 : (g.p[i].M / 128) * (g.p[i].N / g.p[i].tile_n);
   }
   OIS_CHECK_CUDA(launch_pdl(tc_gemm_kernel, tiles, kThreads, kSmemBytes, s, g));
   return OIS_OK;
@@ -476,8 +501,12 @@ static Problem fwd_problem(const OisMlpShape& sh, const float* P32, const uint8_
 struct NetActs { uint8_t *x, *h0, *h1, *h2; };
 
 // up to two independent networks advance layer by layer in the same launches
+// d2_out (single network only): layer 3 also emits the next layer's data gradient for dz = (d_coef, 0, ...) into d2_out
+// (Problem::d_out), and layer 4 is NOT launched: its problem is returned in *last for the caller to group with its
+// next launch (nothing on the gradient chain waits for it).
 static int forward(int count, const OisMlpShape* const* sh, const float* const* P32, const uint8_t* const* img,
-                   const NetActs* acts, float* const* y, uint8_t* const* x_out, int x_col, int B, cudaStream_t s) {
+                   const NetActs* acts, float* const* y, uint8_t* const* x_out, int x_col, int B, cudaStream_t s,
+                   uint8_t* d2_out = nullptr, float d_coef = 0.f, Problem* last = nullptr) {
   for (int l = 0; l < 4; ++l) {
     Group g;
     g.count = count;
@@ -486,6 +515,15 @@ static int forward(int count, const OisMlpShape* const* sh, const float* const* 
       uint8_t* out = l == 0 ? acts[i].h0 : l == 1 ? acts[i].h1 : acts[i].h2;
       g.p[i] = fwd_problem(*sh[i], P32[i], img[i], l, in, out, y[i], x_out ? x_out[i] : nullptr, x_col, B);
     }
+    if (l == 2 && d2_out) {
+      g.p[0].d_out = d2_out;
+      g.p[0].d_w = img[0] + kImgW4;
+      g.p[0].d_coef = d_coef;
+    }
+    if (l == 3 && last) {
+      *last = g.p[0];
+      return OIS_OK;
+    }
     if (int e = launch_group(g, s)) return e;
   }
   return OIS_OK;
@@ -493,8 +531,11 @@ static int forward(int count, const OisMlpShape* const* sh, const float* const* 
 
 // backward given dz = d(loss)/d(pre-activation of the last layer) as tile-blocked bf16 [B, 16].
 // G != null: parameter gradients (flat fp32).  dx != null: d(loss)/d(input) [B, in_dim] fp32.
+// have_d2: d2 = (dz W4) * elu'(h2) was already written by the producer of dz (critic_loss_tc_kernel, actor_dz_kernel,
+// or layer 3 of the forward: Problem::d_out), so the chain starts at layer 3.  extra: a problem that is independent of
+// this backward (the deferred layer 4 of a forward) and rides in its first launch.
 static int backward(const OisMlpShape& sh, const uint8_t* img, float* G, const NetActs& a, const uint8_t* dz, uint8_t* d2,
-                    uint8_t* d1, uint8_t* d0, float* dx, int B, cudaStream_t s) {
+                    uint8_t* d1, uint8_t* d0, float* dx, int B, cudaStream_t s, bool have_d2 = false, const Problem* extra = nullptr) {
   const MlpOffsets o = mlp_offsets(sh);
   // ---- data gradients: d_l = (d_{l+1} W_{l+1}) * elu'(h_l); W read as [k_in, n_out] from the same stored copy
   const uint8_t* din[3] = {dz, d2, d1};
@@ -502,9 +543,14 @@ static int backward(const OisMlpShape& sh, const uint8_t* img, float* G, const N
   const uint8_t* hs[3] = {a.h2, a.h1, a.h0};
   const size_t wo[3] = {kImgW4, kImgW3, kImgW2};
   const int K[3] = {16, 128, 512}, N[3] = {128, 512, 512};
-  for (int i = 0; i < 3; ++i) {
+  for (int i = have_d2 ? 1 : 0; i < 3; ++i) {
     Group g;
     g.count = 1;
+    if (extra) {
+      g.p[1] = *extra;
+      g.count = 2;
+      extra = nullptr;
+    }
     Problem p = base_problem();
     p.a = din[i]; p.a_c8 = K[i] / 8; p.a_rb = 128; p.a_mn = 0;
     p.b = img + wo[i]; p.b_c8 = N[i] / 8; p.b_rb = i == 0 ? 16 : 128; p.b_mn = 1;
@@ -546,18 +592,17 @@ static int backward(const OisMlpShape& sh, const uint8_t* img, float* G, const N
       g.p[g.count++] = p;
     }
   }
+  if (G) {   // bias gradients: column sums of the four pre-activation gradients, in the same launch (EPI_BIAS)
+    const uint8_t* dd[4] = {d0, d1, d2, dz};
+    const int c8[4] = {64, 64, 16, 2}, nv[4] = {512, 512, 128, sh.out_dim};
+    for (int l = 0; l < 4; ++l) {
+      Problem p = base_problem();
+      p.epi = EPI_BIAS; p.a = dd[l]; p.a_c8 = c8[l]; p.K = B; p.out_f32 = G + o.b[l]; p.n_valid = nv[l];
+      g.p[g.count++] = p;
+    }
+  }
   if (g.count)
     if (int e = launch_group(g, s)) return e;
-  if (G) {
-    BiasGradArgs ba;
-    ba.d[0] = d0; ba.d[1] = d1; ba.d[2] = d2; ba.d[3] = dz;
-    ba.c8[0] = 64; ba.c8[1] = 64; ba.c8[2] = 16; ba.c8[3] = 2;
-    ba.n_valid[0] = 512; ba.n_valid[1] = 512; ba.n_valid[2] = 128; ba.n_valid[3] = sh.out_dim;
-    for (int l = 0; l < 4; ++l) ba.out[l] = G + o.b[l];
-    ba.B = B;
-    const int warps = 64 + 64 + 16 + 2;
-    OIS_CHECK_CUDA(launch_pdl(bias_grad_kernel, (warps * 32 + 255) / 256, 256, 0, s, ba));
-  }
   return OIS_OK;
 }
 
@@ -695,12 +740,48 @@ int tcu_forward(OisAgent* a, int count, const int* nets, const float* const* P32
   return forward(count, sh, P32, img, na, y, x_out, x_col, a->batch, s);
 }
 
-int tcu_backward(OisAgent* a, int net, float* G, int acts, float* dx, bool policy_dz, cudaStream_t s) {
+int tcu_backward(OisAgent* a, int net, float* G, int acts, float* dx, bool policy_dz, bool have_d2, cudaStream_t s) {
   State* st = (State*)a->tcu;
   OIS_CHECK_ARG(st && st->valid[net], "backward needs the weight image its forward used");
   return backward(shape_of(a, net), st->img[net], G, st->acts[acts], policy_dz ? st->dz_policy : st->dz, st->d2, st->d1,
-                  st->d0, dx, a->batch, s);
+                  st->d0, dx, a->batch, s, have_d2);
 }
+
+// ddpg.py:420-429 through the critic in ONE chain of launches: q = critic(x) for activation set `acts` with layer 3 also
+// emitting d2 = d(-mean q)/d(pre-activation 3) (the loss gradient w.r.t. q is the constant -1/B, so d2 needs no q), then
+// the data gradients down to dx [B, in_dim]; layer 4 of the forward (q itself, read only by the loss statistics) rides
+// in the first data-gradient launch.  6 launches instead of 4 + 4.
+int tcu_policy_pass(OisAgent* a, int net, const float* P32, int acts, float* q, float* dx, cudaStream_t s) {
+  State* st = (State*)a->tcu;
+  OIS_CHECK_ARG(st, "agent was not created with OIS_PRECISION_BF16");
+  if (int e = tcu_image(a, net, P32, s)) return e;
+  const OisMlpShape* sh[1] = {&shape_of(a, net)};
+  const uint8_t* img[1] = {st->img[net]};
+  const float* P[1] = {P32};
+  NetActs na[1] = {st->acts[acts]};
+  float* y[1] = {q};
+  Problem last;
+  // the coefficient the K = 16 GEMM would have read from dz_policy: bf16(-1 / B)
+  uint16_t cb;
+  {
+    const float c = -1.0f / (float)a->batch;
+    uint32_t u;
+    memcpy(&u, &c, 4);
+    u += 0x7FFFu + ((u >> 16) & 1u);      // round to nearest even
+    cb = (uint16_t)(u >> 16);
+  }
+  const uint32_t cu = (uint32_t)cb << 16;
+  float coef;
+  memcpy(&coef, &cu, 4);
+  if (int e = forward(1, sh, P, img, na, y, nullptr, 0, a->batch, s, st->d2, coef, &last)) return e;
+  return backward(*sh[0], st->img[net], nullptr, st->acts[acts], st->dz_policy, st->d2, st->d1, st->d0, dx, a->batch, s, true, &last);
+}
+
+// buffers the fused loss / output-gradient kernels of agent.cu write: the dz and d2 inputs of a backward, the saved
+// layer-3 activations of activation set `acts`, and row block 0 of W4 inside the image of `net`
+uint8_t* tcu_d2_buffer(OisAgent* a) { return a->tcu ? ((State*)a->tcu)->d2 : nullptr; }
+const uint8_t* tcu_h2_buffer(OisAgent* a, int acts) { return a->tcu ? ((State*)a->tcu)->acts[acts].h2 : nullptr; }
+const uint8_t* tcu_w4_image(OisAgent* a, int net) { return a->tcu ? ((State*)a->tcu)->img[net] + kImgW4 : nullptr; }
 
 // diagnostics hook for tests (deliberately not declared in include/ois_b200.h): C = op(A) op(B) on the tensor cores
 // from tile-blocked bf16 operands the caller prepared; mode bits: 1 = A contracts over its rows, 2 = B likewise

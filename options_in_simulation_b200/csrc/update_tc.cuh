@@ -67,6 +67,13 @@ int tcu_forward(OisAgent* a, int count, const int* nets, const float* const* P32
 // backward of network `net` from the dz buffer through activation set `acts`; G: flat fp32 parameter gradients
 // (nullable), dx: [B, in_dim] fp32 input gradient (nullable); policy_dz: start from the constant -1/B gradient of the
 // policy loss instead of the dz buffer
-int tcu_backward(OisAgent* a, int net, float* G, int acts, float* dx, bool policy_dz, cudaStream_t s);
+// have_d2: the layer-3 gradient d2 is already in tcu_d2_buffer (written together with dz by the fused loss kernels of
+// agent.cu), so the K = 16 data-gradient launch is skipped
+int tcu_backward(OisAgent* a, int net, float* G, int acts, float* dx, bool policy_dz, bool have_d2, cudaStream_t s);
+// the policy loss's trip through the critic (ddpg.py:420-429): q = critic(x of set `acts`) and dx = d(-mean q)/dx
+int tcu_policy_pass(OisAgent* a, int net, const float* P32, int acts, float* q, float* dx, cudaStream_t s);
+uint8_t* tcu_d2_buffer(OisAgent* a);
+const uint8_t* tcu_h2_buffer(OisAgent* a, int acts);
+const uint8_t* tcu_w4_image(OisAgent* a, int net);
 
 }  // namespace ois

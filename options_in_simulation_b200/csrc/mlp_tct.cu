@@ -157,8 +157,11 @@ tct_actor_kernel(const __grid_constant__ Args args) {
   uint64_t* d3_full = h2_ready + 4;
   uint64_t* h3_ready = d3_full + 1;         // 16 warps
   uint64_t* d4_full = h3_ready + 1;
-  uint64_t* noise_ready = d4_full + 1;      // aux warp: the tile's OU noise is in s_noise
-  uint64_t* tile_done = noise_ready + 1;    // 16 warps: every TMEM read of the tile is done
+  // aux warp: the tile's OU noise is in s_noise[tile parity].  TWO barriers, used alternately: the auxiliary warp runs up
+  // to one tile ahead of the warp that consumes the noise at the END of a tile, and a single barrier would then be two
+  // phase completions ahead of its waiter — which a parity wait cannot tell from "not yet" (it would block for ever)
+  uint64_t* noise_ready = d4_full + 1;      // [2]
+  uint64_t* tile_done = noise_ready + 2;    // 16 warps: every TMEM read of the tile is done
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tile_done + 1);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -172,6 +175,10 @@ tct_actor_kernel(const __grid_constant__ Args args) {
     atomicMax(&g_tct_trace[62], t);
   }
 
+  // Set-up.  The weight stream starts as early as possible: thread 0 initialises the barriers, warp 0 signals the two
+  // producer warps (named barrier 2) and they go; they never join another CTA-wide barrier.  Everybody else meets at
+  // named barrier 1 below — including the auxiliary warp, which by then has sat out griddepcontrol.wait (the predecessor
+  // has completed) and has the first tile's observations in registers, so the set-up hides the observation load.
   if (threadIdx.x == 0) {
     for (int i = 0; i < kSlots; ++i) { ptx::mbar_init(&full[i], 1); ptx::mbar_init(&empty[i], 1); }
     ptx::mbar_init(wconst_full, 1);
@@ -181,9 +188,42 @@ tct_actor_kernel(const __grid_constant__ Args args) {
     ptx::mbar_init(d3_full, 1);
     ptx::mbar_init(h3_ready, kEpiWarps);
     ptx::mbar_init(d4_full, 1);
-    ptx::mbar_init(noise_ready, 1);
+    ptx::mbar_init(&noise_ready[0], 1);
+    ptx::mbar_init(&noise_ready[1], 1);
     ptx::mbar_init(tile_done, kEpiWarps);
     ptx::fence_barrier_init();
+  }
+  if (warp == 0) {
+    __syncwarp();
+    asm volatile("bar.arrive 2, 96;" ::: "memory");
+  }
+  if (warp == kWarpProd || warp == kWarpProd + 1) {
+    // ===================================================== producers: one 32 KB weight tile per ring slot, the two threads
+    // alternate (a thread sustains about one bulk copy per 520 cycles whatever its size: profiles/mma_rate.cu).  The
+    // image is older than the previous kernel in the stream (the update's last kernel never triggers its dependents
+    // early, agent.cu), so the stream starts before griddepcontrol.wait.
+    asm volatile("bar.sync 2, 96;" ::: "memory");
+    if (lane == 0 && args.debug != 1) {
+      const int p = warp - kWarpProd;
+      if (p == 0) {
+        ptx::mbar_expect_tx(wconst_full, kH0 * kInPad * 2 + kOutPad * kH2 * 2);
+        ptx::bulk_g2s(s_w1, args.image + kImgW1, kH0 * kInPad * 2, wconst_full);
+        ptx::bulk_g2s(s_w4, args.image + kImgW4, kOutPad * kH2 * 2, wconst_full);
+      }
+      uint32_t n = 0;
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+        for (int s = 0; s < kStagesPerTile; ++s, ++n) {
+          if ((int)(n & 1) != p) continue;
+          const int slot = n % kSlots;
+          wait(&empty[slot], ((n / kSlots) & 1) ^ 1);
+          // W2 tile (mb, kb) in kb-major order; W3 tile kb.  Tile-blocked image: [row block][k chunk][128 rows][8]
+          const size_t src = s < 16 ? kImgW2 + (size_t)((s & 3) * 64 + (s >> 2) * 16) * 2048 : kImgW3 + (size_t)((s - 16) * 16) * 2048;
+          ptx::mbar_expect_tx(&full[slot], kSlotBytes);
+          ptx::bulk_g2s(s_ring + slot * kSlotBytes, args.image + src, kSlotBytes, &full[slot]);
+        }
+      }
+    }
+    return;   // every copy issued is consumed by an MMA of this CTA before the other warps leave
   }
   if (warp == kWarpMma) ptx::tmem_alloc<C::kTmemCols>(tmem_slot);
   if (warp < kEpiWarps) {   // biases, fp32, from the master parameters; all loads of a thread in flight at once
@@ -214,8 +254,25 @@ tct_actor_kernel(const __grid_constant__ Args args) {
     if (args.mean != nullptr && c < args.in_dim) v = is_mean ? (float)args.mean[c] : __fadd_rn(sqrtf((float)args.var[c]), 1e-8f);
     s_scale[lane] = v;
   }
+  float x_aux[kRowsPerLane][8];      // auxiliary warp: raw observations of its next tile
+  auto load_x = [&](int tile) {
+#pragma unroll
+    for (int h = 0; h < kRowsPerLane; ++h) {
+      const int64_t r = (int64_t)tile * NT + lane + 32 * h;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) x_aux[h][j] = (j < args.in_dim && r < args.rows) ? args.io.states[r * args.in_dim + j] : 0.f;
+    }
+  };
+  if (warp == kWarpAux) {
+    // Programmatic dependent launch: everything else in this set-up overlaps the predecessor's tail; the observations are
+    // what the predecessor (the env step) produced.  The next kernel is let go at once: it reads nothing of ours before
+    // its own wait.
+    pdl_wait();
+    if (lane == 0) pdl_trigger();
+    if ((int)blockIdx.x < num_tiles) load_x(blockIdx.x);
+  }
   ptx::tc_fence_before();
-  __syncthreads();
+  asm volatile("bar.sync 1, 576;" ::: "memory");      // all warps but the two producers
   ptx::tc_fence_after();
   const uint32_t tmem = *tmem_slot;
   TCT_STAMP(tr && warp == 0, 1);
@@ -224,32 +281,7 @@ tct_actor_kernel(const __grid_constant__ Args args) {
     return;
   }
 
-  if (warp == kWarpProd || warp == kWarpProd + 1) {
-    // ===================================================== producers: one 32 KB weight tile per ring slot, the two threads
-    // alternate (a thread sustains about one bulk copy per 520 cycles whatever its size: profiles/mma_rate.cu).  The
-    // image is older than the previous kernel in the stream (the update's last kernel never triggers its dependents
-    // early, agent.cu), so the stream starts before griddepcontrol.wait.
-    if (lane == 0) {
-      const int p = warp - kWarpProd;
-      if (p == 0) {
-        ptx::mbar_expect_tx(wconst_full, kH0 * kInPad * 2 + kOutPad * kH2 * 2);
-        ptx::bulk_g2s(s_w1, args.image + kImgW1, kH0 * kInPad * 2, wconst_full);
-        ptx::bulk_g2s(s_w4, args.image + kImgW4, kOutPad * kH2 * 2, wconst_full);
-      }
-      uint32_t n = 0;
-      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
-        for (int s = 0; s < kStagesPerTile; ++s, ++n) {
-          if ((int)(n & 1) != p) continue;
-          const int slot = n % kSlots;
-          wait(&empty[slot], ((n / kSlots) & 1) ^ 1);
-          // W2 tile (mb, kb) in kb-major order; W3 tile kb.  Tile-blocked image: [row block][k chunk][128 rows][8]
-          const size_t src = s < 16 ? kImgW2 + (size_t)((s & 3) * 64 + (s >> 2) * 16) * 2048 : kImgW3 + (size_t)((s - 16) * 16) * 2048;
-          ptx::mbar_expect_tx(&full[slot], kSlotBytes);
-          ptx::bulk_g2s(s_ring + slot * kSlotBytes, args.image + src, kSlotBytes, &full[slot]);
-        }
-      }
-    }
-  } else if (warp == kWarpMma) {
+  if (warp == kWarpMma) {
     // ===================================================== MMA issuer
     const bool leader = ptx::elect_one();
     const uint32_t id_k = ptx::idesc_bf16(128, NT);                 // A, B K-major (layer 1: B = X)
@@ -338,20 +370,10 @@ tct_actor_kernel(const __grid_constant__ Args args) {
     // ===================================================== auxiliary warp: observations -> X operand, then the tile's OU noise
     const int A = args.out_dim;
     const bool row_noise = args.io.ou_state != nullptr && (A == 1 || A == 2 || A == 4);
-    // Programmatic dependent launch: everything above overlapped the predecessor's tail; the observations are what the
-    // predecessor (the env step) produced.  The next kernel is let go at once: it reads nothing of ours before its own wait.
-    pdl_wait();
-    if (lane == 0) pdl_trigger();
+    auto& x = x_aux;
     uint32_t tiles_done = 0;
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++tiles_done) {
       const uint32_t par = tiles_done & 1;
-      float x[kRowsPerLane][8];
-#pragma unroll
-      for (int h = 0; h < kRowsPerLane; ++h) {
-        const int64_t r = (int64_t)tile * NT + lane + 32 * h;
-#pragma unroll
-        for (int j = 0; j < 8; ++j) x[h][j] = (j < args.in_dim && r < args.rows) ? args.io.states[r * args.in_dim + j] : 0.f;
-      }
       if (tiles_done > 0) wait(&d1_full[3], par ^ 1);          // the previous tile's layer 1 has read X
 #pragma unroll
       for (int h = 0; h < kRowsPerLane; ++h) {
@@ -382,7 +404,8 @@ tct_actor_kernel(const __grid_constant__ Args args) {
         }
       }
       __syncwarp();
-      if (lane == 0) ptx::mbar_arrive(noise_ready);
+      if (lane == 0) ptx::mbar_arrive(&noise_ready[par]);
+      if (tile + (int)gridDim.x < num_tiles) load_x(tile + gridDim.x);   // in flight while this tile's MLP runs
     }
   } else {
     // ===================================================== epilogue warps: group g = feature block, quadrant = TMEM lane group
@@ -465,7 +488,7 @@ tct_actor_kernel(const __grid_constant__ Args args) {
           }
         }
         __syncwarp();
-        wait(noise_ready, par);
+        wait(&noise_ready[par], (tiles_done >> 1) & 1);
         const float* b4 = s_bias + kH0 + kH1 + kH2;
         const float* sn = s_noise + par * (NT * 4);
         const bool applied = act_noise_scale(args.io) >= 0.f;
@@ -520,9 +543,9 @@ tct_actor_kernel(const __grid_constant__ Args args) {
       warp_arrive(tile_done);
     }
   }
-  // ---- teardown
+  // ---- teardown (the producers have left; their last copy was consumed by the last layer-3 MMA)
   ptx::tc_fence_before();
-  __syncthreads();
+  asm volatile("bar.sync 1, 576;" ::: "memory");
   if (warp == kWarpMma) ptx::tmem_dealloc<C::kTmemCols>(tmem);
   if (lane == 0) {     // diagnostics: every warp's exit time
     unsigned long long t;
@@ -547,6 +570,8 @@ static cudaError_t launch(const tct::Args& args, int64_t rows, cudaStream_t s) {
   return launch_pdl(tct_actor_kernel<NT>, tiles < sms ? tiles : sms, kThreads, Cfg<NT>::kSmemBytes, s, args);
 }
 
+static long long g_tct_launches = 0;     // diagnostics: launches of the transposed kernel (tests check which kernel served a call)
+
 int tct_actor_forward(OisAgent* a, const uint8_t* image, const float* actor_params, const OisScaler* scaler, const OisActIO* io,
                       int64_t rows, cudaStream_t s) {
   using namespace tct;
@@ -569,12 +594,14 @@ int tct_actor_forward(OisAgent* a, const uint8_t* image, const float* actor_para
   static const int force_nt = getenv("OIS_TCT_NT") ? atoi(getenv("OIS_TCT_NT")) : 0;
   const bool nt32 = force_nt ? force_nt == 32 : (rows + 31) / 32 <= num_sms();
   OIS_CHECK_CUDA(nt32 ? launch<32>(args, rows, s) : launch<64>(args, rows, s));
+  ++g_tct_launches;
   return OIS_OK;
 }
 
 }  // namespace ois
 
 // diagnostics hook for profiles/tct_trace.py (deliberately not declared in include/ois_b200.h)
+extern "C" long long ois_debug_tct_launches() { return ois::g_tct_launches; }
 extern "C" int ois_debug_tct_trace_reset() {
   unsigned long long z[64] = {};
   z[60] = ~0ull;

@@ -33,6 +33,7 @@ names = {0: "start", 1: "setup done", 2: "aux: X written", 3: "MMA: x_ready", **
          16: "epi: d2_full seen", **{17 + g: f"epi: H2 block {g} written" for g in range(4)}, 21: "epi: d3_full seen",
          22: "epi: d4_full seen", 23: "done (actions stored)"}
 lib = ois.lib()
+lib.ois_debug_set_tct_max_rows.argtypes = [C.c_longlong]
 for mode in ("warm", "cold"):
     for it in range(3):
         if mode == "cold":
@@ -49,7 +50,7 @@ for mode in ("warm", "cold"):
         print(f"{(buf[k] - t0) / 1e3:8.2f} us  {names[k]}")
     print(f"all CTAs: first start {(buf[60] - t0) / 1e3:.2f} us, last start {(buf[62] - t0) / 1e3:.2f} us, last end {(buf[61] - t0) / 1e3:.2f} us "
           f"(launch span {(buf[61] - buf[60]) / 1e3:.2f} us)")
-for label, max_rows in (("transposed 64-env tiles (mlp_tct.cu)", 1 << 40), ("128-env row tiles (mlp_tc.cu)", 0)):
+for label, max_rows in (("transposed 64-env tiles (mlp_tct.cu)", 1 << 30), ("128-env row tiles (mlp_tc.cu)", 0)):
     lib.ois_debug_set_tct_max_rows(max_rows)
     for cold in (False, True):
         ts = []

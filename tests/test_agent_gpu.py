@@ -184,30 +184,40 @@ def test_checkpoint_roundtrip_and_reference_format(tmp_path):
 
 def test_bf16_actor_inference_within_stated_tolerance():
     """Both tcgen05 actor kernels against the fp32 oracle: the transposed 64-env-tile kernel (csrc/mlp_tct.cu, the
-    default up to 32 768 rows) and the 128-env-row-tile kernel (csrc/mlp_tc.cu), selected through the row threshold."""
+    default while its 64-env tiles fit one wave of the SMs) and the 128-env-row-tile kernel (csrc/mlp_tc.cu), selected through the row threshold."""
     import torch
+
+    import ctypes
 
     import options_in_simulation_b200 as ois
 
+    lib = ois.lib()
+    lib.ois_debug_set_tct_max_rows.argtypes = [ctypes.c_longlong]
+    lib.ois_debug_tct_launches.restype = ctypes.c_longlong
     _, meta = load("agent_kamma_4d.npz")
     outs = {}
     try:
-        for max_rows in (1 << 40, 0):
-            ois.lib().ois_debug_set_tct_max_rows(max_rows)
-            agent, _ = build_agent(meta, mixed_precision=True)
+        for max_rows in (1 << 30, 0):
+            lib.ois_debug_set_tct_max_rows(max_rows)
+            # batch_size 512: the transposed kernel reads the update's weight image, which exists for batches that are a
+            # multiple of 128 (csrc/update_tc.cu); the launch counter below proves which kernel served each call
+            agent, _ = build_agent(meta, mixed_precision=True, batch_size=512)
             o = make_oracle(meta)
             g = torch.Generator().manual_seed(5)
-            for n in (4096, 1, 63, 64, 65, 100, 64 * 148 + 77, 128 * 148 + 77):
+            # 32-env tiles up to 32 * 148 rows (one wave), 64-env tiles beyond; several tiles per CTA from 64 * 148 rows on
+            for n in (4096, 1, 31, 32, 33, 63, 64, 65, 100, 32 * 148, 32 * 148 + 1, 64 * 148 + 77, 128 * 148 + 77, 32768):
                 states = torch.randn(n, 6, generator=g) * 2
                 z = torch.randn(n, 4, generator=g)
                 agent.supply_draws(normals=z.numpy())
+                before = lib.ois_debug_tct_launches()
                 a = agent.act(states.cuda(), 300, 1000)[0].cpu().numpy()
+                assert lib.ois_debug_tct_launches() - before == (1 if max_rows else 0), (max_rows, n)
                 ao = o.act(states, 300, 1000, normals=z).numpy()
                 err = np.abs(a - ao)
                 assert err.max() <= BF16_ATOL, (max_rows, n, err.max())
                 assert err.mean() <= 3e-3
                 outs[(max_rows, n)] = a
         for n in (4096, 100, 64 * 148 + 77):     # the two kernels agree with each other at least as closely
-            assert np.abs(outs[(1 << 40, n)] - outs[(0, n)]).max() <= BF16_ATOL
+            assert np.abs(outs[(1 << 30, n)] - outs[(0, n)]).max() <= BF16_ATOL
     finally:
-        ois.lib().ois_debug_set_tct_max_rows(-1)
+        lib.ois_debug_set_tct_max_rows(-1)

@@ -196,6 +196,30 @@ int ois_replay_gather(const float* mem_states, const float* mem_actions, const f
 int ois_replay_sample_indices(int64_t* idx, int64_t batch, int64_t len, uint64_t philox_seed,
                               uint64_t philox_offset, void* stream);
 
+/* Device-resident scalars of a CUDA-graph-captured DDPG._update: what changes from one update to the next.  The host
+ * writes the block (plain host->device copy) when its mirrors move for another reason (the memory grew, an eager
+ * sample was drawn, a checkpoint was loaded); ois_replay_sample_gather advances it once per launch. */
+typedef struct OisSampleCtl {
+  int64_t len;         /* len(memory): transitions to sample from (Memory.__len__) */
+  uint64_t draws;      /* philox_offset of the next ois_replay_sample_indices-equivalent draw */
+  int64_t adam_step;   /* optimizer steps completed; after the launch: the 1-based step of the update it feeds
+                          (point OisUpdateIO.adam_step_dev here) */
+  uint32_t ticket;     /* CTAs of the running launch that have finished; 0 between launches */
+  uint32_t pad_;
+} OisSampleCtl;
+
+/* ctl := (len, draws, adam_step, ticket 0), stream-ordered (one single-thread launch; the values are launch arguments). */
+int ois_sample_ctl_set(OisSampleCtl* ctl, int64_t len, uint64_t draws, int64_t adam_step, void* stream);
+
+/* ois_replay_sample_indices(len = ctl->len, offset = ctl->draws) and ois_replay_gather of those indices in ONE launch
+ * (Memory.sample, train/train_kaddpg_1d_nofifo_random_RLIL.py:130-160); idx also receives the indices; the last CTA
+ * advances ctl (draws + 1, adam_step + 1).  Precondition: batch <= ctl->len. */
+int ois_replay_sample_gather(const float* mem_states, const float* mem_actions, const float* mem_rewards,
+                             const float* mem_next_states, const uint8_t* mem_terminated, const uint8_t* mem_truncated,
+                             int64_t* idx, int64_t batch, int32_t obs_dim, int32_t act_dim, float* out_states,
+                             float* out_actions, float* out_rewards, float* out_next_states, uint8_t* out_terminated,
+                             uint8_t* out_truncated, uint64_t philox_seed, OisSampleCtl* ctl, void* stream);
+
 /* ------------------------------------------------------------------------------------------------
  * Agent: DDPG (src/my_agents/ddpg.py) with the models of train/train_kamma_4d_nofifo_random_RLIL.py:21-52
  * ---------------------------------------------------------------------------------------------- */
@@ -339,7 +363,7 @@ const char* ois_last_error_string(void);
 int ois_abi_version(void);
 /* sizeof() of the ABI structs as this library was compiled, so a foreign-language mirror (ctypes, cgo ...)
  * can verify its layout: 0 OisEnvParams, 1 OisEnvState, 2 OisEnvIO, 3 OisMlpShape, 4 OisScaler, 5 OisActIO,
- * 6 OisUpdateIO, 7 OisStepCtl; -1 for an unknown index. */
+ * 6 OisUpdateIO, 7 OisStepCtl, 8 OisSampleCtl; -1 for an unknown index. */
 int ois_struct_size(int which);
 /* name of the SASS feature set compiled in, e.g. "sm_100a tcgen05+tma" */
 const char* ois_build_info(void);

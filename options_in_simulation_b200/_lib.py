@@ -66,6 +66,11 @@ class StepCtl(C.Structure):
                 ("self_advance", _i32), ("ticket", C.c_uint32)]
 
 
+class SampleCtl(C.Structure):
+    """OisSampleCtl: per-update scalars kept on the device for CUDA-graph replay of DDPG._update."""
+    _fields_ = [("len", _i64), ("draws", _u64), ("adam_step", _i64), ("ticket", C.c_uint32), ("pad_", C.c_uint32)]
+
+
 class MlpShape(C.Structure):
     _fields_ = [(n, _i32) for n in ("in_dim", "h0", "h1", "h2", "out_dim", "out_act")]
 
@@ -101,6 +106,8 @@ SYMBOLS = {
     "ois_replay_append": (C.c_int, [_p] * 6 + [_i64, _i64, _i32, _i32] + [_p] * 6 + [_p]),
     "ois_replay_gather": (C.c_int, [_p] * 6 + [_p, _i64, _i64, _i32, _i32] + [_p] * 6 + [_p]),
     "ois_replay_sample_indices": (C.c_int, [_p, _i64, _i64, _u64, _u64, _p]),
+    "ois_sample_ctl_set": (C.c_int, [_p, _i64, _u64, _i64, _p]),
+    "ois_replay_sample_gather": (C.c_int, [_p] * 6 + [_p, _i64, _i32, _i32] + [_p] * 6 + [_u64, _p, _p]),
     "ois_agent_create": (C.c_int, [_PP(_p), _PP(MlpShape), _PP(MlpShape), _i64, _i32, _i32, _p]),
     "ois_agent_destroy": (C.c_int, [_p]),
     "ois_agent_invalidate": (C.c_int, [_p]),

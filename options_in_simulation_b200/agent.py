@@ -664,9 +664,10 @@ class DDPG:
             self.track_data("Target / Target (mean)", st[7])
 
     def _update_graphed(self):
-        """One update as ONE CUDA-graph launch: the sampled indices land in a fixed buffer (the Philox sampler runs
-        outside the graph: its offset and the memory length change per call), the graph holds the gather and the
-        three phases; the Adam step count lives on the device (OisUpdateIO.adam_step_dev)."""
+        """One update as ONE CUDA-graph launch and nothing else: the first node draws the batch indices and gathers the
+        rows (ois_replay_sample_gather), the rest are the three phases.  What changes from update to update — memory
+        length, draw counter, Adam step count — lives in a device-resident OisSampleCtl that the first node advances;
+        the host re-seeds it (one single-thread launch) only when its mirrors moved for another reason."""
         lib, m = L.lib(), self.memory
         if m.sampler != "device" or m._supplied_indexes:
             raise L.OisError("graph_update needs sampler='device' and no supplied indexes")
@@ -677,42 +678,56 @@ class DDPG:
         nets = (self.critic, self.policy, None)
         if self._graph is None:
             idx = torch.empty(self._batch_size, dtype=torch.int64, device=self.device)
-            self._step_dev = torch.tensor([self.critic_optimizer.step], dtype=torch.int64, device=self.device)
-            m.draw_indices(idx)
-            batch = m.sample_by_index(self._tensors_names, idx)[0]      # allocates the batch buffers once, eagerly
+            # OisSampleCtl (len, draws, adam_step, ticket) on the device: the sampler / gather launch inside the graph
+            # reads it and advances it, so a steady-state update is ONE graph launch and nothing else
+            self._sample_ctl = torch.zeros(4, dtype=torch.int64, device=self.device)
+            self._push_sample_ctl()
+            batch = m.sample_gather(self._tensors_names, idx, self._sample_ctl)[0]   # allocates the batch buffers once
             io = self._update_io(batch)
-            io.adam_step_dev = self._step_dev.data_ptr()
+            io.adam_step_dev = self._sample_ctl.data_ptr() + 16
             # this call's update runs eagerly (it also leaves the weight images in their steady state); the same
             # sequence is then captured — capture records, it does not execute — for every later call
-            self._step_dev.add_(1)
             for ph in range(3):
                 L.check(lib.ois_ddpg_update_phase(self._handle, self._scaler_ref(), C.byref(io), ph, scale, L.current_stream()))
                 if ph < 2:
                     self._reduce(nets[ph], grads[ph])
             torch.cuda.synchronize()
             graph = torch.cuda.CUDAGraph()
+            draws, launches = m._draws, m.kernel_launches
             # "thread_local": the NCCL watchdog thread may query events while this thread captures (dp_exchange "nccl")
             with torch.cuda.graph(graph, capture_error_mode="thread_local"):
-                self._step_dev.add_(1)
-                m.sample_by_index(self._tensors_names, idx)
+                m.sample_gather(self._tensors_names, idx, self._sample_ctl)
                 for ph in range(3):
                     L.check(lib.ois_ddpg_update_phase(self._handle, self._scaler_ref(), C.byref(io), ph, scale, L.current_stream()))
                     if ph < 2:
                         self._reduce(nets[ph], grads[ph])
+            m._draws, m.kernel_launches = draws, launches      # the capture recorded a launch, it did not draw
             self._graph = (graph, idx, io, batch)
         else:
             graph, idx = self._graph[0], self._graph[1]
-            m.draw_indices(idx)
+            if (len(m), m._draws, self.critic_optimizer.step) != self._sample_ctl_mirror:
+                self._push_sample_ctl()      # the memory grew, or somebody else drew / stepped since the last replay
             graph.replay()
+            m._draws += 1
+            m.kernel_launches += 1
+            m.sampling_indexes = idx
+        self._sample_ctl_mirror = (len(m), m._draws, self.critic_optimizer.step + 1)
         n = 1
         self.policy_optimizer.step += n
         self.critic_optimizer.step += n
         self._updates += n
-        self.kernel_launches += n * (2 + UPDATE_LAUNCHES_BF16 if self._mixed_precision else 2 + UPDATE_LAUNCHES)
+        self.kernel_launches += n * (UPDATE_LAUNCHES_BF16 if self._mixed_precision else UPDATE_LAUNCHES)   # + the memory's one
         # host-side "weights changed" flags of the library are not touched by a replay: the actor's inference image
         # must be rebuilt by the next act()
         L.check(lib.ois_agent_invalidate(self._handle))
         return n
+
+    def _push_sample_ctl(self):
+        """Device OisSampleCtl := the host mirrors (memory length, draw counter, optimizer steps completed)."""
+        m = self.memory
+        L.check(L.lib().ois_sample_ctl_set(self._sample_ctl.data_ptr(), len(m), m._draws, self.critic_optimizer.step,
+                                           L.current_stream()))
+        self.kernel_launches += 1
 
     def _update(self, timestep, timesteps):
         """ddpg.py:357-465: three C-ABI phases split where skrl all-reduces gradients."""

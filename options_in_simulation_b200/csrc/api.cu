@@ -26,6 +26,7 @@ extern "C" int ois_struct_size(int which) {
     case 5: return (int)sizeof(OisActIO);
     case 6: return (int)sizeof(OisUpdateIO);
     case 7: return (int)sizeof(OisStepCtl);
+    case 8: return (int)sizeof(OisSampleCtl);
     default: return -1;
   }
 }

@@ -83,8 +83,93 @@ __global__ void replay_sample_kernel(int64_t* __restrict__ idx, int64_t batch, i
   idx[b] = (int64_t)x;
 }
 
+// Sampler and gather in ONE launch, with everything that changes from one update to the next read from (and advanced in)
+// a device-resident OisSampleCtl — so a captured CUDA graph of DDPG._update needs no launch outside the graph.  The
+// indices are the ones replay_sample_kernel draws for (len, seed, draws); they are also stored to idx (Memory's
+// sampling_indexes).  The last CTA to finish moves the block to the next update.
+__global__ void __launch_bounds__(kThreads)
+replay_sample_gather_kernel(const float* __restrict__ ms, const float* __restrict__ ma, const float* __restrict__ mr,
+                            const float* __restrict__ mn, const uint8_t* __restrict__ mt, const uint8_t* __restrict__ mu,
+                            int64_t* __restrict__ idx, int64_t batch, int obs_dim, int act_dim, float* __restrict__ os,
+                            float* __restrict__ oa, float* __restrict__ orw, float* __restrict__ on, uint8_t* __restrict__ ot,
+                            uint8_t* __restrict__ ou, uint64_t seed, OisSampleCtl* __restrict__ ctl) {
+  pdl_wait();
+  if (threadIdx.x == 0) pdl_trigger();
+  const int64_t len = ctl->len;
+  const uint64_t draws = ctl->draws;
+  int bits = 2;
+  while ((1ull << bits) < (uint64_t)len) bits += 2;
+  const uint4 k4 = Philox(seed)(draws, 0x5eedull);
+  const uint32_t key[4] = {k4.x, k4.y, k4.z, k4.w};
+  const int lane = threadIdx.x & 15;
+  const int64_t group = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 4;
+  const int64_t ngroups = ((int64_t)gridDim.x * blockDim.x) >> 4;
+  for (int64_t b = group; b < batch; b += ngroups) {
+    uint64_t x = (uint64_t)b;
+    do { x = feistel(x, bits / 2, key); } while (x >= (uint64_t)len);
+    const int64_t j = (int64_t)x;
+    if (lane == 0) idx[b] = j;
+    for (int k = lane; k < obs_dim; k += 16) {
+      os[b * obs_dim + k] = ms[j * obs_dim + k];
+      on[b * obs_dim + k] = mn[j * obs_dim + k];
+    }
+    for (int k = lane; k < act_dim; k += 16) oa[b * act_dim + k] = ma[j * act_dim + k];
+    if (lane == 15) {
+      orw[b] = mr[j];
+      ot[b] = mt[j];
+      ou[b] = mu[j];
+    }
+  }
+  __syncthreads();      // every thread of this CTA has read the block
+  if (threadIdx.x == 0) {
+    __threadfence();
+    if (atomicAdd(&ctl->ticket, 1u) == gridDim.x - 1) {
+      ctl->ticket = 0;
+      ctl->draws = draws + 1;
+      ctl->adam_step += 1;
+    }
+  }
+}
+
 }  // namespace ois
 using namespace ois;
+
+namespace ois {
+__global__ void sample_ctl_set_kernel(OisSampleCtl* ctl, int64_t len, uint64_t draws, int64_t adam_step) {
+  ctl->len = len;
+  ctl->draws = draws;
+  ctl->adam_step = adam_step;
+  ctl->ticket = 0;
+}
+}  // namespace ois
+
+// Values travel as kernel arguments (captured at launch), so the host may call this again before the first call has
+// executed; a plain stream-ordered predecessor of the next ois_replay_sample_gather.
+extern "C" int ois_sample_ctl_set(OisSampleCtl* ctl, int64_t len, uint64_t draws, int64_t adam_step, void* stream) {
+  OIS_CHECK_ARG(ctl && len >= 0 && adam_step >= 0, "bad arguments");
+  sample_ctl_set_kernel<<<1, 1, 0, (cudaStream_t)stream>>>(ctl, len, draws, adam_step);
+  OIS_CHECK_LAUNCH();
+  return OIS_OK;
+}
+
+extern "C" int ois_replay_sample_gather(const float* mem_states, const float* mem_actions, const float* mem_rewards,
+                                        const float* mem_next_states, const uint8_t* mem_terminated,
+                                        const uint8_t* mem_truncated, int64_t* idx, int64_t batch, int32_t obs_dim,
+                                        int32_t act_dim, float* out_states, float* out_actions, float* out_rewards,
+                                        float* out_next_states, uint8_t* out_terminated, uint8_t* out_truncated,
+                                        uint64_t philox_seed, OisSampleCtl* ctl, void* stream) {
+  OIS_CHECK_ARG(mem_states && mem_actions && mem_rewards && mem_next_states && mem_terminated && mem_truncated,
+                "null memory tensor");
+  OIS_CHECK_ARG(out_states && out_actions && out_rewards && out_next_states && out_terminated && out_truncated && idx && ctl,
+                "null output tensor / control block");
+  OIS_CHECK_ARG(batch > 0 && obs_dim > 0 && act_dim > 0, "bad sizes");
+  int64_t blocks = (batch * 16 + kThreads - 1) / kThreads;
+  if (blocks > (int64_t)num_sms() * 8) blocks = (int64_t)num_sms() * 8;
+  OIS_CHECK_CUDA(launch_pdl(replay_sample_gather_kernel, (int)blocks, kThreads, 0, (cudaStream_t)stream, mem_states, mem_actions,
+                            mem_rewards, mem_next_states, mem_terminated, mem_truncated, idx, batch, (int)obs_dim, (int)act_dim,
+                            out_states, out_actions, out_rewards, out_next_states, out_terminated, out_truncated, philox_seed, ctl));
+  return OIS_OK;
+}
 
 extern "C" int ois_replay_append(float* mem_states, float* mem_actions, float* mem_rewards, float* mem_next_states,
                                  uint8_t* mem_terminated, uint8_t* mem_truncated, int64_t memory_index, int64_t n_envs,

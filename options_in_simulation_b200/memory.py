@@ -117,6 +117,21 @@ class Memory:
         self.kernel_launches += 1
         self.sampling_indexes = idx
 
+    def sample_gather(self, names, idx: torch.Tensor, ctl: torch.Tensor):
+        """Sampler and gather as ONE launch driven by a device-resident OisSampleCtl (`ctl`: the struct as four int64
+        words): what a CUDA-graph-captured DDPG._update replays.  The draw counter advances on the device; the host
+        mirror follows arithmetically."""
+        out = self._alloc_out(idx.numel())
+        T = self.tensors
+        L.check(L.lib().ois_replay_sample_gather(
+            *[L.ptr(T[n]) for n in _NAMES], L.ptr(idx), idx.numel(), T["states"].shape[2], T["actions"].shape[2],
+            *[L.ptr(o) for o in out], self._seed, L.ptr(ctl), L.current_stream()))
+        self._draws += 1
+        self.kernel_launches += 1
+        self.sampling_indexes = idx
+        by_name = dict(zip(_NAMES, out))
+        return [[by_name[n] for n in names]]
+
     def sample(self, names, batch_size: int, mini_batches: int = 1, sequence_length: int = 1):
         size = len(self)
         if self._supplied_indexes:

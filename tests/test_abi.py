@@ -32,7 +32,7 @@ def test_struct_sizes_match_c_layout(built_lib):
     """ctypes mirrors vs the compiler's layout (ois_struct_size is part of the ABI for exactly this)."""
     from options_in_simulation_b200 import _lib as L
 
-    for idx, cls in enumerate((L.EnvParams, L.EnvState, L.EnvIO, L.MlpShape, L.Scaler, L.ActIO, L.UpdateIO, L.StepCtl)):
+    for idx, cls in enumerate((L.EnvParams, L.EnvState, L.EnvIO, L.MlpShape, L.Scaler, L.ActIO, L.UpdateIO, L.StepCtl, L.SampleCtl)):
         assert built_lib.ois_struct_size(idx) == ctypes.sizeof(cls), cls.__name__
 
 

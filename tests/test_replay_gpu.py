@@ -144,3 +144,41 @@ def test_fused_append_equals_record_transition_path():
             assert torch.equal(a, b), k
         else:
             assert torch.equal(a.view(torch.int32), b.view(torch.int32)), k
+
+
+def test_sample_gather_matches_the_two_launch_path_and_advances_its_control_block():
+    """ois_replay_sample_gather (what a graph-captured update replays) draws the indices ois_replay_sample_indices draws
+    for the same (len, seed, offset), gathers the same rows, and moves the device-resident OisSampleCtl on."""
+    import torch
+
+    import options_in_simulation_b200 as ois
+    from options_in_simulation_b200 import _lib as L
+
+    n, size = 96, 40
+    m = ois.RandomMemory(memory_size=size, num_envs=n, device="cuda:0", replacement=False, sampler="device", seed=5)
+    names = ("states", "actions", "rewards", "next_states", "terminated", "truncated")
+    for name, d, dt in (("states", 6, torch.float32), ("next_states", 6, torch.float32), ("actions", 4, torch.float32),
+                        ("rewards", 1, torch.float32), ("terminated", 1, torch.bool), ("truncated", 1, torch.bool)):
+        m.create_tensor(name, d, dt)
+    g = torch.Generator(device="cuda").manual_seed(1)
+    for name in ("states", "next_states", "actions", "rewards"):
+        m.tensors[name].copy_(torch.randn(m.tensors[name].shape, device="cuda", generator=g))
+    m.tensors["terminated"].copy_(torch.rand(size, n, 1, device="cuda", generator=g) < 0.1)
+    m.memory_index, m.filled = 17, False          # 17 * 96 transitions to sample from
+    length, batch = len(m), 512
+    ctl = torch.zeros(4, dtype=torch.int64, device="cuda")
+    for draw0, step0 in ((0, 0), (41, 1000)):
+        L.check(ois.lib().ois_sample_ctl_set(ctl.data_ptr(), length, draw0, step0, None))
+        m._draws = draw0
+        for k in range(3):
+            idx = torch.empty(batch, dtype=torch.int64, device="cuda")
+            got = [t.clone() for t in m.sample_gather(names, idx, ctl)[0]]
+            ref_idx = torch.empty(batch, dtype=torch.int64, device="cuda")
+            L.check(ois.lib().ois_replay_sample_indices(ref_idx.data_ptr(), batch, length, m._seed, draw0 + k, None))
+            assert torch.equal(idx, ref_idx) and idx.unique().numel() == batch and int(idx.max()) < length
+            want = m.sample_by_index(names, ref_idx)[0]
+            for a, b in zip(got, want):
+                assert torch.equal(a, b)
+            torch.cuda.synchronize()
+            assert ctl.tolist()[:3] == [length, draw0 + k + 1, step0 + k + 1] and ctl.tolist()[3] == 0
+        assert m._draws == draw0 + 3

@@ -612,6 +612,134 @@ tcu_batch_prep_kernel(const float* __restrict__ states, const float* __restrict_
   }
 }
 
+// The same batch preparation with every thread's rows held in registers (B <= 256 RPT rows, D <= 8, A <= 8): each row is
+// read from global memory ONCE, the two reduction passes and the standardisation run from registers, and the thread packs
+// the bf16 network inputs of its own rows — no second and third sweep over global memory, no store-then-reload of the
+// scaled states.  Summation order, merge and rounding are exactly tcu_batch_prep_kernel's (rows strided by 256 per
+// thread in increasing order, xor-shuffle tree, warp totals in warp order), so the statistics stay bit-identical.
+template <int RPT>
+__global__ void __launch_bounds__(512)
+tcu_batch_prep_reg_kernel(const float* __restrict__ states, const float* __restrict__ next_states,
+                          const float* __restrict__ actions, float* __restrict__ sn, float* __restrict__ s2n, int B, int D, int A,
+                          double* __restrict__ mean, double* __restrict__ var, double* __restrict__ count,
+                          uint8_t* __restrict__ x_critic, uint8_t* __restrict__ x_scratch, uint8_t* __restrict__ x_policy) {
+  __shared__ double s_sum[2][8][8];
+  __shared__ double s_bmean[2][8];
+  __shared__ float s_mu[2][8], s_sd[2][8];
+  pdl_wait();
+  if (threadIdx.x == 0) pdl_trigger();
+  const int t = threadIdx.x, half = t >> 8, tt = t & 255, lane = t & 31, wp = tt >> 5;
+  const float* __restrict__ x = half ? next_states : states;
+  float* __restrict__ y = half ? s2n : sn;
+  float v[RPT][8], act[RPT][8];
+#pragma unroll
+  for (int k = 0; k < RPT; ++k) {
+    const int r = tt + 256 * k;
+#pragma unroll
+    for (int c = 0; c < 8; ++c) {
+      v[k][c] = (r < B && c < D) ? x[(size_t)r * D + c] : 0.f;
+      act[k][c] = (half == 0 && r < B && c < A) ? actions[(size_t)r * A + c] : 0.f;
+    }
+  }
+  if (mean) {
+    double a[8];
+#pragma unroll
+    for (int c = 0; c < 8; ++c) a[c] = 0.0;
+#pragma unroll
+    for (int k = 0; k < RPT; ++k)
+      if (tt + 256 * k < B) {
+#pragma unroll
+        for (int c = 0; c < 8; ++c) if (c < D) a[c] += (double)v[k][c];
+      }
+#pragma unroll
+    for (int c = 0; c < 8; ++c) {
+      if (c < D) {
+        for (int o = 16; o > 0; o >>= 1) a[c] += __shfl_xor_sync(0xffffffffu, a[c], o);
+        if (lane == 0) s_sum[half][wp][c] = a[c];
+      }
+    }
+    __syncthreads();
+    if (tt < D) {
+      double m = 0.0;
+      for (int w = 0; w < 8; ++w) m += s_sum[half][w][tt];
+      s_bmean[half][tt] = m / (double)B;
+    }
+    __syncthreads();
+#pragma unroll
+    for (int c = 0; c < 8; ++c) a[c] = 0.0;
+#pragma unroll
+    for (int k = 0; k < RPT; ++k)
+      if (tt + 256 * k < B) {
+#pragma unroll
+        for (int c = 0; c < 8; ++c)
+          if (c < D) { const double d = (double)v[k][c] - s_bmean[half][c]; a[c] = __fma_rn(d, d, a[c]); }
+      }
+#pragma unroll
+    for (int c = 0; c < 8; ++c) {
+      if (c < D) {
+        for (int o = 16; o > 0; o >>= 1) a[c] += __shfl_xor_sync(0xffffffffu, a[c], o);
+        if (lane == 0) s_sum[half][wp][c] = a[c];
+      }
+    }
+    __syncthreads();
+    if (t < D) {   // the two merges of skrl's _parallel_variance, in the reference's order: states, then next_states
+      double mu = mean[t], vr = var[t], cur = count[0];
+#pragma unroll
+      for (int h = 0; h < 2; ++h) {
+        double m2 = 0.0;
+        for (int w = 0; w < 8; ++w) m2 += s_sum[h][w][t];
+        const double in_mean = (double)(float)s_bmean[h][t];                  // torch.mean -> float32
+        const double in_var = (double)(float)(m2 / (double)(B - 1));           // torch.var (unbiased) -> float32
+        scaler_merge(mu, vr, cur, in_mean, in_var, B);
+        s_mu[h][t] = (float)mu;
+        s_sd[h][t] = sqrtf((float)vr);
+      }
+      mean[t] = mu;
+      var[t] = vr;
+    }
+    __syncthreads();
+    if (t == 0) count[0] += 2.0 * (double)B;   // every reader of count[0] is past the barrier above
+#pragma unroll
+    for (int k = 0; k < RPT; ++k)
+#pragma unroll
+      for (int c = 0; c < 8; ++c)
+        if (c < D) v[k][c] = fminf(fmaxf(__fdiv_rn(__fsub_rn(v[k][c], s_mu[half][c]), __fadd_rn(s_sd[half][c], 1e-8f)), -5.0f), 5.0f);
+  }
+#pragma unroll
+  for (int k = 0; k < RPT; ++k) {
+    const int r = tt + 256 * k;
+    if (r >= B) continue;
+#pragma unroll
+    for (int c = 0; c < 8; ++c) if (c < D) y[(size_t)r * D + c] = v[k][c];
+    // columns 0..15 of the row: scaled states, then (critic input only) the sampled actions, then zeros
+    uint16_t row[16], rowp[16];
+#pragma unroll
+    for (int c = 0; c < 16; ++c) {
+      float xs = 0.f, xa = 0.f;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        if (j == c) xs = c < D ? v[k][j] : xs;
+        if (j == c - D) xa = (c >= D && c < D + A) ? act[k][j] : xa;
+      }
+      rowp[c] = c < D ? tcu_bf16_bits(xs) : (uint16_t)0;
+      row[c] = c < D ? rowp[c] : c < D + A ? tcu_bf16_bits(xa) : (uint16_t)0;
+    }
+    auto pk = [](const uint16_t* q) {
+      return make_uint4((uint32_t)q[0] | ((uint32_t)q[1] << 16), (uint32_t)q[2] | ((uint32_t)q[3] << 16),
+                        (uint32_t)q[4] | ((uint32_t)q[5] << 16), (uint32_t)q[6] | ((uint32_t)q[7] << 16));
+    };
+#pragma unroll
+    for (int c8 = 0; c8 < 2; ++c8) {
+      if (half == 0) {
+        *reinterpret_cast<uint4*>(x_critic + tcu_chunk_off(r, c8, 2, 128)) = pk(row + 8 * c8);
+        *reinterpret_cast<uint4*>(x_policy + tcu_chunk_off(r, c8, 2, 128)) = pk(rowp + 8 * c8);
+      } else {
+        *reinterpret_cast<uint4*>(x_scratch + tcu_chunk_off(r, c8, 2, 128)) = pk(rowp + 8 * c8);
+      }
+    }
+  }
+}
+
 // Model.update_parameters: p_t.mul_(1 - polyak); p_t.add_(polyak * p)
 __global__ void polyak_kernel(float* __restrict__ pt, const float* __restrict__ p, int64_t n, float tau) {
   const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -881,10 +1009,19 @@ extern "C" int ois_ddpg_update_phase(OisAgent* a, const OisScaler* scaler, const
       uint8_t* x_critic = tcu_x_buffer(a, TCU_ACTS_CRITIC);
       uint8_t* x_scratch = tcu_x_buffer(a, TCU_ACTS_SCRATCH);
       uint8_t* x_policy = tcu_x_buffer(a, TCU_ACTS_POLICY);
-      OIS_CHECK_CUDA(launch_pdl(tcu_batch_prep_kernel, 1, 512, 0, s, io->states, io->next_states, io->actions, a->u_sn, a->u_s2n, B,
-                                D, A, has_scaler ? scaler->running_mean : (double*)nullptr,
-                                has_scaler ? scaler->running_variance : (double*)nullptr,
-                                has_scaler ? scaler->current_count : (double*)nullptr, x_critic, x_scratch, x_policy));
+      double* const sm = has_scaler ? scaler->running_mean : (double*)nullptr;
+      double* const sv = has_scaler ? scaler->running_variance : (double*)nullptr;
+      double* const sc = has_scaler ? scaler->current_count : (double*)nullptr;
+      static const bool prep_generic = getenv("OIS_PREP_GENERIC") != nullptr;      // diagnostics: the three-sweep kernel
+      if (!prep_generic && D <= 8 && A <= 8 && B <= 512)        // every row of a thread in registers (agent.cu above)
+        OIS_CHECK_CUDA(launch_pdl(tcu_batch_prep_reg_kernel<2>, 1, 512, 0, s, io->states, io->next_states, io->actions, a->u_sn,
+                                  a->u_s2n, B, D, A, sm, sv, sc, x_critic, x_scratch, x_policy));
+      else if (!prep_generic && D <= 8 && A <= 8 && B <= 1024)
+        OIS_CHECK_CUDA(launch_pdl(tcu_batch_prep_reg_kernel<4>, 1, 512, 0, s, io->states, io->next_states, io->actions, a->u_sn,
+                                  a->u_s2n, B, D, A, sm, sv, sc, x_critic, x_scratch, x_policy));
+      else
+        OIS_CHECK_CUDA(launch_pdl(tcu_batch_prep_kernel, 1, 512, 0, s, io->states, io->next_states, io->actions, a->u_sn, a->u_s2n,
+                                  B, D, A, sm, sv, sc, x_critic, x_scratch, x_policy));
       // ddpg.py:385-386 target actor on next_states and ddpg.py:399 critic on (states, actions) are independent: they
       // advance layer by layer in the same grouped launches; the target actions land in the scratch input's columns D..
       {

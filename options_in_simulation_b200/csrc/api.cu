@@ -43,3 +43,16 @@ extern "C" int ois_step_ctl_advance(OisStepCtl* ctl, void* stream) {
   OIS_CHECK_LAUNCH();
   return OIS_OK;
 }
+
+namespace ois {
+int& launch_budget() {
+  static int budget = -1;
+  return budget;
+}
+}  // namespace ois
+
+// diagnostics hook (deliberately not declared in include/ois_b200.h): see launch_budget() in ois_common.cuh
+extern "C" int ois_debug_launch_budget(int n) {
+  ois::launch_budget() = n;
+  return 0;
+}

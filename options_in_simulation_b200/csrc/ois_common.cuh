@@ -93,8 +93,15 @@ __device__ inline float2 normal2(uint32_t a, uint32_t b) {
 __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 __device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 
+// diagnostics (profiles/update_phases.py): remaining launches launch_pdl may still issue; < 0 = unlimited.  With a
+// budget of k only the first k launches of a sequence run, so timing k = 1, 2, ... gives every launch's share of a chain.
+int& launch_budget();
+
 template <typename... KArgs, typename... Args>
 inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream, Args... args) {
+  int& budget = launch_budget();
+  if (budget == 0) return cudaSuccess;
+  if (budget > 0) --budget;
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = grid;
   cfg.blockDim = block;

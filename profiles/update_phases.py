@@ -43,9 +43,35 @@ def timed(name, fn, reps=50):
     out[name] = round(1e3 * e0.elapsed_time(e1) / reps, 1)
 
 
-timed("empty_graph(add_)", lambda: ag._step_dev.add_(0))
-timed("gather", lambda: ag.memory.sample_by_index(ag._tensors_names, idx))
+timed("empty_graph(add_)", lambda: ag._sample_ctl.add_(0))
+
+
+def sample_gather():
+    ag.memory.sample_gather(ag._tensors_names, idx, ag._sample_ctl)
+    ag.memory._draws -= 1
+
+
+timed("sample+gather", sample_gather)
 for ph in range(3):
     timed(f"phase{ph}", lambda ph=ph: L.check(lib.ois_ddpg_update_phase(ag._handle, ag._scaler_ref(), C.byref(io), ph, 1.0, L.current_stream())))
-timed("whole", lambda: [L.check(lib.ois_ddpg_update_phase(ag._handle, ag._scaler_ref(), C.byref(io), ph, 1.0, L.current_stream())) for ph in range(3)])
+timed("phases 0-2", lambda: [L.check(lib.ois_ddpg_update_phase(ag._handle, ag._scaler_ref(), C.byref(io), ph, 1.0, L.current_stream())) for ph in range(3)])
+timed("whole update", lambda: (sample_gather(), [L.check(lib.ois_ddpg_update_phase(ag._handle, ag._scaler_ref(), C.byref(io), ph, 1.0, L.current_stream())) for ph in range(3)]))
 print(json.dumps({"precision": args.precision, "us": out}))
+# every launch's share of the chain: phase p cut off after its first k launches (launch_budget, csrc/ois_common.cuh)
+chain = {}
+for ph in range(3):
+    prev, k, shares = 0.0, 1, []
+    while k <= 20:
+        def cut(ph=ph, k=k):
+            lib.ois_debug_launch_budget(k)
+            L.check(lib.ois_ddpg_update_phase(ag._handle, ag._scaler_ref(), C.byref(io), ph, 1.0, L.current_stream()))
+            lib.ois_debug_launch_budget(-1)
+        timed("cut", cut)
+        shares.append(round(out["cut"] - prev, 1))
+        if abs(out["cut"] - out[f"phase{ph}"]) < 0.25 and k > 1 and shares[-1] < 0.3:
+            shares.pop()
+            break
+        prev = out["cut"]
+        k += 1
+    chain[f"phase{ph}"] = shares
+print(json.dumps({"us_added_by_each_launch": chain}))

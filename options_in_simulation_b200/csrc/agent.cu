@@ -632,6 +632,9 @@ tcu_batch_prep_reg_kernel(const float* __restrict__ states, const float* __restr
   const float* __restrict__ x = half ? next_states : states;
   float* __restrict__ y = half ? s2n : sn;
   float v[RPT][8], act[RPT][8];
+  // the running statistics are needed only after both reduction passes: requested now, their latency hides behind them
+  double mu_run = 0.0, vr_run = 0.0, cur_run = 0.0;
+  if (mean && t < D) { mu_run = mean[t]; vr_run = var[t]; cur_run = count[0]; }
 #pragma unroll
   for (int k = 0; k < RPT; ++k) {
     const int r = tt + 256 * k;
@@ -683,7 +686,7 @@ tcu_batch_prep_reg_kernel(const float* __restrict__ states, const float* __restr
     }
     __syncthreads();
     if (t < D) {   // the two merges of skrl's _parallel_variance, in the reference's order: states, then next_states
-      double mu = mean[t], vr = var[t], cur = count[0];
+      double mu = mu_run, vr = vr_run, cur = cur_run;
 #pragma unroll
       for (int h = 0; h < 2; ++h) {
         double m2 = 0.0;

@@ -20,7 +20,8 @@ fn.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_int, C.c_int] + [C.
 tr = lib.ois_debug_tcu_trace
 tr.argtypes = [C.c_void_p, C.c_int]
 
-for (M, N, K, tile_n, mode, name) in [(512, 512, 512, 128, 0, "fwd L2"), (512, 512, 512, 128, 2, "dgrad L2"),
+for (M, N, K, tile_n, mode, name) in [(512, 512, 512, 32, 0, "fwd L2 t32"), (512, 512, 512, 64, 0, "fwd L2 t64"), (512, 128, 512, 32, 0, "fwd L3 t32"),
+                                       (512, 512, 512, 128, 0, "fwd L2"), (512, 512, 512, 128, 2, "dgrad L2"),
                                        (512, 512, 512, 128, 3, "wgrad L2"), (512, 512, 16, 128, 0, "fwd L1"),
                                        (512, 16, 128, 16, 0, "fwd L4"), (512, 128, 512, 128, 0, "fwd L3")]:
     ks = min(K, 128)
@@ -44,7 +45,9 @@ for (M, N, K, tile_n, mode, name) in [(512, 512, 512, 128, 0, "fwd L2"), (512, 5
           f"stages {rel[3:7]} acc {rel[8]} epi {rel[9]}")
 
 # steady-state rate: 200 back-to-back programmatic-dependent launches of one GEMM
-for (M, N, K, tile_n, mode, name) in [(512, 512, 512, 128, 0, "fwd L2"), (512, 512, 512, 128, 3, "wgrad L2"), (512, 16, 128, 16, 0, "fwd L4")]:
+for (M, N, K, tile_n, mode, name) in [(512, 512, 512, 32, 0, "fwd L2 t32"), (512, 512, 512, 64, 0, "fwd L2 t64"), (512, 128, 512, 32, 0, "fwd L3 t32"),
+                                       (512, 512, 128, 32, 0, "K128 t32"),
+                                       (512, 512, 512, 128, 0, "fwd L2"), (512, 512, 512, 128, 3, "wgrad L2"), (512, 16, 128, 16, 0, "fwd L4")]:
     ks = min(K, 128)
     A, B = torch.randn(M, K), torch.randn(N, K)
     a_store, a_rb = (A.T.contiguous(), ks) if mode & 1 else (A, 128)

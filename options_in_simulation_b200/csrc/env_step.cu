@@ -301,6 +301,18 @@ __device__ __forceinline__ int64_t replay_row_base(const OisEnvIO& io, int64_t n
   return io.ctl ? io.ctl->replay_row * n : 0;
 }
 
+// Diagnostics (not part of the public ABI; profiles/tct_trace.py): %globaltimer of the earliest CTA start [0], the earliest
+// and latest return from griddepcontrol.wait [1], [2], and the latest CTA end [3] of the last launch.
+// Compiled in only with -DOIS_ENV_TRACE (make EXTRA=-DOIS_ENV_TRACE): four atomics per CTA are visible at 6000 CTAs.
+__device__ unsigned long long g_env_trace[4];
+#ifndef OIS_ENV_TRACE
+#define ENV_STAMP_MIN(k) do { } while (0)
+#define ENV_STAMP_MAX(k) do { } while (0)
+#else
+#define ENV_STAMP_MIN(k) do { if (threadIdx.x == 0) { unsigned long long t_; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_)); atomicMin(&g_env_trace[k], t_); } } while (0)
+#define ENV_STAMP_MAX(k) do { if (threadIdx.x == 0) { unsigned long long t_; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_)); atomicMax(&g_env_trace[k], t_); } } while (0)
+#endif
+
 template <bool kStats, bool kEval>
 __global__ void __launch_bounds__(kEnvThreads, kEnvMinBlocks)
 env_step_kernel(const __grid_constant__ OisEnvParams p, const __grid_constant__ OisEnvState st,
@@ -310,7 +322,24 @@ env_step_kernel(const __grid_constant__ OisEnvParams p, const __grid_constant__ 
   // was still running.  The predecessor may be another env step (tests, dynamics-only loops), so nothing is read
   // before the wait; what overlaps is the launch itself.  The next kernel (the next actor step) is let go at once: it
   // reads nothing of ours before its own wait.
+  // ... with one exception that is always safe: L2 prefetch hints for this thread's first env.  A hint moves no data
+  // into the SM, so whatever the predecessor still writes is what the loads after the wait will see (L2 is the point of
+  // coherence); it only makes those loads L2 hits when the state was last touched long ago (a cold cache, or an evicted
+  // TLB entry, is ~2 us of latency in front of a ~5 us kernel).
+  {
+    const int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (j < n) {
+      auto pf = [](const void* q) { asm volatile("prefetch.global.L2 [%0];" ::"l"(q)); };
+      pf(st.pose_vx + 4 * j); pf(st.twist_prev + 4 * j); pf(st.wheel_speed + 4 * j); pf(st.commands + 4 * j);
+      pf(st.sums_a + 4 * j); pf(st.sums_b + 4 * j); pf(st.sim_steps + j); pf(st.episode_buf + j);
+      if (kEval) { pf(st.sums_eval + 4 * j); pf(st.old_torques + 4 * j); }
+      if (io.replay_states != nullptr) pf(io.obs + 6 * j);
+    }
+  }
+  ENV_STAMP_MIN(0);
   pdl_wait();
+  ENV_STAMP_MIN(1);
+  ENV_STAMP_MAX(2);
   pdl_trigger();
   if (kStats) {
     if (threadIdx.x < OIS_EP_STATS_LEN) s_stats[threadIdx.x] = 0.f;
@@ -616,6 +645,7 @@ env_step_kernel(const __grid_constant__ OisEnvParams p, const __grid_constant__ 
     if (__syncthreads_or(any_reset_local) && threadIdx.x == 0) atomicOr(io.any_reset_flags + (env_flag_slot(io) + 1) % 3, 1);
     if (blockIdx.x == 0 && threadIdx.x == 0) io.any_reset_flags[(env_flag_slot(io) + 2) % 3] = 0;
   }
+  ENV_STAMP_MAX(3);
   // Graph replay: the last CTA to finish moves the step-control block to the next step.  Every reader of the block — the
   // actor kernel, which completed before this grid's pdl_wait returned, and all CTAs of this grid, which take their
   // ticket only after their last use of it — is done by then.
@@ -789,6 +819,14 @@ extern "C" int ois_env_step(const OisEnvParams* params, const OisEnvState* state
   else le = launch_pdl(env_step_kernel<false, false>, grid, kEnvThreads, 0, s, *params, *state, *io, n_envs, dv);
   OIS_CHECK_CUDA(le);
   return OIS_OK;
+}
+
+extern "C" int ois_debug_env_trace(unsigned long long* out_host, int reset) {
+  if (reset) {
+    const unsigned long long z[4] = {~0ull, ~0ull, 0ull, 0ull};
+    return cudaMemcpyToSymbol(ois::g_env_trace, z, sizeof(z)) == cudaSuccess ? 0 : -2;
+  }
+  return cudaMemcpyFromSymbol(out_host, ois::g_env_trace, sizeof(unsigned long long) * 4) == cudaSuccess ? 0 : -2;
 }
 
 extern "C" int ois_dynamics_step(const OisEnvParams* params, const OisEnvState* state, const float* wheel_torqs,

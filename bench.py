@@ -440,6 +440,32 @@ def kernels_back_to_back(world, reps=20):
     return b.elapsed_time(c) / reps, a.elapsed_time(b) / reps
 
 
+def actor_device_span(world, flush, reps=9):
+    """Duration of the transposed actor kernel on the device's own clock: %globaltimer of the first CTA's start to the
+    last warp's exit (diagnostic stamps of csrc/mlp_tct.cu), median over `reps` flushed steps.  An event pair around ONE
+    kernel reads ~6 us more than this (front-end latency of the two records, profiles/micro/launch_overhead.cu)."""
+    import ctypes
+
+    import options_in_simulation_b200 as ois
+
+    lib, torch = ois.lib(), world.torch
+    spans = []
+    for _ in range(reps):
+        torch.cuda.synchronize()
+        if lib.ois_debug_tct_trace_reset() != 0:
+            return None
+        flush.zero_()
+        world.step()
+        torch.cuda.synchronize()
+        buf = (ctypes.c_ulonglong * 64)()
+        lib.ois_debug_tct_trace(buf, 64)
+        if buf[61] == 0 or buf[60] == 2 ** 64 - 1:
+            return None                      # the 128-env-row-tile kernel served this size: no stamps
+        spans.append((buf[61] - buf[60]) * 1e-6)
+    spans.sort()
+    return spans[len(spans) // 2]
+
+
 def e2e_timed(world, steps, warmup):
     """Host in the loop: observations come from pinned host memory, results go back to pinned host memory."""
     torch = world.torch
@@ -859,6 +885,13 @@ def main():
                     "peak": hbm_peak, "unit": "GB/s", "traffic": tr("env"), "ms": env_ms}
         act_roof = {"kernel": "actor MLP (ois_agent_act)", "bound": "tensor", "achieved": act_flop / (act_ms * 1e-3) / 1e12,
                     "peak": tc_peak, "unit": "TFLOP/s", "traffic": tr("actor"), "ms": act_ms}
+        span = actor_device_span(world, flush)
+        if span:
+            act_roof["device_span_ms"] = span
+            act_roof["achieved_device_span"] = act_flop / (span * 1e-3) / 1e12
+            act_roof["frac_device_span"] = act_roof["achieved_device_span"] / tc_peak
+            act_roof["ms_note"] = ("ms / achieved / frac: CUDA events around the one kernel (they include ~6 us of front-end latency "
+                                   "of the two event records); *_device_span: first CTA start to last warp exit on %globaltimer")
         for r in (env_roof, act_roof):
             r["frac"] = r["achieved"] / r["peak"]
             r["peak_source"] = peak_src

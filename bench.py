@@ -755,6 +755,29 @@ def run_eval_sweep(args, wl, n, device, rank, world_size, dist):
                       "episodes": [int(x) for x in out["episodes"]], "episode_period_steps": period,
                       "all_reduce_us": reduce_us, "all_reduce_bytes": 2 * 10 * 8,
                       "note": "random-init policy: the curve is a parity artefact (tests/test_eval_sweep_gpu.py), not a control result"}}
+    # the two kernels of one eval step on their own (events between the calls, L2 flushed), as in the headline workload
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except OSError:
+        pass
+    hbm_peak, tc_peak = float(peaks.get("hbm_gbs", 6650.0)), float(peaks.get("bf16_tflops", 1590.0))
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=device)
+    act_ms, env_ms = kernel_split(world, 50, flush)
+    env_bytes = ENV_BYTES[wl["variant"]] * n            # eval: no replay append
+    roofs = [{"kernel": "env_step_kernel", "bound": "hbm", "achieved": env_bytes / (env_ms * 1e-3) / 1e9, "peak": hbm_peak,
+              "unit": "GB/s", "traffic": None, "ms": env_ms},
+             {"kernel": "actor MLP (ois_agent_act)", "bound": "tensor", "achieved": ACTOR_FLOP[wl["act_dim"]] * n / (act_ms * 1e-3) / 1e12,
+              "peak": tc_peak, "unit": "TFLOP/s", "traffic": None, "ms": act_ms}]
+    for r in roofs:
+        r["frac"] = r["achieved"] / r["peak"]
+        r["peak_source"] = "measured (MEASURED_PEAKS.json, burst)" if peaks else "fallback (B200_PROFILING.md)"
+    roofs.sort(key=lambda r: -r["ms"])
+    line["roofline"], line["roofline_other"] = roofs
+    if world_size == 1 and not args.no_extras:
+        v, k, dt = time_cpu_port(wl, n)
+        line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": host_cores(), "kind": "port",
+                                "sample": f"{k} steps x {n} envs in {dt:.1f} s (numpy env oracle + CPU-torch actor, oracle/)"}
     emit(line)
 
 

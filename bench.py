@@ -357,6 +357,14 @@ class World:
     def launches(self):
         return self.task.kernel_launches + self.agent.kernel_launches + self.memory.kernel_launches
 
+    def step_fused(self):
+        """The same step through rollout.fused_step: one kernel launch where the library can serve it."""
+        from options_in_simulation_b200.rollout import fused_step
+
+        self.obs, rew, term, _, _ = fused_step(self.env, self.agent, self.obs, self.t, self.T)
+        self.t += 1
+        return rew, term
+
     def step(self):
         """One policy step through the public API (what the trainer's loop body does, base_KA_DDPG.py:175-219)."""
         actions = self.agent.act(self.obs, self.t, self.T)[0]
@@ -366,10 +374,11 @@ class World:
         return rew, term
 
 
-def device_timed(world, steps, warmup, flush):
+def device_timed(world, steps, warmup, flush, fused=False):
     torch = world.torch
+    step = world.step_fused if fused else world.step
     for _ in range(warmup):
-        world.step()
+        step()
     ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
     torch.cuda.synchronize()
     l0 = world.launches()
@@ -377,7 +386,7 @@ def device_timed(world, steps, warmup, flush):
         if flush is not None:
             flush.zero_()
         a.record()
-        world.step()
+        step()
         b.record()
     torch.cuda.synchronize()
     return sum(a.elapsed_time(b) for a, b in ev) / steps, world.launches() - l0
@@ -569,7 +578,7 @@ def graph_device_timed(world, steps, warmup, flush):
     torch.cuda.synchronize()
     world.t = g.timestep
     world.obs = world.task.obs_clipped
-    return sum(a.elapsed_time(b) for a, b in ev) / steps
+    return sum(a.elapsed_time(b) for a, b in ev) / steps, sum(g._per_step)
 
 
 def update_timed(world, iters=30):
@@ -841,27 +850,31 @@ def main():
     barrier()
     e2e_copy_ms, _, _, _ = e2e_graph_timed(world, min(args.steps, 200), 5, mode="copy")
     barrier()
-    graph_ms = graph_device_timed(world, args.steps, 5, flush)
+    graph_ms, graph_kernels_per_step = graph_device_timed(world, args.steps, 5, flush)
+    barrier()
+    fused_ms, fused_launches = device_timed(world, args.steps, 5, flush, fused=True)
     barrier()
     host_ms = host_issue_timed(world)
     barrier()
     clocks = sampler.stop() if rank == 0 else None      # sampled across ALL the timed legs above
-    per_rank = [[ms, graph_ms, host_ms, e2e_ms]]
+    per_rank = [[ms, graph_ms, host_ms, e2e_ms, fused_ms]]
     if world_size > 1:
         mine = torch.tensor(per_rank[0], device=device, dtype=torch.float64)
         allr = [torch.empty_like(mine) for _ in range(world_size)]
         dist.all_gather(allr, mine)
         per_rank = [a.tolist() for a in allr]
-        t = torch.tensor([ms, e2e_ms, e2e_eager_ms, graph_ms, e2e_copy_ms, e2e_pipe_ms], device=device, dtype=torch.float64)
+        t = torch.tensor([ms, e2e_ms, e2e_eager_ms, graph_ms, e2e_copy_ms, e2e_pipe_ms, fused_ms], device=device, dtype=torch.float64)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        ms, e2e_ms, e2e_eager_ms, graph_ms, e2e_copy_ms, e2e_pipe_ms = t.tolist()
+        ms, e2e_ms, e2e_eager_ms, graph_ms, e2e_copy_ms, e2e_pipe_ms, fused_ms = t.tolist()
     # the same device-resident step issued two ways, both timed over EXACTLY args.steps steps, max over ranks: call by
     # call (2 launches per step from Python) and as one graph launch per step; the headline is the faster of the two
     # (with several ranks sharing a host the call-by-call loop becomes host-bound on the slowest rank)
     call_ms = ms
     issue = "call-by-call (agent.act + env.step)"
     if graph_ms < ms:
-        ms, issue, launches = graph_ms, "rollout.RolloutGraph replay (one graph launch per step)", 2 * args.steps
+        ms, issue, launches = graph_ms, "rollout.RolloutGraph replay (one graph launch per step)", graph_kernels_per_step * args.steps
+    if fused_ms < ms:
+        ms, issue, launches = fused_ms, "rollout.fused_step (agent.act + env.step + record_transition as one kernel launch)", fused_launches
     value = world_size * n * 1e3 / ms
     e2e_value = world_size * n * 1e3 / e2e_ms
     e2e_sorted = sorted(r[3] for r in per_rank)
@@ -889,10 +902,10 @@ def main():
                 "call_by_call_ms_per_step": e2e_eager_ms,
                 "call_by_call_value": world_size * n * 1e3 / e2e_eager_ms,
                 "host_cores_per_rank": len(pinned) if pinned else None},
-        "issue_paths": {"call_by_call_ms_per_step": call_ms, "graph_replay_ms_per_step": graph_ms,
+        "issue_paths": {"call_by_call_ms_per_step": call_ms, "graph_replay_ms_per_step": graph_ms, "fused_step_ms_per_step": fused_ms,
                         "host_issue_ms_per_step": max(r[2] for r in per_rank),
                         "per_rank_ms": [[round(x, 5) for x in r] for r in per_rank],
-                        "note": "max over ranks; per_rank_ms = [call-by-call, graph replay, host issue time, e2e] per rank"},
+                        "note": "max over ranks; per_rank_ms = [call-by-call, graph replay, host issue time, e2e, fused step] per rank"},
         "gpu_launches": launches, "clocks": clocks,
     }
 

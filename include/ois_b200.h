@@ -281,6 +281,16 @@ int ois_agent_sync_weights(OisAgent* agent, const float* actor_params, int64_t n
 int ois_agent_act(OisAgent* agent, const float* actor_params, const OisScaler* scaler, const OisActIO* io,
                   int64_t n_rows, void* stream);
 
+/* Rollout fusion.  Between _begin and _end (per host thread) an ois_agent_act that the one-launch policy step can serve
+ * (bf16 handle, at most 32 x SMs rows, act_dim <= 4, not the random phase) is recorded instead of launched, and the
+ * ois_env_step that follows on the same stream and consumes its `actions` buffer launches actor + env step as ONE kernel
+ * (the loop body of src/my_trainers/base_KA_DDPG.py:175-219).  Results are bit-identical to the two launches.  Any other
+ * call pattern simply launches the recorded actor first; _end launches it if nothing consumed it. */
+int ois_rollout_fuse_begin(void);
+int ois_rollout_fuse_end(void);
+/* one-launch policy steps issued by this process so far (a caller that counts kernel launches subtracts the difference) */
+int64_t ois_rollout_fused_launches(void);
+
 /* Plain MLP forward (Model.act): y[N,out] = mlp(x[N,in]); x already preprocessed. */
 int ois_mlp_forward(OisAgent* agent, const OisMlpShape* shape, const float* params, const float* x, float* y,
                     int64_t n_rows, void* stream);

@@ -113,6 +113,9 @@ SYMBOLS = {
     "ois_agent_invalidate": (C.c_int, [_p]),
     "ois_agent_act": (C.c_int, [_p, _p, _PP(Scaler), _PP(ActIO), _i64, _p]),
     "ois_agent_sync_weights": (C.c_int, [_p, _p, C.c_int64, _p]),
+    "ois_rollout_fuse_begin": (C.c_int, []),
+    "ois_rollout_fuse_end": (C.c_int, []),
+    "ois_rollout_fused_launches": (_i64, []),
     "ois_scaler_forward": (C.c_int, [_PP(Scaler), _p, _p, _i64, _i32, _i32, _p]),
     "ois_mlp_forward": (C.c_int, [_p, _PP(MlpShape), _p, _p, _p, _i64, _p]),
     "ois_ddpg_update_phase": (C.c_int, [_p, _PP(Scaler), _PP(UpdateIO), _i32, _f, _p]),

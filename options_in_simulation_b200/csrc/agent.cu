@@ -840,9 +840,59 @@ static int comm_for(const OisUpdateIO* io, int kind, const float* grad, int64_t 
   return OIS_OK;
 }
 
+// ---------------------------------------------------------------------------------------------------------------
+// Deferred actor launch (rollout fusion).  Between ois_rollout_fuse_begin and ois_rollout_fuse_end (per host thread) a
+// bf16 ois_agent_act that the fused kernel can serve is RECORDED instead of launched; the ois_env_step that follows
+// and consumes its actions launches both as one kernel (rollout_try_fuse).  Anything else launches the recorded actor
+// first, so stream order is what the caller wrote.
+// ---------------------------------------------------------------------------------------------------------------
+struct PendingAct {
+  bool armed = false, have = false, has_scaler = false;
+  OisAgent* a = nullptr;
+  const float* params = nullptr;
+  OisScaler scaler;
+  OisActIO io;
+  int64_t n = 0;
+  cudaStream_t s = nullptr;
+};
+static thread_local PendingAct g_pend;
+
+static int launch_pending() {
+  if (!g_pend.have) return OIS_OK;
+  g_pend.have = false;
+  return tc_actor_forward(g_pend.a, g_pend.params, g_pend.has_scaler ? &g_pend.scaler : nullptr, &g_pend.io, g_pend.n, g_pend.s);
+}
+
+int rollout_try_fuse(const OisEnvParams* params, const OisEnvState* state, const OisEnvIO* io, int64_t n, cudaStream_t s) {
+  if (!g_pend.have) return 0;
+  OisAgent* a = g_pend.a;
+  const bool fusable = g_pend.n == n && g_pend.s == s && io->actions == g_pend.io.actions && io->ep_stats == nullptr &&
+                       io->comp0 == nullptr && !params->eval_sums && params->act_dim == a->actor.out_dim;
+  if (!fusable) {
+    const int e = launch_pending();
+    return e ? e : 0;
+  }
+  g_pend.have = false;
+  if (int e = tc_sync_image(a, g_pend.params, n, s)) return e;
+  const int e = tct_rollout_forward(a, tcu_image_if_valid(a, TCU_ACTOR, g_pend.params), g_pend.params,
+                                    g_pend.has_scaler ? &g_pend.scaler : nullptr, &g_pend.io, params, state, io, n, s);
+  return e ? e : 1;
+}
+
 }  // namespace ois
 
 using namespace ois;
+
+extern "C" int ois_rollout_fuse_begin(void) {
+  if (int e = launch_pending()) return e;
+  g_pend.armed = true;
+  return OIS_OK;
+}
+
+extern "C" int ois_rollout_fuse_end(void) {
+  g_pend.armed = false;
+  return launch_pending();
+}
 
 // ------------------------------------------------------------------------------------------- C ABI
 extern "C" int ois_agent_create(OisAgent** out, const OisMlpShape* actor, const OisMlpShape* critic, int64_t max_rows,
@@ -965,6 +1015,18 @@ extern "C" int ois_agent_act(OisAgent* a, const float* actor_params, const OisSc
   const int A = a->actor.out_dim, D = a->actor.in_dim;
   if (!io->random_phase) {
     if (a->precision == OIS_PRECISION_BF16) {
+      if (g_pend.armed && !g_pend.have && tc_use_transposed(a, n_rows) && tct_can_fuse_env(n_rows) && A <= 4) {
+        g_pend.have = true;               // recorded: the env step that consumes these actions launches both (rollout_try_fuse)
+        g_pend.a = a;
+        g_pend.params = actor_params;
+        g_pend.has_scaler = scaler != nullptr;
+        if (scaler) g_pend.scaler = *scaler;
+        g_pend.io = *io;
+        g_pend.n = n_rows;
+        g_pend.s = s;
+        return OIS_OK;
+      }
+      if (int e = launch_pending()) return e;
       return tc_actor_forward(a, actor_params, scaler, io, n_rows, s);   // exploration fused into its epilogue
     } else {
       const float* x = io->states;

@@ -45,4 +45,15 @@ int tct_actor_forward(OisAgent* a, const uint8_t* image, const float* actor_para
 int tc_actor_forward(OisAgent* a, const float* actor_params, const OisScaler* scaler, const OisActIO* io, int64_t rows,
                      cudaStream_t s);
 
+// the fused policy step (mlp_tct.cu): the transposed actor kernel with the env step of each tile run by the CTA that
+// produced its actions; rows must satisfy tct_can_fuse_env
+bool tc_use_transposed(const OisAgent* a, int64_t rows);
+bool tct_can_fuse_env(int64_t rows);
+int tct_rollout_forward(OisAgent* a, const uint8_t* image, const float* actor_params, const OisScaler* scaler, const OisActIO* io,
+                        const OisEnvParams* ep, const OisEnvState* es, const OisEnvIO* eio, int64_t rows, cudaStream_t s);
+// Called by ois_env_step (env_step.cu): if ois_agent_act deferred an actor launch on this thread (between
+// ois_rollout_fuse_begin / _end) and this env step consumes exactly its actions, both run as ONE launch (returns 1);
+// otherwise the deferred actor launch is issued first and the caller launches the env kernel itself (returns 0).
+int rollout_try_fuse(const OisEnvParams* params, const OisEnvState* state, const OisEnvIO* io, int64_t n, cudaStream_t s);
+
 }  // namespace ois

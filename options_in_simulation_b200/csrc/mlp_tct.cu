@@ -25,6 +25,7 @@
 // Numerics: identical contract to mlp_tc.cu (bf16 operands, fp32 accumulation, fp32 bias / activation); tests compare
 // both kernels with the fp32 oracle (tests/test_agent_gpu.py).
 #include "agent.cuh"
+#include "env_one.cuh"
 #include "explore.cuh"
 #include "tc_ptx.cuh"
 #include "update_tc.cuh"
@@ -56,7 +57,7 @@ struct Cfg {
   static constexpr int kOffOut = kOffScale + 2 * kInPad * 4;     // 2 x [NT envs][8] fp32 (by tile parity)
   static constexpr int kOffNoise = kOffOut + 2 * NT * 8 * 4;     // 2 x [NT envs][4] fp32
   static constexpr int kOffBar = kOffNoise + 2 * NT * 4 * 4;
-  static constexpr int kSmemBytes = kOffBar + 256;
+  static constexpr int kSmemBytes = kOffBar + 320;
   static_assert(kSmemBytes <= 232448, "shared memory budget");
   // TMEM columns: D1 blocks at 0, D2 blocks at 4 NT, D3 / D4 (layers 3, 4) reuse D1's
   static constexpr int kColD1 = 0, kColD2 = 4 * NT, kColD3 = 0, kColD4 = NT;
@@ -105,6 +106,17 @@ __device__ __forceinline__ float tanh_fast(float z) {
   return y;
 }
 
+// The env step fused behind the actor (kEnv): the auxiliary warp, which has nothing to do once the tile's observations
+// and noise are prepared, loads the state of the tile's envs while the MLP runs and steps them the moment warp 0 has the
+// actions — no second kernel, no hand-over through a grid boundary, and no wait for the slowest actor CTA.
+struct EnvFuse {
+  OisEnvParams p;
+  OisEnvState st;
+  OisEnvIO io;
+  EnvDerived dv;
+  int64_t n;
+};
+
 struct Args {
   const float* params;        // fp32 master (biases)
   const uint8_t* image;       // tile-blocked bf16 image of the actor (update_tc.cuh: kImgW1..kImgW4)
@@ -129,9 +141,9 @@ __device__ __forceinline__ void act_store32(const uint32_t (&v)[32], float bias,
   }
 }
 
-template <int NT>
+template <int NT, bool kEnv>
 __global__ void __launch_bounds__(kThreads, 1)
-tct_actor_kernel(const __grid_constant__ Args args) {
+tct_actor_kernel(const __grid_constant__ Args args, const __grid_constant__ EnvFuse ef) {
   using C = Cfg<NT>;
   constexpr int kSlots = C::kSlots;
   constexpr int kRowsPerLane = NT / 32;        // aux / final warp: envs per lane
@@ -162,7 +174,8 @@ tct_actor_kernel(const __grid_constant__ Args args) {
   // phase completions ahead of its waiter — which a parity wait cannot tell from "not yet" (it would block for ever)
   uint64_t* noise_ready = d4_full + 1;      // [2]
   uint64_t* tile_done = noise_ready + 2;    // 16 warps: every TMEM read of the tile is done
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tile_done + 1);
+  uint64_t* act_ready = tile_done + 1;      // kEnv: warp 0 has left the tile's final actions in s_out
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(act_ready + 1);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int num_tiles = (int)((args.rows + NT - 1) / NT);
@@ -191,6 +204,7 @@ tct_actor_kernel(const __grid_constant__ Args args) {
     ptx::mbar_init(&noise_ready[0], 1);
     ptx::mbar_init(&noise_ready[1], 1);
     ptx::mbar_init(tile_done, kEpiWarps);
+    ptx::mbar_init(act_ready, 1);
     ptx::fence_barrier_init();
   }
   if (warp == 0) {
@@ -406,6 +420,45 @@ tct_actor_kernel(const __grid_constant__ Args args) {
       __syncwarp();
       if (lane == 0) ptx::mbar_arrive(&noise_ready[par]);
       if (tile + (int)gridDim.x < num_tiles) load_x(tile + gridDim.x);   // in flight while this tile's MLP runs
+      if (kEnv) {
+        // ---- the env step of this tile's envs (one tile per CTA: the host guarantees it).  State loads are in flight
+        // while the MLP runs (this warp sat out griddepcontrol.wait at the top: the previous step's stores are visible)
+        EnvLoaded el[kRowsPerLane];
+#pragma unroll
+        for (int h = 0; h < kRowsPerLane; ++h) {
+          const int64_t i = (int64_t)tile * NT + lane + 32 * h;
+          if (i < ef.n) env_load(ef.st, ef.io, i, el[h]);
+        }
+        wait(act_ready, par);
+        const float* sa_ = s_out + par * (NT * 8);
+#pragma unroll
+        for (int h = 0; h < kRowsPerLane; ++h) {
+          const int r = lane + 32 * h;
+          const int64_t i = (int64_t)tile * NT + r;
+          if (i < ef.n) {
+            el[h].act = *reinterpret_cast<const float4*>(sa_ + r * 8);
+            env_one_direct(ef.p, ef.st, ef.io, ef.dv, ef.n, i, el[h]);
+          }
+        }
+        // the last CTA to finish its envs moves the step-control block on (as the tail of env_step_kernel does): every
+        // reader of the block in this CTA — this warp, and warp 0 before it signalled act_ready — is done
+        if (ef.io.ctl != nullptr && ef.io.ctl->self_advance) {
+          __syncwarp();
+          if (lane == 0) {
+            OisStepCtl* c = const_cast<OisStepCtl*>(ef.io.ctl);
+            if (ef.io.done_flag) __threadfence_system();
+            else __threadfence();
+            if (atomicAdd(&c->ticket, 1u) == gridDim.x - 1) {
+              c->ticket = 0;
+              step_ctl_advance(c);
+              if (ef.io.done_flag) {
+                __threadfence_system();
+                *reinterpret_cast<volatile uint32_t*>(ef.io.done_flag) = (uint32_t)c->step;
+              }
+            }
+          }
+        }
+      }
     }
   } else {
     // ===================================================== epilogue warps: group g = feature block, quadrant = TMEM lane group
@@ -527,6 +580,7 @@ tct_actor_kernel(const __grid_constant__ Args args) {
                 }
               }
             }
+            if (kEnv) *reinterpret_cast<float4*>(so + r * 8) = make_float4(a[0], A > 1 ? a[1] : 0.f, A > 2 ? a[2] : 0.f, A > 3 ? a[3] : 0.f);
             float* out = args.io.actions + grow * A;
             if (A == 4) *reinterpret_cast<float4*>(out) = make_float4(a[0], a[1], a[2], a[3]);
             else if (A == 2) *reinterpret_cast<float2*>(out) = make_float2(a[0], a[1]);
@@ -535,6 +589,10 @@ tct_actor_kernel(const __grid_constant__ Args args) {
               for (int j = 0; j < 8; ++j) if (j < A) out[j] = a[j];
             }
           }
+        }
+        if (kEnv) {
+          __syncwarp();
+          if (lane == 0) ptx::mbar_arrive(act_ready);
         }
         if (args.io.noise_stats && args.io.ou_state && applied) noise_stats_warp(args.io, mx, mn, sm);
         TCT_STAMP(tr && tiles_done == 0, 23);
@@ -556,29 +614,29 @@ tct_actor_kernel(const __grid_constant__ Args args) {
 
 }  // namespace tct
 
-template <int NT>
-static cudaError_t launch(const tct::Args& args, int64_t rows, cudaStream_t s) {
+template <int NT, bool kEnv>
+static cudaError_t launch(const tct::Args& args, const tct::EnvFuse& ef, int64_t rows, cudaStream_t s) {
   using namespace tct;
   static bool attr = false;
   if (!attr) {
-    cudaError_t e = cudaFuncSetAttribute(tct_actor_kernel<NT>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg<NT>::kSmemBytes);
+    cudaError_t e = cudaFuncSetAttribute(tct_actor_kernel<NT, kEnv>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg<NT>::kSmemBytes);
     if (e != cudaSuccess) return e;
     attr = true;
   }
   const int tiles = (int)((rows + NT - 1) / NT);
   const int sms = num_sms();
-  return launch_pdl(tct_actor_kernel<NT>, tiles < sms ? tiles : sms, kThreads, Cfg<NT>::kSmemBytes, s, args);
+  return launch_pdl(tct_actor_kernel<NT, kEnv>, tiles < sms ? tiles : sms, kThreads, Cfg<NT>::kSmemBytes, s, args, ef);
 }
 
 static long long g_tct_launches = 0;     // diagnostics: launches of the transposed kernel (tests check which kernel served a call)
+static long long g_tct_fused_launches = 0;
 
-int tct_actor_forward(OisAgent* a, const uint8_t* image, const float* actor_params, const OisScaler* scaler, const OisActIO* io,
-                      int64_t rows, cudaStream_t s) {
+static int fill_args(OisAgent* a, const uint8_t* image, const float* actor_params, const OisScaler* scaler, const OisActIO* io,
+                     int64_t rows, tct::Args& args) {
   using namespace tct;
   OIS_CHECK_ARG(a->actor.h0 == kH0 && a->actor.h1 == kH1 && a->actor.h2 == kH2, "the tcgen05 actor is built for 512-512-128 hidden layers");
   OIS_CHECK_ARG(a->actor.in_dim <= 8 && a->actor.out_dim <= 8, "actor in_dim <= 8 and out_dim <= 8");
   OIS_CHECK_ARG(image, "no bf16 image of the actor weights");
-  Args args;
   args.params = actor_params;
   args.image = image;
   args.mean = scaler ? scaler->running_mean : nullptr;
@@ -590,11 +648,42 @@ int tct_actor_forward(OisAgent* a, const uint8_t* image, const float* actor_para
   args.io = *io;
   static const int debug = getenv("OIS_TCT_DEBUG_MODE") ? atoi(getenv("OIS_TCT_DEBUG_MODE")) : 0;
   args.debug = debug;
+  return OIS_OK;
+}
+
+int tct_actor_forward(OisAgent* a, const uint8_t* image, const float* actor_params, const OisScaler* scaler, const OisActIO* io,
+                      int64_t rows, cudaStream_t s) {
+  using namespace tct;
+  Args args;
+  if (int e = fill_args(a, image, actor_params, scaler, io, rows, args)) return e;
+  static const EnvFuse none = {};
   // 32-env tiles while they still fit one wave of the SMs (twice the CTAs, half the epilogue per thread), else 64
   static const int force_nt = getenv("OIS_TCT_NT") ? atoi(getenv("OIS_TCT_NT")) : 0;
   const bool nt32 = force_nt ? force_nt == 32 : (rows + 31) / 32 <= num_sms();
-  OIS_CHECK_CUDA(nt32 ? launch<32>(args, rows, s) : launch<64>(args, rows, s));
+  OIS_CHECK_CUDA((nt32 ? launch<32, false>(args, none, rows, s) : launch<64, false>(args, none, rows, s)));
   ++g_tct_launches;
+  return OIS_OK;
+}
+
+// rows that the fused policy step (actor + env step in one launch) serves: one 32-env tile per CTA, one wave
+bool tct_can_fuse_env(int64_t rows) { return rows > 0 && (rows + 31) / 32 <= num_sms(); }
+
+int tct_rollout_forward(OisAgent* a, const uint8_t* image, const float* actor_params, const OisScaler* scaler, const OisActIO* io,
+                        const OisEnvParams* ep, const OisEnvState* es, const OisEnvIO* eio, int64_t rows, cudaStream_t s) {
+  using namespace tct;
+  OIS_CHECK_ARG(tct_can_fuse_env(rows), "the fused policy step needs one 32-env tile per CTA");
+  OIS_CHECK_ARG(a->actor.out_dim <= 4 && a->actor.out_dim == ep->act_dim, "actor out_dim must be the env's act_dim (<= 4)");
+  Args args;
+  if (int e = fill_args(a, image, actor_params, scaler, io, rows, args)) return e;
+  EnvFuse ef;
+  ef.p = *ep;
+  ef.st = *es;
+  ef.io = *eio;
+  ef.dv = make_env_derived(ep);
+  ef.n = rows;
+  OIS_CHECK_CUDA((launch<32, true>(args, ef, rows, s)));
+  ++g_tct_launches;
+  ++g_tct_fused_launches;
   return OIS_OK;
 }
 
@@ -602,6 +691,8 @@ int tct_actor_forward(OisAgent* a, const uint8_t* image, const float* actor_para
 
 // diagnostics hook for profiles/tct_trace.py (deliberately not declared in include/ois_b200.h)
 extern "C" long long ois_debug_tct_launches() { return ois::g_tct_launches; }
+extern "C" long long ois_debug_tct_fused_launches() { return ois::g_tct_fused_launches; }
+extern "C" int64_t ois_rollout_fused_launches(void) { return (int64_t)ois::g_tct_fused_launches; }
 extern "C" int ois_debug_tct_trace_reset() {
   unsigned long long z[64] = {};
   z[60] = ~0ull;

@@ -55,7 +55,7 @@ class RolloutGraph:
     ``host_io="copy"`` keeps explicit copy nodes instead (H2D of the observations, ONE packed D2H) and a device
     synchronise per step."""
 
-    def __init__(self, env, agent, timestep: int, timesteps: int, host_io: bool = False):
+    def __init__(self, env, agent, timestep: int, timesteps: int, host_io: bool = False, fuse: bool = True):
         task = env.task
         if not agent._fused_replay or task._replay is None:
             raise L.OisError("RolloutGraph needs agent.fuse_replay_with(task) (the append is part of the captured kernel)")
@@ -68,6 +68,7 @@ class RolloutGraph:
         self.env, self.task, self.agent, self.memory = env, task, agent, task._replay
         self.timestep, self.timesteps = int(timestep), int(timesteps)
         self.host_io = host_io
+        self.fuse = bool(fuse)           # actor + env step as one kernel where the library can (csrc/mlp_tct.cu, kEnv)
         self.kernel_launches = 0
         dev, n, A = task.device, task.num_envs, task.num_actions
         self._dev_index = dev.index
@@ -132,6 +133,17 @@ class RolloutGraph:
         pinned pack the observations are read from (zero-copy mode; the results go to the other one)."""
         ctl = self._ctl.data_ptr()
         n = self.task.num_envs
+        if self.fuse:
+            # actor + env step as ONE kernel where the library can serve it (ois_rollout_fuse_begin: the act call is
+            # recorded, the env step that consumes its actions launches both); otherwise the same two launches as before
+            L.check(L.lib().ois_rollout_fuse_begin())
+        try:
+            self._issue_calls(src, ctl, n)
+        finally:
+            if self.fuse:
+                L.check(L.lib().ois_rollout_fuse_end())
+
+    def _issue_calls(self, src, ctl, n):
         if self.host_io == "copy":
             self._d_states.copy_(self._h_in, non_blocking=True)
             self.agent.act(self._d_states, self.timestep, self.timesteps, _ctl=ctl, _out=self._actions)
@@ -205,9 +217,11 @@ class RolloutGraph:
         launched_and_waited = False
         if not self._warm:
             before = self._host_state()
+            fused0 = L.lib().ois_rollout_fused_launches()
             self._issue(src)
             after = self._host_state()
-            self._per_step = (after[1] - before[1], after[3] - before[3])
+            fused = L.lib().ois_rollout_fused_launches() - fused0        # act + env step went out as one kernel
+            self._per_step = (after[1] - before[1] - fused, after[3] - before[3])
             self._set_host_state(before)
             self._warm = True
         else:
@@ -239,3 +253,26 @@ class RolloutGraph:
             _device_synchronize()     # copy-node mode: one device synchronise per step
             return self.h_next_states, self.h_rewards, self.h_terminated
         return t.obs_clipped, t.rew_buf.view(-1, 1), t.reset_buf.view(-1, 1)
+
+
+def fused_step(env, agent, states, timestep: int, timesteps: int):
+    """One policy step of the trainer's loop body — ``agent.act`` -> ``env.step`` -> ``agent.record_transition``
+    (src/my_trainers/base_KA_DDPG.py:175-219) — issued eagerly as ONE kernel launch where the library can serve it
+    (bf16 agent, at most 32 x SMs envs, fused replay append, past ``random_timesteps``, ``write_interval`` 0), and as the
+    usual two launches otherwise.  Returns what ``env.step`` returns.  Results are bit-identical to the three separate
+    calls (tests/test_rollout_graph_gpu.py)."""
+    fuse = agent.write_interval <= 0 and agent._fused_replay
+    lib = L.lib()
+    before = lib.ois_rollout_fused_launches()
+    if fuse:
+        L.check(lib.ois_rollout_fuse_begin())
+    try:
+        actions = agent.act(states, timestep, timesteps)[0]
+        out = env.step(actions)
+    finally:
+        if fuse:
+            L.check(lib.ois_rollout_fuse_end())
+    env.task.kernel_launches -= lib.ois_rollout_fused_launches() - before     # act + env step were one launch
+    next_states, rewards, terminated, truncated, _ = out
+    agent.record_transition(None, None, rewards, next_states, terminated, truncated, None, timestep, timesteps)
+    return out

@@ -72,31 +72,34 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import bench
 
 w = bench.World(bench.WORKLOADS["kamma_4d"], n, "bf16", torch.device("cuda", 0), seed=1)
-for cold in (False, True):
-    for it in range(5):
-        torch.cuda.synchronize()
-        lib.ois_debug_tct_trace_reset()
-        lib.ois_debug_env_trace(None, 1)
-        flush.zero_() if cold else flush[: 64 << 20].zero_()     # as in bench.py: the host queues both launches behind it
-        w.step()
-        torch.cuda.synchronize()
-    buf = (C.c_ulonglong * 64)()
-    lib.ois_debug_tct_trace(buf, 64)
-    t0 = buf[0]
-    eb = (C.c_ulonglong * 4)()
-    lib.ois_debug_env_trace(eb, 0)
-    print(f"env kernel of the same step (us after the actor's start): first CTA start {(eb[0] - t0) / 1e3:.2f}, griddepcontrol.wait "
-          f"returned {(eb[1] - t0) / 1e3:.2f} .. {(eb[2] - t0) / 1e3:.2f}, last CTA end {(eb[3] - t0) / 1e3:.2f}")
-    print(f"bench.World step, {'cold' if cold else 'warm'} L2: first start {(buf[60] - t0) / 1e3:.2f} us, last start {(buf[62] - t0) / 1e3:.2f} us, "
-          f"last end {(buf[61] - t0) / 1e3:.2f} us (span {(buf[61] - buf[60]) / 1e3:.2f} us); X written {(buf[2] - t0) / 1e3:.2f}, "
-          f"L2 issued {(buf[8] - t0) / 1e3:.2f}, done {(buf[23] - t0) / 1e3:.2f}")
-    ev = [torch.cuda.Event(enable_timing=True) for _ in range(3)]
-    if cold:
-        flush.zero_()
-    ev[0].record()
-    actions = w.agent.act(w.obs, w.t, w.T)[0]
-    ev[1].record()
-    w.obs = w.env.step(actions)[0]
-    ev[2].record()
-    torch.cuda.synchronize()
-    print(f"   events: act {ev[0].elapsed_time(ev[1]) * 1e3:.2f} us, env {ev[1].elapsed_time(ev[2]) * 1e3:.2f} us")
+for fused in (True, False):
+  step = w.step_fused if fused else w.step
+  print("== rollout.fused_step (actor + env step: one kernel)" if fused else "== agent.act + env.step (two kernels; env stamps need make EXTRA=-DOIS_ENV_TRACE)")
+  for cold in (False, True):
+      for it in range(5):
+          torch.cuda.synchronize()
+          lib.ois_debug_tct_trace_reset()
+          lib.ois_debug_env_trace(None, 1)
+          flush.zero_() if cold else flush[: 64 << 20].zero_()     # as in bench.py: the host queues both launches behind it
+          step()
+          torch.cuda.synchronize()
+      buf = (C.c_ulonglong * 64)()
+      lib.ois_debug_tct_trace(buf, 64)
+      t0 = buf[0]
+      eb = (C.c_ulonglong * 4)()
+      lib.ois_debug_env_trace(eb, 0)
+      print(f"env kernel of the same step (us after the actor's start): first CTA start {(eb[0] - t0) / 1e3:.2f}, griddepcontrol.wait "
+            f"returned {(eb[1] - t0) / 1e3:.2f} .. {(eb[2] - t0) / 1e3:.2f}, last CTA end {(eb[3] - t0) / 1e3:.2f}")
+      print(f"bench.World step, {'cold' if cold else 'warm'} L2: first start {(buf[60] - t0) / 1e3:.2f} us, last start {(buf[62] - t0) / 1e3:.2f} us, "
+            f"last end {(buf[61] - t0) / 1e3:.2f} us (span {(buf[61] - buf[60]) / 1e3:.2f} us); X written {(buf[2] - t0) / 1e3:.2f}, "
+            f"L2 issued {(buf[8] - t0) / 1e3:.2f}, done {(buf[23] - t0) / 1e3:.2f}")
+      ev = [torch.cuda.Event(enable_timing=True) for _ in range(3)]
+      if cold:
+          flush.zero_()
+      ev[0].record()
+      actions = w.agent.act(w.obs, w.t, w.T)[0]
+      ev[1].record()
+      w.obs = w.env.step(actions)[0]
+      ev[2].record()
+      torch.cuda.synchronize()
+      print(f"   events: act {ev[0].elapsed_time(ev[1]) * 1e3:.2f} us, env {ev[1].elapsed_time(ev[2]) * 1e3:.2f} us")

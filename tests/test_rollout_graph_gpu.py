@@ -172,3 +172,35 @@ def test_trainer_with_graph_rollout_equals_call_by_call_trainer(precision):
         assert torch.equal(getattr(wa["agent"], name).flat, getattr(wb["agent"], name).flat), name
     assert wa["agent"]._updates == wb["agent"]._updates == 20
     assert_worlds_equal(wa, wb)
+
+
+@pytest.mark.parametrize("variant,n", [("KAMMA_medium", 4096), ("KAMMA_medium", 1000), ("KA_DDPG_2D", 333), ("KA_DDPG_1D", 64),
+                                       ("KAMMA_medium", 32 * 148 + 5)])
+def test_fused_step_is_bit_identical_to_act_then_env_step(variant, n):
+    """rollout.fused_step: actor + env step (+ replay append) as ONE kernel (csrc/mlp_tct.cu, kEnv) against the three
+    separate calls, 11 steps over a 5-slot ring with an update in between; the launch counter proves which path ran
+    (the last size is one env too many for one 32-env tile per CTA: it must fall back to the two launches)."""
+    import ctypes
+
+    import torch
+
+    import options_in_simulation_b200 as ois
+    from options_in_simulation_b200.rollout import fused_step
+
+    lib = ois.lib()
+    lib.ois_debug_tct_fused_launches.restype = ctypes.c_longlong
+    wa = make_world(variant, n, "bf16", t_e=1006)
+    wb = make_world(variant, n, "bf16", t_e=1006)
+    before = lib.ois_debug_tct_fused_launches()
+    for k in range(11):
+        oa, ra, da = eager_step(wa, 1000 + k)
+        ob, rb, db, _, _ = fused_step(wb["env"], wb["agent"], wb["obs"], 1000 + k, T_TOTAL)
+        wb["obs"] = ob
+        torch.cuda.synchronize()
+        assert torch.equal(oa, ob) and torch.equal(ra, rb) and torch.equal(da, db), k
+        if k == 5 and n * 5 >= 512:
+            for w in (wa, wb):
+                w["agent"]._update(1000 + k, T_TOTAL)
+    fused = lib.ois_debug_tct_fused_launches() - before
+    assert fused == (11 if n <= 32 * 148 else 0), fused
+    assert_worlds_equal(wa, wb)

@@ -295,6 +295,19 @@ int64_t ois_rollout_fused_launches(void);
 int ois_mlp_forward(OisAgent* agent, const OisMlpShape* shape, const float* params, const float* x, float* y,
                     int64_t n_rows, void* stream);
 
+/* ois_mlp_forward without a handle and without any allocation.  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops,
+ * harnesses that forbid it).  Same kernels and bit-identical results as ois_mlp_forward (fp32); the hidden activations
+ * live in ONE file-scope device array inside the library (csrc/no_alloc.cu: 4096 x (512 + 512 + 128) fp32 = 18 MiB per
+ * GPU that loads the library, held until exit) instead of a handle's cudaMalloc'ed workspace.  The call allocates
+ * nothing (no cudaMalloc / cudaFree / allocating library routine).  Limits: n_rows <= OIS_STATIC_MLP_MAX_ROWS and hidden
+ * sizes <= 512, 512, 128, else OIS_ERR_INVALID_ARG with ois_last_error_string() naming the limit.  Every call on a device
+ * shares the array (it keeps the last call's contents; nothing in it needs to start at zero): calls that overlap on the
+ * GPU race, so serialise them on one stream or with events. */
+#define OIS_STATIC_MLP_MAX_ROWS 4096
+int ois_mlp_forward_static(const OisMlpShape* shape, const float* params, const float* x, float* y, int64_t n_rows,
+                           void* stream);
+
 /* ------------------------------------------------------------------------------------------------
  * Data-parallel gradient exchange over NVLink peer memory (one process per GPU, one node).
  * Replaces the two Model.reduce_parameters calls of DDPG._update (src/my_agents/ddpg.py:409-410 critic,

@@ -118,6 +118,7 @@ SYMBOLS = {
     "ois_rollout_fused_launches": (_i64, []),
     "ois_scaler_forward": (C.c_int, [_PP(Scaler), _p, _p, _i64, _i32, _i32, _p]),
     "ois_mlp_forward": (C.c_int, [_p, _PP(MlpShape), _p, _p, _p, _i64, _p]),
+    "ois_mlp_forward_static": (C.c_int, [_PP(MlpShape), _p, _p, _p, _i64, _p]),
     "ois_ddpg_update_phase": (C.c_int, [_p, _PP(Scaler), _PP(UpdateIO), _i32, _f, _p]),
     "ois_step_ctl_advance": (C.c_int, [_p, _p]),
     "ois_graph_launch": (C.c_int, [_p, _p]),

@@ -4,6 +4,9 @@
 // own copy of this text because its staging is interleaved with the arithmetic.  The two must stay the same arithmetic,
 // statement for statement: tests/test_rollout_graph_gpu.py holds the fused step bit-identical to act + env step.
 #pragma once
+#ifndef ENV_ONE_STAMP
+#define ENV_ONE_STAMP(slot) do { } while (0)   // timeline diagnostics of the including kernel (mlp_tct.cu)
+#endif
 #include "env_core.cuh"
 
 namespace ois {
@@ -134,7 +137,9 @@ __device__ __forceinline__ int env_one_direct(const OisEnvParams& p, const OisEn
   Skid s;
   s.px = pv.x; s.py = pv.y; s.yaw = pv.z; s.vx = pv.w; s.vy = tp.x; s.r = tp.y;
   s.w[0] = wv.x; s.w[1] = wv.y; s.w[2] = wv.z; s.w[3] = wv.w;
+  ENV_ONE_STAMP(31);
   if (p.physics) skid_steps(s, wt, p);
+  ENV_ONE_STAMP(32);
 
   // ------------------------------------------------------------------ group B: issued one iteration ago
   float4 sa = L.sa;
@@ -231,6 +236,7 @@ __device__ __forceinline__ int env_one_direct(const OisEnvParams& p, const OisEn
     q[2] = make_float2(oc[4], oc[5]);
   }
   __stcs(io.rew + i, rew);
+  ENV_ONE_STAMP(33);
   io.reset[i] = reset ? 1 : 0;
   if (io.timeout) __stcs(io.timeout + i, (int64_t)(timeout ? 1 : 0));
 

@@ -25,6 +25,22 @@
 // Numerics: identical contract to mlp_tc.cu (bf16 operands, fp32 accumulation, fp32 bias / activation); tests compare
 // both kernels with the fp32 oracle (tests/test_agent_gpu.py).
 #include "agent.cuh"
+namespace ois { namespace tct {
+__device__ unsigned long long g_tct_trace[64];
+// latest warp exit of the launch (reported as slot 61).  A symbol of its own: with the exit stamp in g_tct_trace the
+// compiler kept &g_tct_trace[60] from the entry stamps alive to the end of the kernel, spilled it in the kEnv build,
+// and that spill store — the first local-memory access of every thread, a cold translation after an L2 flush — delayed
+// the bias loads queued behind it by ~2 us.
+__device__ unsigned long long g_tct_last_end;
+} }
+#define ENV_ONE_STAMP(slot)                                              \
+  do {                                                                   \
+    if (blockIdx.x == 0 && (threadIdx.x & 31) == 0) {                    \
+      unsigned long long t_;                                             \
+      asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_));             \
+      ::ois::tct::g_tct_trace[slot] = t_;                                \
+    }                                                                    \
+  } while (0)
 #include "env_one.cuh"
 #include "explore.cuh"
 #include "tc_ptx.cuh"
@@ -56,7 +72,8 @@ struct Cfg {
   static constexpr int kOffScale = kOffBias + kBiasTotal * 4;    // mean[16], 1 / (sqrt(var)+eps) [16]
   static constexpr int kOffOut = kOffScale + 2 * kInPad * 4;     // 2 x [NT envs][8] fp32 (by tile parity)
   static constexpr int kOffNoise = kOffOut + 2 * NT * 8 * 4;     // 2 x [NT envs][4] fp32
-  static constexpr int kOffBar = kOffNoise + 2 * NT * 4 * 4;
+  static constexpr int kOffStage = kOffNoise + 2 * NT * 4 * 4;   // [NT envs][8] fp32: raw observations of the next tile (LDGSTS)
+  static constexpr int kOffBar = kOffStage + NT * 8 * 4;
   static constexpr int kSmemBytes = kOffBar + 320;
   static_assert(kSmemBytes <= 232448, "shared memory budget");
   // TMEM columns: D1 blocks at 0, D2 blocks at 4 NT, D3 / D4 (layers 3, 4) reuse D1's
@@ -64,7 +81,6 @@ struct Cfg {
   static constexpr int kTmemCols = 8 * NT;
 };
 
-__device__ unsigned long long g_tct_trace[64];
 __device__ __forceinline__ void stamp(int slot) {
   unsigned long long t;
   asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
@@ -157,6 +173,7 @@ tct_actor_kernel(const __grid_constant__ Args args, const __grid_constant__ EnvF
   float* s_scale = reinterpret_cast<float*>(smem + C::kOffScale);
   float* s_out = reinterpret_cast<float*>(smem + C::kOffOut);
   float* s_noise = reinterpret_cast<float*>(smem + C::kOffNoise);
+  float* s_stage = reinterpret_cast<float*>(smem + C::kOffStage);
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + C::kOffBar);
   uint64_t* full = bars;                    // [kSlots] ring slot filled (producer tx bytes)
   uint64_t* empty = full + kSlots;          // [kSlots] ring slot consumed (MMA commit)
@@ -181,11 +198,14 @@ tct_actor_kernel(const __grid_constant__ Args args, const __grid_constant__ EnvF
   const int num_tiles = (int)((args.rows + NT - 1) / NT);
   const bool tr = blockIdx.x == 0 && lane == 0;
   TCT_STAMP(tr && warp == 0, 0);
-  if (lane == 0) {   // diagnostics: earliest warp start / latest warp start / latest warp end of the launch (slots 60, 62, 61)
+  // diagnostics: earliest / latest CTA start and latest warp end of the launch (slots 60, 62, 61).  Reductions without a
+  // return value, spelled out: as atomicMin / atomicMax the kEnv build compiled them to ATOMG (with a return the warp
+  // later waits for), 2560 of them per launch on one address — 2.4 us before warps 0..15 reached the set-up barrier.
+  if (threadIdx.x == 0) {
     unsigned long long t;
     asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
-    atomicMin(&g_tct_trace[60], t);
-    atomicMax(&g_tct_trace[62], t);
+    asm volatile("red.relaxed.gpu.global.min.u64 [%0], %1;" ::"l"(&g_tct_trace[60]), "l"(t) : "memory");
+    asm volatile("red.relaxed.gpu.global.max.u64 [%0], %1;" ::"l"(&g_tct_trace[62]), "l"(t) : "memory");
   }
 
   // Set-up.  The weight stream starts as early as possible: thread 0 initialises the barriers, warp 0 signals the two
@@ -239,6 +259,7 @@ tct_actor_kernel(const __grid_constant__ Args args, const __grid_constant__ EnvF
     }
     return;   // every copy issued is consumed by an MMA of this CTA before the other warps leave
   }
+  TCT_STAMP(tr && warp == kWarpMma, 37);
   if (warp == kWarpMma) ptx::tmem_alloc<C::kTmemCols>(tmem_slot);
   if (warp < kEpiWarps) {   // biases, fp32, from the master parameters; all loads of a thread in flight at once
     const int64_t b0 = (int64_t)kH0 * args.in_dim, w1 = b0 + kH0, b1 = w1 + (int64_t)kH1 * kH0, w2 = b1 + kH1;
@@ -268,23 +289,31 @@ tct_actor_kernel(const __grid_constant__ Args args, const __grid_constant__ EnvF
     if (args.mean != nullptr && c < args.in_dim) v = is_mean ? (float)args.mean[c] : __fadd_rn(sqrtf((float)args.var[c]), 1e-8f);
     s_scale[lane] = v;
   }
-  float x_aux[kRowsPerLane][8];      // auxiliary warp: raw observations of its next tile
+  // auxiliary warp: the raw observations of its next tile travel global -> shared asynchronously (LDGSTS), each lane its
+  // own rows.  (Held in registers across the set-up barrier and the MLP they were spilled by ptxas in the kEnv build, and
+  // the spill store waits for the load: 2.4 us of exposed HBM latency before the first MMA.)
   auto load_x = [&](int tile) {
 #pragma unroll
     for (int h = 0; h < kRowsPerLane; ++h) {
       const int64_t r = (int64_t)tile * NT + lane + 32 * h;
+      if (r < args.rows) {
 #pragma unroll
-      for (int j = 0; j < 8; ++j) x_aux[h][j] = (j < args.in_dim && r < args.rows) ? args.io.states[r * args.in_dim + j] : 0.f;
+        for (int j = 0; j < 8; ++j)
+          if (j < args.in_dim) ptx::cp_async4(s_stage + (lane + 32 * h) * 8 + j, args.io.states + r * args.in_dim + j);
+      }
     }
   };
   if (warp == kWarpAux) {
     // Programmatic dependent launch: everything else in this set-up overlaps the predecessor's tail; the observations are
     // what the predecessor (the env step) produced.  The next kernel is let go at once: it reads nothing of ours before
     // its own wait.
+    TCT_STAMP(tr, 24);
     pdl_wait();
+    TCT_STAMP(tr, 25);
     if (lane == 0) pdl_trigger();
     if ((int)blockIdx.x < num_tiles) load_x(blockIdx.x);
   }
+  TCT_STAMP(tr && (warp == 0 || warp >= kWarpMma), warp == 0 ? 34 : warp == kWarpMma ? 35 : 36);
   ptx::tc_fence_before();
   asm volatile("bar.sync 1, 576;" ::: "memory");      // all warps but the two producers
   ptx::tc_fence_after();
@@ -384,10 +413,20 @@ tct_actor_kernel(const __grid_constant__ Args args, const __grid_constant__ EnvF
     // ===================================================== auxiliary warp: observations -> X operand, then the tile's OU noise
     const int A = args.out_dim;
     const bool row_noise = args.io.ou_state != nullptr && (A == 1 || A == 2 || A == 4);
-    auto& x = x_aux;
+    float x[kRowsPerLane][8];
     uint32_t tiles_done = 0;
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++tiles_done) {
       const uint32_t par = tiles_done & 1;
+      ptx::cp_async_wait_all();                                // this lane's rows of the tile are in s_stage
+#pragma unroll
+      for (int h = 0; h < kRowsPerLane; ++h) {
+        const bool live = (int64_t)tile * NT + lane + 32 * h < args.rows;
+        const float4 lo = *reinterpret_cast<const float4*>(s_stage + (lane + 32 * h) * 8);
+        const float4 hi = *reinterpret_cast<const float4*>(s_stage + (lane + 32 * h) * 8 + 4);
+        const float raw[8] = {lo.x, lo.y, lo.z, lo.w, hi.x, hi.y, hi.z, hi.w};
+#pragma unroll
+        for (int j = 0; j < 8; ++j) x[h][j] = (live && j < args.in_dim) ? raw[j] : 0.f;
+      }
       if (tiles_done > 0) wait(&d1_full[3], par ^ 1);          // the previous tile's layer 1 has read X
 #pragma unroll
       for (int h = 0; h < kRowsPerLane; ++h) {
@@ -419,7 +458,9 @@ tct_actor_kernel(const __grid_constant__ Args args, const __grid_constant__ EnvF
       }
       __syncwarp();
       if (lane == 0) ptx::mbar_arrive(&noise_ready[par]);
-      if (tile + (int)gridDim.x < num_tiles) load_x(tile + gridDim.x);   // in flight while this tile's MLP runs
+      // next tile's observations: in flight while this tile's MLP runs (kEnv: one tile per CTA — and the observations must
+      // not stay live across the env step, where they would be spilled and the spill store would wait for the load)
+      if (!kEnv && tile + (int)gridDim.x < num_tiles) load_x(tile + gridDim.x);
       if (kEnv) {
         // ---- the env step of this tile's envs (one tile per CTA: the host guarantees it).  State loads are in flight
         // while the MLP runs (this warp sat out griddepcontrol.wait at the top: the previous step's stores are visible)
@@ -429,7 +470,9 @@ tct_actor_kernel(const __grid_constant__ Args args, const __grid_constant__ EnvF
           const int64_t i = (int64_t)tile * NT + lane + 32 * h;
           if (i < ef.n) env_load(ef.st, ef.io, i, el[h]);
         }
+        TCT_STAMP(tr && tiles_done == 0, 28);
         wait(act_ready, par);
+        TCT_STAMP(tr && tiles_done == 0, 29);
         const float* sa_ = s_out + par * (NT * 8);
 #pragma unroll
         for (int h = 0; h < kRowsPerLane; ++h) {
@@ -440,6 +483,7 @@ tct_actor_kernel(const __grid_constant__ Args args, const __grid_constant__ EnvF
             env_one_direct(ef.p, ef.st, ef.io, ef.dv, ef.n, i, el[h]);
           }
         }
+        TCT_STAMP(tr && tiles_done == 0, 30);
         // the last CTA to finish its envs moves the step-control block on (as the tail of env_step_kernel does): every
         // reader of the block in this CTA — this warp, and warp 0 before it signalled act_ready — is done
         if (ef.io.ctl != nullptr && ef.io.ctl->self_advance) {
@@ -608,7 +652,7 @@ tct_actor_kernel(const __grid_constant__ Args args, const __grid_constant__ EnvF
   if (lane == 0) {     // diagnostics: every warp's exit time
     unsigned long long t;
     asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
-    atomicMax(&g_tct_trace[61], t);
+    asm volatile("red.relaxed.gpu.global.max.u64 [%0], %1;" ::"l"(&g_tct_last_end), "l"(t) : "memory");
   }
 }
 
@@ -696,9 +740,12 @@ extern "C" int64_t ois_rollout_fused_launches(void) { return (int64_t)ois::g_tct
 extern "C" int ois_debug_tct_trace_reset() {
   unsigned long long z[64] = {};
   z[60] = ~0ull;
+  if (cudaMemcpyToSymbol(ois::tct::g_tct_last_end, z, sizeof(unsigned long long)) != cudaSuccess) return -2;
   return cudaMemcpyToSymbol(ois::tct::g_tct_trace, z, sizeof(z)) == cudaSuccess ? 0 : -2;
 }
 extern "C" int ois_debug_tct_trace(unsigned long long* out_host, int n) {
   if (n > 64) n = 64;
-  return cudaMemcpyFromSymbol(out_host, ois::tct::g_tct_trace, sizeof(unsigned long long) * n) == cudaSuccess ? 0 : -2;
+  if (cudaMemcpyFromSymbol(out_host, ois::tct::g_tct_trace, sizeof(unsigned long long) * n) != cudaSuccess) return -2;
+  if (n > 61 && cudaMemcpyFromSymbol(out_host + 61, ois::tct::g_tct_last_end, sizeof(unsigned long long)) != cudaSuccess) return -2;
+  return 0;
 }

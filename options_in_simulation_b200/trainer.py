@@ -34,6 +34,8 @@ SEQUENTIAL_TRAINER_DEFAULT_CONFIG = {   # src/my_trainers/sequential.py:14-20
     "kind": "auto",          # "KA_DDPG" (relabel) | "KA" (no relabel) | "auto": the env variant's pairing
     "log_interval": None,    # steps between env-0 / episode logging reads; None = agent.write_interval
     "pre_step_hook": None,   # callable(trainer, timestep) run at the top of every timestep (parity tests supply draws)
+    "fuse_policy_step": True,  # eager loop: issue act + env.step as ONE kernel where the library can (rollout.fused_step;
+                               # bit-identical to the two launches; needs agent.fuse_replay_with(task), headless)
     "graph_rollout": False,  # act + env.step (+ fused replay append) as ONE CUDA-graph launch per timestep once past
                              # random_timesteps (rollout.RolloutGraph; needs agent.fuse_replay_with(task), write_interval 0)
 }
@@ -113,6 +115,8 @@ class SequentialTrainer:
         if self.cfg["graph_rollout"]:
             from .rollout import RolloutGraph
             graph = RolloutGraph(env, agent, max(self.initial_timestep, agent._random_timesteps), self.timesteps)
+        from .rollout import fused_step
+        fuse_step = bool(self.cfg["fuse_policy_step"] and agent._fused_replay and not agent.secondary_memories and self.headless)
         for timestep in self._progress():
             if hook is not None:
                 hook(self, timestep)
@@ -126,15 +130,18 @@ class SequentialTrainer:
                 agent.post_interaction(timestep=timestep, timesteps=self.timesteps)     # base_KA_DDPG.py:283 (again)
                 continue
             with torch.no_grad():
-                actions = agent.act(states, timestep=timestep, timesteps=self.timesteps)[0]
-                next_states, rewards, terminated, truncated, infos = env.step(actions)
-                if self.kind == "KA_DDPG":   # base_KA_DDPG.py:212
-                    actions = None if agent._fused_replay else env.task.wheel_torqs / env.task.action_scale
-                if not self.headless:
-                    env.render()
-                agent.record_transition(states=states, actions=actions, rewards=rewards, next_states=next_states,
-                                        terminated=terminated, truncated=truncated, infos=infos, timestep=timestep,
-                                        timesteps=self.timesteps)
+                if fuse_step:    # act + env.step (+ the fused replay append) as one kernel launch; same results
+                    next_states, rewards, terminated, truncated, infos = fused_step(env, agent, states, timestep, self.timesteps)
+                else:
+                    actions = agent.act(states, timestep=timestep, timesteps=self.timesteps)[0]
+                    next_states, rewards, terminated, truncated, infos = env.step(actions)
+                    if self.kind == "KA_DDPG":   # base_KA_DDPG.py:212
+                        actions = None if agent._fused_replay else env.task.wheel_torqs / env.task.action_scale
+                    if not self.headless:
+                        env.render()
+                    agent.record_transition(states=states, actions=actions, rewards=rewards, next_states=next_states,
+                                            terminated=terminated, truncated=truncated, infos=infos, timestep=timestep,
+                                            timesteps=self.timesteps)
                 if self.log_interval > 0 and timestep % self.log_interval == 0:
                     self._log_env(infos)
             agent.post_interaction(timestep=timestep, timesteps=self.timesteps)     # base_KA_DDPG.py:265

@@ -36,7 +36,8 @@ __device__ __forceinline__ void env_load(const OisEnvState& st, const OisEnvIO& 
 
 // returns 1 when the env was reset this step
 __device__ __forceinline__ int env_one_direct(const OisEnvParams& p, const OisEnvState& st, const OisEnvIO& io, const EnvDerived& dv,
-                                              const int64_t n, const int64_t i, const EnvLoaded& L) {
+                                              const int64_t n, const int64_t i, const EnvLoaded& L,
+                                              const bool defer_obs_clipped, float (&obs_clipped_out)[6]) {
   constexpr bool kStats = false, kEval = false;
   float acc[OIS_EP_STATS_LEN] = {};     // dead (kStats is false): keeps the shared text compiling
   int any_reset_local = 0;
@@ -229,7 +230,10 @@ __device__ __forceinline__ int env_one_direct(const OisEnvParams& p, const OisEn
   float oc[6];
 #pragma unroll
   for (int k = 0; k < 6; ++k) oc[k] = io.clip_obs > 0.f ? clipf(ob[k], -io.clip_obs, io.clip_obs) : ob[k];
-  if (io.obs_clipped) {   // what the env wrapper returns: clamp(obs_buf, +-clipObservations)  (rl_task.py:99)
+#pragma unroll
+  for (int k = 0; k < 6; ++k) obs_clipped_out[k] = oc[k];
+  if (defer_obs_clipped) {   // the caller stores the tile's rows itself (coalesced: mlp_tct.cu)
+  } else if (io.obs_clipped) {   // what the env wrapper returns: clamp(obs_buf, +-clipObservations)  (rl_task.py:99)
     float2* q = reinterpret_cast<float2*>(io.obs_clipped + 6 * i);
     q[0] = make_float2(oc[0], oc[1]);
     q[1] = make_float2(oc[2], oc[3]);

@@ -414,12 +414,12 @@ env_step_kernel(const __grid_constant__ OisEnvParams p, const __grid_constant__ 
       if (io.done_flag) __threadfence_system();
       else __threadfence();
       if (atomicAdd(&c->ticket, 1u) == gridDim.x - 1) {
+        if (io.done_flag) {     // every CTA's results are out (each fenced system-wide before its ticket): tell the host which
+          __threadfence();      // step is complete — before the block's own update, which the host does not wait for
+          *reinterpret_cast<volatile uint32_t*>(io.done_flag) = (uint32_t)(c->step + 1);
+        }
         c->ticket = 0;
         step_ctl_advance(c);
-        if (io.done_flag) {     // every CTA's results are out: tell the host which step is complete
-          __threadfence_system();
-          *reinterpret_cast<volatile uint32_t*>(io.done_flag) = (uint32_t)c->step;
-        }
       }
     }
   }

@@ -292,14 +292,25 @@ tct_actor_kernel(const __grid_constant__ Args args, const __grid_constant__ EnvF
   // auxiliary warp: the raw observations of its next tile travel global -> shared asynchronously (LDGSTS), each lane its
   // own rows.  (Held in registers across the set-up barrier and the MLP they were spilled by ptxas in the kEnv build, and
   // the spill store waits for the load: 2.4 us of exposed HBM latency before the first MMA.)
+  // Layout of the staging buffer: the tile's rows packed, [NT][in_dim].  A full tile is one contiguous, 16-byte aligned
+  // block of the observation matrix: it is copied in 16-byte pieces (whole sectors, each read once — it matters when the
+  // observations sit in pinned HOST memory and every piece is a PCIe read); a ragged last tile goes element by element.
+  const bool x_wide = (reinterpret_cast<uintptr_t>(args.io.states) & 15) == 0;
   auto load_x = [&](int tile) {
+    const int64_t r0 = (int64_t)tile * NT;
+    if (x_wide && r0 + NT <= args.rows) {
+      const float* src = args.io.states + r0 * args.in_dim;
+      const int chunks = NT * args.in_dim / 4;
+      for (int c = lane; c < chunks; c += 32) ptx::cp_async16(s_stage + 4 * c, src + 4 * c);
+    } else {
 #pragma unroll
-    for (int h = 0; h < kRowsPerLane; ++h) {
-      const int64_t r = (int64_t)tile * NT + lane + 32 * h;
-      if (r < args.rows) {
+      for (int h = 0; h < kRowsPerLane; ++h) {
+        const int64_t r = r0 + lane + 32 * h;
+        if (r < args.rows) {
 #pragma unroll
-        for (int j = 0; j < 8; ++j)
-          if (j < args.in_dim) ptx::cp_async4(s_stage + (lane + 32 * h) * 8 + j, args.io.states + r * args.in_dim + j);
+          for (int j = 0; j < 8; ++j)
+            if (j < args.in_dim) ptx::cp_async4(s_stage + (lane + 32 * h) * args.in_dim + j, args.io.states + r * args.in_dim + j);
+        }
       }
     }
   };
@@ -417,16 +428,15 @@ tct_actor_kernel(const __grid_constant__ Args args, const __grid_constant__ EnvF
     uint32_t tiles_done = 0;
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++tiles_done) {
       const uint32_t par = tiles_done & 1;
-      ptx::cp_async_wait_all();                                // this lane's rows of the tile are in s_stage
+      ptx::cp_async_wait_all();                                // every lane's copies have landed ...
+      __syncwarp();                                            // ... before any lane reads the rows others fetched
 #pragma unroll
       for (int h = 0; h < kRowsPerLane; ++h) {
         const bool live = (int64_t)tile * NT + lane + 32 * h < args.rows;
-        const float4 lo = *reinterpret_cast<const float4*>(s_stage + (lane + 32 * h) * 8);
-        const float4 hi = *reinterpret_cast<const float4*>(s_stage + (lane + 32 * h) * 8 + 4);
-        const float raw[8] = {lo.x, lo.y, lo.z, lo.w, hi.x, hi.y, hi.z, hi.w};
 #pragma unroll
-        for (int j = 0; j < 8; ++j) x[h][j] = (live && j < args.in_dim) ? raw[j] : 0.f;
+        for (int j = 0; j < 8; ++j) x[h][j] = (live && j < args.in_dim) ? s_stage[(lane + 32 * h) * args.in_dim + j] : 0.f;
       }
+      __syncwarp();                                            // all reads done before the next tile's copies are issued
       if (tiles_done > 0) wait(&d1_full[3], par ^ 1);          // the previous tile's layer 1 has read X
 #pragma unroll
       for (int h = 0; h < kRowsPerLane; ++h) {
@@ -470,36 +480,65 @@ tct_actor_kernel(const __grid_constant__ Args args, const __grid_constant__ EnvF
           const int64_t i = (int64_t)tile * NT + lane + 32 * h;
           if (i < ef.n) env_load(ef.st, ef.io, i, el[h]);
         }
+        // the step-control block of the next step, evaluated while the MLP runs (lane 0; parked in the scaler constants'
+        // shared memory, which is dead once X is written: one tile per CTA) — the last CTA only stores it
+        const bool advance = ef.io.ctl != nullptr && ef.io.ctl->self_advance;
+        StepCtlNext* s_next = reinterpret_cast<StepCtlNext*>(s_scale);
+        static_assert(sizeof(StepCtlNext) <= 2 * kInPad * 4, "StepCtlNext is parked in the scaler constants");
+        if (advance && lane == 0) *s_next = step_ctl_next(ef.io.ctl);
         TCT_STAMP(tr && tiles_done == 0, 28);
         wait(act_ready, par);
         TCT_STAMP(tr && tiles_done == 0, 29);
         const float* sa_ = s_out + par * (NT * 8);
+        // The wrapper's observations [n, 6] (what the host reads back — pinned HOST memory in the host-in-the-loop mode) of a
+        // full tile leave as whole 16-byte pieces of one contiguous block, staged through shared memory, instead of three
+        // 8-byte stores per lane at a 24-byte stride (partial sectors: several PCIe writes per sector).
+        const int64_t t0 = (int64_t)tile * NT;
+        const bool oc_wide = ef.io.obs_clipped != nullptr && t0 + NT <= ef.n && (reinterpret_cast<uintptr_t>(ef.io.obs_clipped) & 15) == 0;
 #pragma unroll
         for (int h = 0; h < kRowsPerLane; ++h) {
           const int r = lane + 32 * h;
-          const int64_t i = (int64_t)tile * NT + r;
+          const int64_t i = t0 + r;
           if (i < ef.n) {
             el[h].act = *reinterpret_cast<const float4*>(sa_ + r * 8);
-            env_one_direct(ef.p, ef.st, ef.io, ef.dv, ef.n, i, el[h]);
+            float oc[6];
+            env_one_direct(ef.p, ef.st, ef.io, ef.dv, ef.n, i, el[h], oc_wide, oc);
+            if (oc_wide) {
+#pragma unroll
+              for (int k = 0; k < 6; k += 2) *reinterpret_cast<float2*>(s_stage + r * 6 + k) = make_float2(oc[k], oc[k + 1]);
+            }
           }
         }
+        if (oc_wide) {
+          __syncwarp();
+          float4* dst = reinterpret_cast<float4*>(ef.io.obs_clipped + t0 * 6);
+          for (int c = lane; c < NT * 6 / 4; c += 32) dst[c] = *reinterpret_cast<const float4*>(s_stage + 4 * c);
+        }
         TCT_STAMP(tr && tiles_done == 0, 30);
-        // the last CTA to finish its envs moves the step-control block on (as the tail of env_step_kernel does): every
-        // reader of the block in this CTA — this warp, and warp 0 before it signalled act_ready — is done
-        if (ef.io.ctl != nullptr && ef.io.ctl->self_advance) {
+        // The last CTA to finish its envs moves the step-control block on (as the tail of env_step_kernel does).  Every
+        // reader of the block in this CTA is done: warp 0 read it before it signalled act_ready, this warp's reads fed the
+        // addresses and values of stores it has issued.  With a host waiting (done_flag) the CTA's results — stores to
+        // pinned host memory — are made visible system-wide before the ticket; the last CTA, having seen every ticket, then
+        // only has to keep its flag store behind that observation (a GPU-scope fence), and stores the block afterwards:
+        // the host does not wait for it, the next launch is ordered behind this kernel anyway.
+        if (advance) {
           __syncwarp();
           if (lane == 0) {
             OisStepCtl* c = const_cast<OisStepCtl*>(ef.io.ctl);
             if (ef.io.done_flag) __threadfence_system();
-            else __threadfence();
+            TCT_STAMP(tr, 38);
             if (atomicAdd(&c->ticket, 1u) == gridDim.x - 1) {
-              c->ticket = 0;
-              step_ctl_advance(c);
+              stamp(40);
+              const StepCtlNext nx = *s_next;
               if (ef.io.done_flag) {
-                __threadfence_system();
-                *reinterpret_cast<volatile uint32_t*>(ef.io.done_flag) = (uint32_t)c->step;
+                __threadfence();
+                *reinterpret_cast<volatile uint32_t*>(ef.io.done_flag) = (uint32_t)nx.step;
               }
+              c->ticket = 0;
+              step_ctl_store(c, nx);
+              stamp(41);
             }
+            TCT_STAMP(tr, 39);
           }
         }
       }

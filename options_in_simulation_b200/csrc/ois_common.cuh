@@ -119,18 +119,41 @@ inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, s
 // The one place the per-step scalars of a graph-replayed rollout step are derived (see OisStepCtl in ois_b200.h); run by a
 // single thread.  The noise scale follows ddpg.py:247-251 in double, as the host path (agent.py: DDPG.act) evaluates it
 // before narrowing to float.
-__device__ inline void step_ctl_advance(OisStepCtl* c) {
-  c->step += 1;
-  c->env_philox_offset += 1;
-  c->act_philox_offset += 1;
-  c->replay_row = c->replay_rows > 0 ? (c->replay_row + 1) % c->replay_rows : 0;
-  c->flag_slot = (c->flag_slot + 1) % 3;
+// The block's contents for the NEXT policy step.  Split from the store so that a kernel can evaluate it (an fp64 division,
+// a 64-bit modulo, a dozen dependent loads: ~1.6 us for one thread) while it waits for something else, and its last CTA
+// only has to store the result.
+struct StepCtlNext {
+  int64_t step;
+  uint64_t env_philox_offset, act_philox_offset;
+  int64_t replay_row;
+  double timestep;
+  int32_t flag_slot;
+  float noise_scale;
+};
+__device__ inline StepCtlNext step_ctl_next(const OisStepCtl* c) {
+  StepCtlNext nx;
+  nx.step = c->step + 1;
+  nx.env_philox_offset = c->env_philox_offset + 1;
+  nx.act_philox_offset = c->act_philox_offset + 1;
+  nx.replay_row = c->replay_rows > 0 ? (c->replay_row + 1) % c->replay_rows : 0;
+  nx.flag_slot = (c->flag_slot + 1) % 3;
   const double t = c->timestep + 1.0;
-  c->timestep = t;
-  c->noise_scale = t <= c->expl_timesteps
+  nx.timestep = t;
+  nx.noise_scale = t <= c->expl_timesteps
       ? (float)((1.0 - t / c->expl_timesteps) * (c->expl_initial_scale - c->expl_final_scale) + c->expl_final_scale)
       : -1.0f;
+  return nx;
 }
+__device__ inline void step_ctl_store(OisStepCtl* c, const StepCtlNext& nx) {
+  c->step = nx.step;
+  c->env_philox_offset = nx.env_philox_offset;
+  c->act_philox_offset = nx.act_philox_offset;
+  c->replay_row = nx.replay_row;
+  c->flag_slot = nx.flag_slot;
+  c->timestep = nx.timestep;
+  c->noise_scale = nx.noise_scale;
+}
+__device__ inline void step_ctl_advance(OisStepCtl* c) { step_ctl_store(c, step_ctl_next(c)); }
 
 // streaming 16-byte accesses: every state field is touched once per step
 __device__ inline float4 ld_stream4(const float* p) { return __ldcs(reinterpret_cast<const float4*>(p)); }

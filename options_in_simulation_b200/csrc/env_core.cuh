@@ -122,18 +122,31 @@ __device__ __forceinline__ SideOut side(float2 w, float2 tau, float nu /* -u of 
   return o;
 }
 
-__device__ __forceinline__ void skid_steps(Skid& s, const float tau[4], const OisEnvParams& p) {
+// What the sub-steps need that depends on neither the torques nor the loop: three IEEE divisions and sincos(yaw).  Split
+// off so that a caller that has the state before it has the torques (the one-launch policy step, mlp_tct.cu) can evaluate
+// it while it waits; the arithmetic is the same either way.
+struct SkidPre { float m_h, J_h, Iw_h, sn, cs; };
+__device__ __forceinline__ SkidPre skid_prepare(float yaw, const OisEnvParams& p) {
+  SkidPre q;
+  const float h = p.sim_dt;
+  q.m_h = p.mass / h;
+  q.J_h = p.yaw_inertia / h;
+  q.Iw_h = p.wheel_inertia / h + p.wheel_damping;
+  sincosf(yaw, &q.sn, &q.cs);
+  return q;
+}
+
+__device__ __forceinline__ void skid_steps(Skid& s, const float tau[4], const OisEnvParams& p, const SkidPre& pre) {
   const float h = p.sim_dt, R = p.wheel_radius, c = p.wheel_damping;
   const float a = p.half_wheelbase, b = p.half_track;
   const float m = p.mass;
-  const float m_h = m / h, J_h = p.yaw_inertia / h, Iw_h = p.wheel_inertia / h + c;
+  const float m_h = pre.m_h, J_h = pre.J_h, Iw_h = pre.Iw_h;
   const float eps2 = p.slip_eps * p.slip_eps, aa = a * a, bb = b * b;
   const float wmax = p.wheel_speed_max;
   const float2 R2 = bc(R), RR2 = bc(R * R), Iwh2 = bc(Iw_h), nc2 = bc(-c), mu2 = bc(p.mu_n);
   float2 wL = make_float2(s.w[0], s.w[1]), wR = make_float2(s.w[2], s.w[3]);   // left / right side, (front, rear)
   const float2 tL = make_float2(tau[0], tau[1]), tR = make_float2(tau[2], tau[3]);
-  float sn, cs;
-  sincosf(s.yaw, &sn, &cs);
+  float sn = pre.sn, cs = pre.cs;
 #pragma unroll 1
   for (int it = 0; it < p.decimation; ++it) {
     const float vx = s.vx, vy = s.vy, r = s.r;
@@ -177,6 +190,9 @@ __device__ __forceinline__ void skid_steps(Skid& s, const float tau[4], const Oi
     s.py += h * (s.vx * sn + s.vy * cs);
   }
   s.w[0] = wL.x; s.w[1] = wL.y; s.w[2] = wR.x; s.w[3] = wR.y;
+}
+__device__ __forceinline__ void skid_steps(Skid& s, const float tau[4], const OisEnvParams& p) {
+  skid_steps(s, tau, p, skid_prepare(s.yaw, p));
 }
 
 // warp-level sum

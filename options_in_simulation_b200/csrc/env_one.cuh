@@ -35,8 +35,11 @@ __device__ __forceinline__ void env_load(const OisEnvState& st, const OisEnvIO& 
 }
 
 // returns 1 when the env was reset this step
+// `act_fn()` yields the env's action row; it is called as late as the arithmetic allows, so that a caller whose actions
+// arrive late (it may block in there) has everything that depends on the state alone behind it by then.
+template <class ActFn>
 __device__ __forceinline__ int env_one_direct(const OisEnvParams& p, const OisEnvState& st, const OisEnvIO& io, const EnvDerived& dv,
-                                              const int64_t n, const int64_t i, const EnvLoaded& L,
+                                              const int64_t n, const int64_t i, const EnvLoaded& L, ActFn&& act_fn,
                                               const bool defer_obs_clipped, float (&obs_clipped_out)[6]) {
   constexpr bool kStats = false, kEval = false;
   float acc[OIS_EP_STATS_LEN] = {};     // dead (kStats is false): keeps the shared text compiling
@@ -49,17 +52,6 @@ __device__ __forceinline__ int env_one_direct(const OisEnvParams& p, const OisEn
   const float4 wv = L.wv;
   float4 cmd = L.cmd;
   int64_t sim = L.sim;
-  float a4[4];
-  {
-    const float4 a = L.act;
-    if (p.act_dim == 4) { a4[0] = a.x; a4[1] = a.y; a4[2] = a.z; a4[3] = a.w; }            // KAMMA_medium.py:600
-    else if (p.act_dim == 2) { a4[0] = a.x; a4[1] = a.x; a4[2] = a.y; a4[3] = a.y; }       // KA_DDPG_2D.py:624
-    else { a4[0] = a4[1] = a4[2] = a4[3] = a.x; }                                          // KA_DDPG_1D.py:600
-  }
-  if (io.clip_actions > 0.f) {      // VecEnvRLGames.step clamps the actions before pre_physics_step (clipActions)
-#pragma unroll
-    for (int j = 0; j < 4; ++j) a4[j] = clipf(a4[j], -io.clip_actions, io.clip_actions);
-  }
   const bool need_mask_draw = p.blend == OIS_BLEND_SWITCH && io.rand_mask == nullptr;
 
   // ------------------------------------------------------------------ pre_physics_step :604-636
@@ -75,16 +67,36 @@ __device__ __forceinline__ int env_one_direct(const OisEnvParams& p, const OisEn
   const float g1 = gamma_assist(p.gamma1_mode, p.gamma1_const, decay);
   const float g2 = gamma_assist(p.gamma2_mode, p.gamma2_const, decay);
   float tq[4], wt[4];
+  float mask = 0.f, nmask = 0.f, ng = 0.f;
   if (p.blend == OIS_BLEND_SWITCH) {          // :632-636
     const float rm = need_mask_draw ? u01(philox2x32((uint32_t)i, (uint32_t)env_philox_offset(io),
                                                      (uint32_t)io.philox_seed ^ (uint32_t)(io.philox_seed >> 32) ^ (uint32_t)(i >> 32)))
                                     : __ldcs(io.rand_mask + i);
-    const float mask = rm < g1 ? 1.0f : 0.0f;
-    const float nmask = sub(1.0f, mask);
+    mask = rm < g1 ? 1.0f : 0.0f;
+    nmask = sub(1.0f, mask);
+  } else {                                    // KA_DDPG_1D.py:632-633
+    ng = sub(1.0f, g1);
+  }
+  // calculate_metrics :770 — linear_acc lags a step: it uses the pre-physics projection
+  const float lin_acc = cdiv(sub(current_v, tp.z), dv.dt);
+  SkidPre skid_pre = {};
+  if (p.physics) skid_pre = skid_prepare(pv.z, p);
+  // ------------------------------------------------------------------ the actions (everything above needs the state alone)
+  float a4[4];
+  {
+    const float4 a = act_fn();
+    if (p.act_dim == 4) { a4[0] = a.x; a4[1] = a.y; a4[2] = a.z; a4[3] = a.w; }            // KAMMA_medium.py:600
+    else if (p.act_dim == 2) { a4[0] = a.x; a4[1] = a.x; a4[2] = a.y; a4[3] = a.y; }       // KA_DDPG_2D.py:624
+    else { a4[0] = a4[1] = a4[2] = a4[3] = a.x; }                                          // KA_DDPG_1D.py:600
+  }
+  if (io.clip_actions > 0.f) {      // VecEnvRLGames.step clamps the actions before pre_physics_step (clipActions)
+#pragma unroll
+    for (int j = 0; j < 4; ++j) a4[j] = clipf(a4[j], -io.clip_actions, io.clip_actions);
+  }
+  if (p.blend == OIS_BLEND_SWITCH) {
 #pragma unroll
     for (int j = 0; j < 4; ++j) tq[j] = add(mul(mask, crit[j]), mul(nmask, mul(a4[j], p.action_scale)));
-  } else {                                    // KA_DDPG_1D.py:632-633
-    const float ng = sub(1.0f, g1);
+  } else {
 #pragma unroll
     for (int j = 0; j < 4; ++j) tq[j] = add(mul(mul(ng, a4[j]), p.action_scale), mul(g1, crit[j]));
   }
@@ -112,8 +124,6 @@ __device__ __forceinline__ int env_one_direct(const OisEnvParams& p, const OisEn
     c[19] = g2; c[26] = guiding; c[28] = g1;
   }
   const float r3 = add(add(add(mul(wt[0], wt[0]), mul(wt[1], wt[1])), mul(wt[2], wt[2])), mul(wt[3], wt[3]));
-  // calculate_metrics :770 — linear_acc lags a step: it uses the pre-physics projection
-  const float lin_acc = cdiv(sub(current_v, tp.z), dv.dt);
   float smooth = 0.f;
   if (kEval) {                                // KAMMA_eval.py:677-685
     float4 ot = ld_stream4(st.old_torques + 4 * i);
@@ -139,7 +149,7 @@ __device__ __forceinline__ int env_one_direct(const OisEnvParams& p, const OisEn
   s.px = pv.x; s.py = pv.y; s.yaw = pv.z; s.vx = pv.w; s.vy = tp.x; s.r = tp.y;
   s.w[0] = wv.x; s.w[1] = wv.y; s.w[2] = wv.z; s.w[3] = wv.w;
   ENV_ONE_STAMP(31);
-  if (p.physics) skid_steps(s, wt, p);
+  if (p.physics) skid_steps(s, wt, p, skid_pre);
   ENV_ONE_STAMP(32);
 
   // ------------------------------------------------------------------ group B: issued one iteration ago

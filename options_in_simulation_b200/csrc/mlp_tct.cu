@@ -487,8 +487,6 @@ tct_actor_kernel(const __grid_constant__ Args args, const __grid_constant__ EnvF
         static_assert(sizeof(StepCtlNext) <= 2 * kInPad * 4, "StepCtlNext is parked in the scaler constants");
         if (advance && lane == 0) *s_next = step_ctl_next(ef.io.ctl);
         TCT_STAMP(tr && tiles_done == 0, 28);
-        wait(act_ready, par);
-        TCT_STAMP(tr && tiles_done == 0, 29);
         const float* sa_ = s_out + par * (NT * 8);
         // The wrapper's observations [n, 6] (what the host reads back — pinned HOST memory in the host-in-the-loop mode) of a
         // full tile leave as whole 16-byte pieces of one contiguous block, staged through shared memory, instead of three
@@ -500,9 +498,15 @@ tct_actor_kernel(const __grid_constant__ Args args, const __grid_constant__ EnvF
           const int r = lane + 32 * h;
           const int64_t i = t0 + r;
           if (i < ef.n) {
-            el[h].act = *reinterpret_cast<const float4*>(sa_ + r * 8);
             float oc[6];
-            env_one_direct(ef.p, ef.st, ef.io, ef.dv, ef.n, i, el[h], oc_wide, oc);
+            // the env's arithmetic up to the first use of its actions runs while the MLP is still busy; act_ready is waited
+            // for inside (a completed phase: a second wait of the same parity returns at once)
+            auto actions = [&]() {
+              wait(act_ready, par);
+              TCT_STAMP(tr && tiles_done == 0 && h == 0, 29);
+              return *reinterpret_cast<const float4*>(sa_ + r * 8);
+            };
+            env_one_direct(ef.p, ef.st, ef.io, ef.dv, ef.n, i, el[h], actions, oc_wide, oc);
             if (oc_wide) {
 #pragma unroll
               for (int k = 0; k < 6; k += 2) *reinterpret_cast<float2*>(s_stage + r * 6 + k) = make_float2(oc[k], oc[k + 1]);

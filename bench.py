@@ -449,7 +449,7 @@ def kernels_back_to_back(world, reps=20):
     return b.elapsed_time(c) / reps, a.elapsed_time(b) / reps
 
 
-def actor_device_span(world, flush, reps=9):
+def actor_device_span(world, flush, reps=9, fused=False):
     """Duration of the transposed actor kernel on the device's own clock: %globaltimer of the first CTA's start to the
     last warp's exit (diagnostic stamps of csrc/mlp_tct.cu), median over `reps` flushed steps.  An event pair around ONE
     kernel reads ~6 us more than this (front-end latency of the two records, profiles/micro/launch_overhead.cu)."""
@@ -464,7 +464,7 @@ def actor_device_span(world, flush, reps=9):
         if lib.ois_debug_tct_trace_reset() != 0:
             return None
         flush.zero_()
-        world.step()
+        world.step_fused() if fused else world.step()
         torch.cuda.synchronize()
         buf = (ctypes.c_ulonglong * 64)()
         lib.ois_debug_tct_trace(buf, 64)
@@ -596,10 +596,11 @@ def update_timed(world, iters=30):
 
 
 def train_timed(world, flush, steps=30):
-    """One policy step followed by two updates (the reference trainer's cadence), device-timed."""
+    """One policy step (the one-launch step the trainer issues, rollout.fused_step) followed by two updates (the reference
+    trainer's cadence), device-timed."""
     torch = world.torch
     for _ in range(3):
-        world.step()
+        world.step_fused()
         world.agent._update(world.t, world.T)
         world.agent._update(world.t, world.T)
     ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
@@ -607,7 +608,7 @@ def train_timed(world, flush, steps=30):
     for a, b in ev:
         flush.zero_()
         a.record()
-        world.step()
+        world.step_fused()
         world.agent._update(world.t, world.T)
         world.agent._update(world.t, world.T)
         b.record()
@@ -935,6 +936,25 @@ def main():
         dom, other = (act_roof, env_roof) if act_ms >= env_ms else (env_roof, act_roof)
         out["roofline"] = dom
         out["roofline_other"] = other
+        if issue.startswith("rollout.fused_step") or graph_kernels_per_step == 1:
+            # the timed step is ONE kernel (actor MLP + env step + replay append): that launch is the dominant kernel, its
+            # duration between events is the step itself; the two kernels it replaces stay in the line for comparison
+            fspan = actor_device_span(world, flush, fused=True)
+            fused_roof = {"kernel": "tct_actor_kernel<32, kEnv> (csrc/mlp_tct.cu): actor MLP + env step + replay append, the ONE launch "
+                                    "of the timed step",
+                          "bound": "tensor", "achieved": act_flop / (ms * 1e-3) / 1e12, "peak": tc_peak, "unit": "TFLOP/s",
+                          "traffic": tr("fused"), "ms": ms, "also_hbm_bytes": env_bytes,
+                          "ms_note": "ms: CUDA events around the one launch = the timed step (max over ranks); the env step's "
+                                     "algorithmic bytes ride in the same launch (also_hbm_bytes)",
+                          "peak_source": peak_src, "traffic_source": traffic_src}
+            fused_roof["frac"] = fused_roof["achieved"] / tc_peak
+            if fspan:
+                fused_roof["device_span_ms"] = fspan
+                fused_roof["achieved_device_span"] = act_flop / (fspan * 1e-3) / 1e12
+                fused_roof["frac_device_span"] = fused_roof["achieved_device_span"] / tc_peak
+            out["roofline"] = fused_roof
+            out["roofline_other"] = act_roof
+            out["roofline_env"] = env_roof
         if not args.no_extras and world_size == 1:
             scale = []
             del world

@@ -19,7 +19,8 @@ for spec in sys.argv[1:]:
     scale = {"byte": 1, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
     seen = {}
     for r in rows[2:]:
-        kind = "env" if "env_step_kernel" in r[ik] else "actor" if "actor_kernel" in r[ik] else None
+        kind = ("env" if "env_step_kernel" in r[ik] else "fused" if "actor_kernel<32, 1>" in r[ik]      # kEnv: actor + env step
+                else "actor" if "actor_kernel" in r[ik] else None)
         if kind is None:
             continue
         b = float(r[ir].replace(",", "")) * scale[units[ir]] + float(r[iw].replace(",", "")) * scale[units[iw]]

@@ -17,11 +17,11 @@ world = bench.World(wl, 4096, "bf16", torch.device("cuda", 0), seed=1)
 if profiled:
     world.agent.cfg["graph_update"] = False
 for _ in range(300 // max(1, 4096 // 512) + 3):      # fill enough transitions for a 512 batch
-    world.step()
+    world.step_fused()
 
 
 def train_step():
-    world.step()
+    world.step_fused()
     world.agent._update(world.t, world.T)
     world.agent._update(world.t, world.T)
 

@@ -20,7 +20,10 @@
 
 namespace ois {
 
-constexpr int kEnvThreads = 128;
+#ifndef OIS_ENV_THREADS
+#define OIS_ENV_THREADS 128
+#endif
+constexpr int kEnvThreads = OIS_ENV_THREADS;
 #ifndef OIS_ENV_MIN_BLOCKS
 #define OIS_ENV_MIN_BLOCKS 5
 #endif
@@ -477,7 +480,11 @@ reset_idx_kernel(const __grid_constant__ OisEnvParams p, const __grid_constant__
 
 static int grid_for(int64_t n, int threads) {
   int64_t blocks = (n + threads - 1) / threads;
-  static const int waves = getenv("OIS_ENV_WAVES") ? atoi(getenv("OIS_ENV_WAVES")) : 8;   // measured: 2 -> 8 waves = 63.6 -> 70.3 % of HBM at 4M envs (tail balance)
+  // waves of resident CTAs (tail balance against per-thread prefetch depth), measured on B200 (profiles/env_waves_sweep.py):
+  // 1M envs 3 / 4 / 6 / 8 / 12 / 16 waves = 64.9 / 66.8 / 67.9 / 67.0 / 65.4 / 65.4 % of measured HBM; 4M envs 4 / 8 / 16 =
+  // 68.3 / 71.5 / 73.0 %.  Block sizes 64 / 96 / 256 at equal warps per SM change nothing.
+  static const int waves_env = getenv("OIS_ENV_WAVES") ? atoi(getenv("OIS_ENV_WAVES")) : 0;
+  const int waves = waves_env > 0 ? waves_env : (n >= ((int64_t)1 << 21) ? 16 : 8);
   const int64_t cap = (int64_t)num_sms() * kEnvMinBlocks * waves;   // `waves` waves of resident CTAs; grid-stride beyond
   if (blocks > cap) blocks = cap;
   if (blocks < 1) blocks = 1;

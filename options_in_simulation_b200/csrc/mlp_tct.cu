@@ -249,6 +249,11 @@ tct_actor_kernel(const __grid_constant__ Args args, const __grid_constant__ EnvF
         for (int s = 0; s < kStagesPerTile; ++s, ++n) {
           if ((int)(n & 1) != p) continue;
           const int slot = n % kSlots;
+          // The first two stages go out at once; the rest of the first ring fill waits until the first tile's X operand is
+          // written.  All CTAs filling their rings at the same moment is 20 MB through the L2 -> SM fabric (~1.7 us at
+          // ~6300 B/clk chip-wide), and the tile's few hundred bytes of observations queue behind it: they are the head of
+          // the whole dependent chain, the weights of stage k are not needed before ~0.6 + 0.4 k us after X.
+          if (n == 2 || n == 3) wait(x_ready, 0);
           wait(&empty[slot], ((n / kSlots) & 1) ^ 1);
           // W2 tile (mb, kb) in kb-major order; W3 tile kb.  Tile-blocked image: [row block][k chunk][128 rows][8]
           const size_t src = s < 16 ? kImgW2 + (size_t)((s & 3) * 64 + (s >> 2) * 16) * 2048 : kImgW3 + (size_t)((s - 16) * 16) * 2048;
@@ -282,13 +287,14 @@ tct_actor_kernel(const __grid_constant__ Args args, const __grid_constant__ EnvF
       if (i < kBiasTotal) s_bias[i] = bv[k];
     }
   }
-  if (warp == kWarpAux) {   // RunningStandardScaler constants: mean.float(), sqrt(var.float()) + eps
-    const int c = lane & (kInPad - 1);
-    const bool is_mean = lane < kInPad;
-    float v = is_mean ? 0.f : 1.f;
-    if (args.mean != nullptr && c < args.in_dim) v = is_mean ? (float)args.mean[c] : __fadd_rn(sqrtf((float)args.var[c]), 1e-8f);
-    s_scale[lane] = v;
-  }
+  // RunningStandardScaler constants (in_dim <= 8): s_scale[0..7] = mean.float(), [8..15] = d = sqrt(var.float()) + eps,
+  // [16..23] = RN(1 / d).  The auxiliary warp REQUESTS them here and consumes them only after it has issued the
+  // observation copies below: a cold load (0.7 us after an L2 flush) between the kernel's start and the first observation
+  // request would sit on the critical path of the whole tile.
+  const int sc_kind = lane >> 3, sc_c = lane & 7;
+  const bool sc_live = warp == kWarpAux && args.mean != nullptr && sc_kind < 3 && sc_c < args.in_dim;
+  double sc_raw = 0.0;
+  if (sc_live) sc_raw = sc_kind == 0 ? args.mean[sc_c] : args.var[sc_c];
   // auxiliary warp: the raw observations of its next tile travel global -> shared asynchronously (LDGSTS), each lane its
   // own rows.  (Held in registers across the set-up barrier and the MLP they were spilled by ptxas in the kEnv build, and
   // the spill store waits for the load: 2.4 us of exposed HBM latency before the first MMA.)
@@ -323,6 +329,14 @@ tct_actor_kernel(const __grid_constant__ Args args, const __grid_constant__ EnvF
     TCT_STAMP(tr, 25);
     if (lane == 0) pdl_trigger();
     if ((int)blockIdx.x < num_tiles) load_x(blockIdx.x);
+    asm volatile("" : "+d"(sc_raw));      // the scaler constants are consumed from here on (after the copies were issued)
+    float v = sc_kind == 0 ? 0.f : 1.f;
+    if (sc_live && sc_kind == 0) v = (float)sc_raw;
+    if (sc_live && sc_kind != 0) {
+      v = __fadd_rn(sqrtf((float)sc_raw), 1e-8f);
+      if (sc_kind == 2) v = __frcp_rn(v);
+    }
+    s_scale[lane] = v;
   }
   TCT_STAMP(tr && (warp == 0 || warp >= kWarpMma), warp == 0 ? 34 : warp == kWarpMma ? 35 : 36);
   ptx::tc_fence_before();
@@ -428,8 +442,10 @@ tct_actor_kernel(const __grid_constant__ Args args, const __grid_constant__ EnvF
     uint32_t tiles_done = 0;
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++tiles_done) {
       const uint32_t par = tiles_done & 1;
+      TCT_STAMP(tr && tiles_done == 0, 42);
       ptx::cp_async_wait_all();                                // every lane's copies have landed ...
       __syncwarp();                                            // ... before any lane reads the rows others fetched
+      TCT_STAMP(tr && tiles_done == 0, 43);
 #pragma unroll
       for (int h = 0; h < kRowsPerLane; ++h) {
         const bool live = (int64_t)tile * NT + lane + 32 * h < args.rows;
@@ -442,14 +458,24 @@ tct_actor_kernel(const __grid_constant__ Args args, const __grid_constant__ EnvF
       for (int h = 0; h < kRowsPerLane; ++h) {
         const int r = lane + 32 * h;
         if (args.mean != nullptr) {
+          // (x - mean) / d as q0 = t rc, q = q0 + (t - d q0) rc: the correctly rounded quotient for all but rare operands
+          // (<= 1 ulp otherwise), three dependent FMA-pipe instructions instead of the IEEE division's ~12 with a
+          // slow-path call — this warp's few hundred instructions run once per launch from a cold instruction cache and
+          // head the tile's whole dependent chain.  The result is rounded to bf16 right below.  (Padding columns: mean 0,
+          // d = rc = 1.)
 #pragma unroll
-          for (int j = 0; j < 8; ++j)
-            if (j < args.in_dim) x[h][j] = fminf(fmaxf(__fdiv_rn(__fsub_rn(x[h][j], s_scale[j]), s_scale[kInPad + j]), -5.0f), 5.0f);
+          for (int j = 0; j < 8; ++j) {
+            const float t = __fsub_rn(x[h][j], s_scale[j]), d = s_scale[8 + j], rc = s_scale[16 + j];
+            const float q0 = __fmul_rn(t, rc);
+            const float q = fabsf(q0) < 1e30f ? __fmaf_rn(__fmaf_rn(-d, q0, t), rc, q0) : q0;
+            x[h][j] = fminf(fmaxf(q, -5.0f), 5.0f);
+          }
         }
         *reinterpret_cast<uint4*>(s_x + r * 16) = make_uint4(ptx::pack_bf16(x[h][0], x[h][1]), ptx::pack_bf16(x[h][2], x[h][3]),
                                                              ptx::pack_bf16(x[h][4], x[h][5]), ptx::pack_bf16(x[h][6], x[h][7]));
         *reinterpret_cast<uint4*>(s_x + NT * 16 + r * 16) = make_uint4(0u, 0u, 0u, 0u);     // k 8..15 (in_dim <= 8)
       }
+      TCT_STAMP(tr && tiles_done == 0, 44);
       ptx::fence_async_smem();
       __syncwarp();
       if (lane == 0) ptx::mbar_arrive(x_ready);

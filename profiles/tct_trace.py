@@ -95,7 +95,7 @@ for fused in (True, False):
             f"L2 issued {(buf[8] - t0) / 1e3:.2f}, done {(buf[23] - t0) / 1e3:.2f}; set-up done {(buf[1] - t0) / 1e3:.2f}, aux before / after "
             f"griddepcontrol.wait {(buf[24] - t0) / 1e3:.2f} / {(buf[25] - t0) / 1e3:.2f}; env part: loads issued {(buf[28] - t0) / 1e3:.2f}, "
             f"actions seen {(buf[29] - t0) / 1e3:.2f}, envs stepped {(buf[30] - t0) / 1e3:.2f} "
-            f"[at the set-up barrier: warp 0 {(buf[34] - t0) / 1e3:.2f}, MMA warp {(buf[35] - t0) / 1e3:.2f} (before tmem alloc {(buf[37] - t0) / 1e3:.2f}), aux warp {(buf[36] - t0) / 1e3:.2f}] "
+            f"[aux after the barrier: enters its loop {(buf[42] - t0) / 1e3:.2f}, copies landed {(buf[43] - t0) / 1e3:.2f}, X computed {(buf[44] - t0) / 1e3:.2f}] [at the set-up barrier: warp 0 {(buf[34] - t0) / 1e3:.2f}, MMA warp {(buf[35] - t0) / 1e3:.2f} (before tmem alloc {(buf[37] - t0) / 1e3:.2f}), aux warp {(buf[36] - t0) / 1e3:.2f}] "
             f"(sub-steps begin {(buf[31] - t0) / 1e3:.2f}, end {(buf[32] - t0) / 1e3:.2f}, final stores {(buf[33] - t0) / 1e3:.2f})")
       ev = [torch.cuda.Event(enable_timing=True) for _ in range(3)]
       if cold:

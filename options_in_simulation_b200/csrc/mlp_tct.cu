@@ -230,6 +230,7 @@ tct_actor_kernel(const __grid_constant__ Args args, const __grid_constant__ EnvF
   if (warp == 0) {
     __syncwarp();
     asm volatile("bar.arrive 2, 96;" ::: "memory");
+    asm volatile("bar.arrive 3, 64;" ::: "memory");     // ... and the auxiliary warp (its x_ready / noise_ready arrivals)
   }
   if (warp == kWarpProd || warp == kWarpProd + 1) {
     // ===================================================== producers: one 32 KB weight tile per ring slot, the two threads
@@ -266,13 +267,17 @@ tct_actor_kernel(const __grid_constant__ Args args, const __grid_constant__ EnvF
   }
   TCT_STAMP(tr && warp == kWarpMma, 37);
   if (warp == kWarpMma) ptx::tmem_alloc<C::kTmemCols>(tmem_slot);
-  if (warp < kEpiWarps) {   // biases, fp32, from the master parameters; all loads of a thread in flight at once
+  // Biases, fp32, from the master parameters: REQUESTED here (all loads of a thread in flight at once), consumed after the
+  // set-up barrier — nobody waits at the barrier for a cold load.  Thread t's first two values are the layer-1 / layer-2
+  // biases of the feature it owns in the epilogue (bv[0], bv[1] stay in registers); layers 3 / 4 read the third through
+  // shared memory (written after the barrier; its readers come through later mbarrier waits).
+  constexpr int kBiasIters = (kBiasTotal + kEpiWarps * 32 - 1) / (kEpiWarps * 32);
+  float bv[kBiasIters] = {};
+  if (warp < kEpiWarps) {
     const int64_t b0 = (int64_t)kH0 * args.in_dim, w1 = b0 + kH0, b1 = w1 + (int64_t)kH1 * kH0, w2 = b1 + kH1;
     const int64_t b2 = w2 + (int64_t)kH2 * kH1, w3 = b2 + kH2, b3 = w3 + (int64_t)args.out_dim * kH2;
-    constexpr int kIters = (kBiasTotal + kEpiWarps * 32 - 1) / (kEpiWarps * 32);
-    float bv[kIters];
 #pragma unroll
-    for (int k = 0; k < kIters; ++k) {
+    for (int k = 0; k < kBiasIters; ++k) {
       const int i = threadIdx.x + k * kEpiWarps * 32;
       float v = 0.f;
       if (i < kH0) v = __ldg(args.params + b0 + i);
@@ -280,11 +285,6 @@ tct_actor_kernel(const __grid_constant__ Args args, const __grid_constant__ EnvF
       else if (i < kH0 + kH1 + kH2) v = __ldg(args.params + b2 + i - kH0 - kH1);
       else if (i < kBiasTotal && (i - kH0 - kH1 - kH2) < args.out_dim) v = __ldg(args.params + b3 + i - kH0 - kH1 - kH2);
       bv[k] = v;
-    }
-#pragma unroll
-    for (int k = 0; k < kIters; ++k) {
-      const int i = threadIdx.x + k * kEpiWarps * 32;
-      if (i < kBiasTotal) s_bias[i] = bv[k];
     }
   }
   // RunningStandardScaler constants (in_dim <= 8): s_scale[0..7] = mean.float(), [8..15] = d = sqrt(var.float()) + eps,
@@ -337,16 +337,29 @@ tct_actor_kernel(const __grid_constant__ Args args, const __grid_constant__ EnvF
       if (sc_kind == 2) v = __frcp_rn(v);
     }
     s_scale[lane] = v;
+    // this warp does not join the set-up barrier below: it needs neither the TMEM address nor the biases, only the
+    // initialised mbarriers (named barrier 3 with warp 0) — X is then written as soon as the observations have landed
+    asm volatile("bar.sync 3, 64;" ::: "memory");
   }
   TCT_STAMP(tr && (warp == 0 || warp >= kWarpMma), warp == 0 ? 34 : warp == kWarpMma ? 35 : 36);
-  ptx::tc_fence_before();
-  asm volatile("bar.sync 1, 576;" ::: "memory");      // all warps but the two producers
-  ptx::tc_fence_after();
-  const uint32_t tmem = *tmem_slot;
+  uint32_t tmem = 0;
+  if (warp != kWarpAux) {
+    ptx::tc_fence_before();
+    asm volatile("bar.sync 1, 544;" ::: "memory");      // epilogue warps + the MMA warp
+    ptx::tc_fence_after();
+    tmem = *tmem_slot;
+  }
   TCT_STAMP(tr && warp == 0, 1);
   if (args.debug == 1) {
     if (warp == kWarpMma) ptx::tmem_dealloc<C::kTmemCols>(tmem);
     return;
+  }
+  if (warp < kEpiWarps) {
+#pragma unroll
+    for (int k = 2; k < kBiasIters; ++k) {
+      const int i = threadIdx.x + k * kEpiWarps * 32;
+      if (i < kBiasTotal) s_bias[i] = bv[k];
+    }
   }
 
   if (warp == kWarpMma) {
@@ -526,7 +539,9 @@ tct_actor_kernel(const __grid_constant__ Args args, const __grid_constant__ EnvF
           if (i < ef.n) {
             float oc[6];
             // the env's arithmetic up to the first use of its actions runs while the MLP is still busy; act_ready is waited
-            // for inside (a completed phase: a second wait of the same parity returns at once)
+            // for inside (a completed phase: a second wait of the same parity returns at once).  (A dry pass of the same
+            // code on made-up actions beforehand, to warm the instruction cache, was measured: no gain — this part is bound
+            // by its dependent chains.)
             auto actions = [&]() {
               wait(act_ready, par);
               TCT_STAMP(tr && tiles_done == 0 && h == 0, 29);
@@ -600,7 +615,7 @@ tct_actor_kernel(const __grid_constant__ Args args, const __grid_constant__ EnvF
       // ---- layer 1 block g -> H1 block g
       wait(&d1_full[g], par);
       ptx::tc_fence_after();
-      block_to_h(C::kColD1 + g * NT, s_bias[g * 128 + f], hdst);
+      block_to_h(C::kColD1 + g * NT, bv[0], hdst);
       ptx::fence_async_smem();
       warp_arrive(&h1_ready[g]);
       TCT_STAMP(tr && q == 0 && tiles_done == 0, 12 + g);
@@ -608,7 +623,7 @@ tct_actor_kernel(const __grid_constant__ Args args, const __grid_constant__ EnvF
       wait(d2_full, par);
       ptx::tc_fence_after();
       TCT_STAMP(tr && q == 0 && g == 0 && tiles_done == 0, 16);
-      block_to_h(C::kColD2 + g * NT, s_bias[kH0 + g * 128 + f], hdst);
+      block_to_h(C::kColD2 + g * NT, bv[1], hdst);
       ptx::fence_async_smem();
       warp_arrive(&h2_ready[g]);
       TCT_STAMP(tr && q == 0 && tiles_done == 0, 17 + g);
@@ -667,8 +682,11 @@ tct_actor_kernel(const __grid_constant__ Args args, const __grid_constant__ EnvF
             float a[8];
 #pragma unroll
             for (int j = 0; j < 8; ++j) {
-              const float z = so[r * 8 + j] + b4[j];
-              a[j] = args.out_act == OIS_ACT_SIGMOID ? sigmoid_fast(z) : args.out_act == OIS_ACT_TANH ? tanh_fast(z) : z;
+              a[j] = 0.f;
+              if (j < A) {      // (warp-uniform: the outputs beyond act_dim are never stored)
+                const float z = so[r * 8 + j] + b4[j];
+                a[j] = args.out_act == OIS_ACT_SIGMOID ? sigmoid_fast(z) : args.out_act == OIS_ACT_TANH ? tanh_fast(z) : z;
+              }
             }
             if (row_noise) {
               if (applied) {
@@ -716,7 +734,7 @@ tct_actor_kernel(const __grid_constant__ Args args, const __grid_constant__ EnvF
   }
   // ---- teardown (the producers have left; their last copy was consumed by the last layer-3 MMA)
   ptx::tc_fence_before();
-  asm volatile("bar.sync 1, 576;" ::: "memory");
+  asm volatile("bar.sync 4, 576;" ::: "memory");
   if (warp == kWarpMma) ptx::tmem_dealloc<C::kTmemCols>(tmem);
   if (lane == 0) {     // diagnostics: every warp's exit time
     unsigned long long t;

@@ -21,6 +21,7 @@ ncu --set full --clock-control none --import-source on -k regex:'env_step_kernel
     -o gpurun_out/${tag}_full_1m -f python bench.py --envs 1048576 --steps 6 --warmup 3 --no-extras > gpurun_out/${tag}_ncu_full_1m.log 2>&1; echo "ncu full 1m exit $?"
 ncu --set full --clock-control none --import-source on -k regex:tct_actor_kernel -s 20 -c 2 \
     -o gpurun_out/${tag}_full_fused -f python profiles/fused_probe.py > gpurun_out/${tag}_ncu_full_fused.log 2>&1; echo "ncu full fused exit $?"
+python profiles/step_hist.py > gpurun_out/${tag}_step_hist.txt 2>&1; echo "step hist exit $?"
 python profiles/e2e_trace.py > gpurun_out/${tag}_e2e_trace.txt 2>&1; echo "e2e trace exit $?"
 python profiles/tct_trace.py 4096 > gpurun_out/${tag}_tct_trace_4096.txt 2>&1; echo "trace exit $?"
 python profiles/update_phases.py > gpurun_out/${tag}_update_phases.json 2>&1; echo "phases exit $?"

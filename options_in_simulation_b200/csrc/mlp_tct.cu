@@ -88,12 +88,15 @@ __device__ __forceinline__ void stamp(int slot) {
 }
 #define TCT_STAMP(cond, slot) do { if (cond) stamp(slot); } while (0)
 
+// Suspend-time hint of every mbarrier wait below.  Measured (OIS_TCT_DEBUG_MODE=4): layer 3's MMAs take 48 cycles each with
+// the other warps parked and 108 with 16 epilogue warps re-polling d3_full at the default (short) time limit.
+constexpr uint32_t kWaitHintNs = 20000;
 // mbarrier wait that cannot hang the GPU: a protocol bug traps after ~2^27 failed polls instead of spinning forever.
 // (No printf in the product build: a kernel that contains one pays several microseconds per launch for the print FIFO.)
 __device__ __forceinline__ void wait(uint64_t* bar, uint32_t parity) {
   uint32_t polls = 0;
-  while (!ptx::mbar_try_wait(bar, parity)) {
-    if (++polls > (1u << 27)) {
+  while (!ptx::mbar_try_wait_hint(bar, parity, kWaitHintNs)) {
+    if (++polls > (1u << 24)) {
 #ifdef OIS_TCT_DEBUG
       printf("tct_actor_kernel: barrier at shared 0x%x of CTA %d never completed (warp %d)\n", ptx::smem_u32(bar), blockIdx.x,
              threadIdx.x >> 5);
@@ -260,6 +263,7 @@ tct_actor_kernel(const __grid_constant__ Args args, const __grid_constant__ EnvF
           const size_t src = s < 16 ? kImgW2 + (size_t)((s & 3) * 64 + (s >> 2) * 16) * 2048 : kImgW3 + (size_t)((s - 16) * 16) * 2048;
           ptx::mbar_expect_tx(&full[slot], kSlotBytes);
           ptx::bulk_g2s(s_ring + slot * kSlotBytes, args.image + src, kSlotBytes, &full[slot]);
+          TCT_STAMP(blockIdx.x == 0 && n >= 12 && n < 20, 40 + n);     // 52..59: stages 12..19 requested
         }
       }
     }
@@ -363,8 +367,14 @@ tct_actor_kernel(const __grid_constant__ Args args, const __grid_constant__ EnvF
   }
 
   if (warp == kWarpMma) {
-    // ===================================================== MMA issuer
+    // ===================================================== MMA issuer: ONE elected thread runs the whole issue loop.
+    // What the issuing thread does BETWEEN two tiles is not hidden by the tensor pipe's queue — measured with the other
+    // warps parked (OIS_TCT_DEBUG_MODE, since removed): layer 3's 32 MMAs take 47 cycles each issued back to back and 85 in
+    // a loop that per tile re-converged the warp, waited with all 32 lanes and rebuilt sixteen descriptors.  So: no
+    // warp-wide step inside a layer (the other 31 lanes wait at a __syncwarp per layer), descriptors by one addition from
+    // the tile's first (the address field is the low 14 bits of `lo`; ring and H lie below 256 KB, so no carry).
     const bool leader = ptx::elect_one();
+    const bool trl = blockIdx.x == 0;
     const uint32_t id_k = ptx::idesc_bf16(128, NT);                 // A, B K-major (layer 1: B = X)
     const uint32_t id_n = id_k | (1u << 16);                        // B env-major (MN-major)
     constexpr uint32_t hi_a = ptx::smem_desc_hi(128);               // K-major: SBO = next 8 rows
@@ -374,78 +384,83 @@ tct_actor_kernel(const __grid_constant__ Args args, const __grid_constant__ EnvF
     const uint32_t x_lo = ptx::smem_desc_lo(ptx::smem_u32(s_x), NT * 16);
     const uint32_t w1a = ptx::smem_u32(s_w1), w4a = ptx::smem_u32(s_w4);
     uint32_t tiles_done = 0, n = 0;
-    wait(wconst_full, 0);
+    if (leader) wait(wconst_full, 0);
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++tiles_done) {
       const uint32_t par = tiles_done & 1;
-      if (tiles_done > 0) { wait(tile_done, par ^ 1); }
-      // ---- layer 1: four 128-feature blocks, K = 16 (one MMA each)
-      wait(x_ready, par);
-      ptx::tc_fence_after();
-      TCT_STAMP(tr && tiles_done == 0, 3);
       if (leader) {
+        if (tiles_done > 0) wait(tile_done, par ^ 1);
+        // ---- layer 1: four 128-feature blocks, K = 16 (one MMA each)
+        wait(x_ready, par);
+        ptx::tc_fence_after();
+        TCT_STAMP(trl && tiles_done == 0, 3);
 #pragma unroll
         for (int mb = 0; mb < 4; ++mb) {
           ptx::mma_ss(tmem + C::kColD1 + mb * NT, ptx::make_desc(ptx::smem_desc_lo(w1a + mb * 4096, 2048), hi_a),
                       ptx::make_desc(x_lo, hi_a), id_k, false);
           ptx::mma_commit(&d1_full[mb]);
         }
-      }
-      __syncwarp();
-      // ---- layer 2: kb-outer; tile (mb, kb) of W2 from the ring, B = block kb of H1
+        // ---- layer 2: kb-outer; tile (mb, kb) of W2 from the ring, B = block kb of H1
 #pragma unroll 1
-      for (int kb = 0; kb < 4; ++kb) {
-        wait(&h1_ready[kb], par);
-        ptx::tc_fence_after();
-        TCT_STAMP(tr && tiles_done == 0, 4 + kb);
-#pragma unroll 1
-        for (int mb = 0; mb < 4; ++mb, ++n) {
-          const int slot = n % kSlots;
-          wait(&full[slot], (n / kSlots) & 1);
+        for (int kb = 0; kb < 4; ++kb) {
+          wait(&h1_ready[kb], par);
           ptx::tc_fence_after();
-          if (leader) {
-            const uint32_t a0 = ring + slot * kSlotBytes, b0 = hb + kb * 128 * 16;
+          TCT_STAMP(trl && tiles_done == 0, 4 + kb);
+          const uint32_t b_lo = ptx::smem_desc_lo(hb + kb * 128 * 16, 128);
+#pragma unroll 1
+          for (int mb = 0; mb < 4; ++mb, ++n) {
+            const int slot = n % kSlots;
+            wait(&full[slot], (n / kSlots) & 1);      // (bulk-copy data -> MMA: both the async proxy, no tcgen05 fence)
+            const uint32_t a_lo = ptx::smem_desc_lo(ring + slot * kSlotBytes, 2048);
 #pragma unroll
             for (int kk = 0; kk < 8; ++kk)
-              ptx::mma_ss(tmem + C::kColD2 + mb * NT, ptx::make_desc(ptx::smem_desc_lo(a0 + kk * 4096, 2048), hi_a),
-                          ptx::make_desc(ptx::smem_desc_lo(b0 + kk * 256, 128), hi_b512), id_n, (kb | kk) != 0);
+              ptx::mma_ss(tmem + C::kColD2 + mb * NT, ptx::make_desc(a_lo + kk * (4096 >> 4), hi_a),
+                          ptx::make_desc(b_lo + kk * (256 >> 4), hi_b512), id_n, (kb | kk) != 0);
             ptx::mma_commit(&empty[slot]);
-            if (kb == 3 && mb == 3) ptx::mma_commit(d2_full);
           }
-          __syncwarp();
         }
+        ptx::mma_commit(d2_full);
+        TCT_STAMP(trl && tiles_done == 0, 8);
+        wait(d2_full, par);
       }
-      TCT_STAMP(tr && tiles_done == 0, 8);
-      // ---- layer 3: 128 features, K = 512 in four ring tiles, B = block kb of H2
+      // The epilogue warps do not poll d2_full / d3_full themselves: they sit in a hardware named barrier (5 / 6) and this
+      // warp — idle until the next layer's operand is written anyway — waits for the commit and lets them go.
+      __syncwarp();
+      asm volatile("bar.arrive 5, 544;" ::: "memory");
+      if (leader) {
+        // ---- layer 3: 128 features, K = 512 in four ring tiles, B = block kb of H2
 #pragma unroll 1
-      for (int kb = 0; kb < 4; ++kb, ++n) {
-        const int slot = n % kSlots;
-        wait(&h2_ready[kb], par);
-        wait(&full[slot], (n / kSlots) & 1);
-        ptx::tc_fence_after();
-        if (leader) {
-          const uint32_t a0 = ring + slot * kSlotBytes, b0 = hb + kb * 128 * 16;
+        for (int kb = 0; kb < 4; ++kb, ++n) {
+          const int slot = n % kSlots;
+          wait(&h2_ready[kb], par);
+          ptx::tc_fence_after();
+          wait(&full[slot], (n / kSlots) & 1);
+          const uint32_t a_lo = ptx::smem_desc_lo(ring + slot * kSlotBytes, 2048);
+          const uint32_t b_lo = ptx::smem_desc_lo(hb + kb * 128 * 16, 128);
 #pragma unroll
           for (int kk = 0; kk < 8; ++kk)
-            ptx::mma_ss(tmem + C::kColD3, ptx::make_desc(ptx::smem_desc_lo(a0 + kk * 4096, 2048), hi_a),
-                        ptx::make_desc(ptx::smem_desc_lo(b0 + kk * 256, 128), hi_b512), id_n, (kb | kk) != 0);
+            ptx::mma_ss(tmem + C::kColD3, ptx::make_desc(a_lo + kk * (4096 >> 4), hi_a),
+                        ptx::make_desc(b_lo + kk * (256 >> 4), hi_b512), id_n, (kb | kk) != 0);
           ptx::mma_commit(&empty[slot]);
-          if (kb == 3) ptx::mma_commit(d3_full);
         }
-        __syncwarp();
-      }
-      TCT_STAMP(tr && tiles_done == 0, 9);
-      // ---- layer 4: W4 [16 (read as 128) rows, 128 k], B = H3 (env-major over 128 features)
-      wait(h3_ready, par);
-      ptx::tc_fence_after();
-      if (leader) {
-#pragma unroll
-        for (int kk = 0; kk < 8; ++kk)
-          ptx::mma_ss(tmem + C::kColD4, ptx::make_desc(ptx::smem_desc_lo(w4a + kk * 512, 256), hi_a),
-                      ptx::make_desc(ptx::smem_desc_lo(hb + kk * 256, 128), hi_b128), id_n, kk != 0);
-        ptx::mma_commit(d4_full);
+        ptx::mma_commit(d3_full);
+        TCT_STAMP(trl && tiles_done == 0, 9);
+        wait(d3_full, par);
       }
       __syncwarp();
-      TCT_STAMP(tr && tiles_done == 0, 10);
+      asm volatile("bar.arrive 6, 544;" ::: "memory");
+      if (leader) {
+        // ---- layer 4: W4 [16 (read as 128) rows, 128 k], B = H3 (env-major over 128 features)
+        wait(h3_ready, par);
+        ptx::tc_fence_after();
+        const uint32_t a_lo = ptx::smem_desc_lo(w4a, 256), b_lo = ptx::smem_desc_lo(hb, 128);
+#pragma unroll
+        for (int kk = 0; kk < 8; ++kk)
+          ptx::mma_ss(tmem + C::kColD4, ptx::make_desc(a_lo + kk * (512 >> 4), hi_a),
+                      ptx::make_desc(b_lo + kk * (256 >> 4), hi_b128), id_n, kk != 0);
+        ptx::mma_commit(d4_full);
+        TCT_STAMP(trl && tiles_done == 0, 10);
+      }
+      __syncwarp();
     }
   } else if (warp == kWarpAux) {
     // ===================================================== auxiliary warp: observations -> X operand, then the tile's OU noise
@@ -620,7 +635,7 @@ tct_actor_kernel(const __grid_constant__ Args args, const __grid_constant__ EnvF
       warp_arrive(&h1_ready[g]);
       TCT_STAMP(tr && q == 0 && tiles_done == 0, 12 + g);
       // ---- layer 2 block g -> H2 block g (H1 is dead: every layer-2 MMA has completed)
-      wait(d2_full, par);
+      asm volatile("bar.sync 5, 544;" ::: "memory");      // d2_full has completed (the MMA warp saw it)
       ptx::tc_fence_after();
       TCT_STAMP(tr && q == 0 && g == 0 && tiles_done == 0, 16);
       block_to_h(C::kColD2 + g * NT, bv[1], hdst);
@@ -629,7 +644,7 @@ tct_actor_kernel(const __grid_constant__ Args args, const __grid_constant__ EnvF
       TCT_STAMP(tr && q == 0 && tiles_done == 0, 17 + g);
       // ---- layer 3: group g takes envs g NT/4 .. of the 128 features -> H3 (env-major over 128 features)
       {
-        wait(d3_full, par);
+        asm volatile("bar.sync 6, 544;" ::: "memory");    // d3_full has completed
         ptx::tc_fence_after();
         TCT_STAMP(tr && q == 0 && g == 0 && tiles_done == 0, 21);
         constexpr int kE = NT / 4;                     // envs per group: 16 or 8

@@ -31,7 +31,8 @@ flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
 names = {0: "start", 1: "setup done", 2: "aux: X written", 3: "MMA: x_ready", **{4 + k: f"MMA: h1_ready[{k}]" for k in range(4)},
          8: "MMA: L2 all issued", 9: "MMA: L3 all issued", 10: "MMA: L4 issued", **{12 + g: f"epi: H1 block {g} written" for g in range(4)},
          16: "epi: d2_full seen", **{17 + g: f"epi: H2 block {g} written" for g in range(4)}, 21: "epi: d3_full seen",
-         22: "epi: d4_full seen", 23: "done (actions stored)"}
+         22: "epi: d4_full seen", 23: "done (actions stored)", **{52 + k: f"producer: stage {12 + k} requested" for k in range(8)},
+         **{45 + k: f"MMA: L3 tile {k} in shared memory" for k in range(4)}}
 lib = ois.lib()
 lib.ois_debug_set_tct_max_rows.argtypes = [C.c_longlong]
 for mode in ("warm", "cold"):
@@ -48,6 +49,8 @@ for mode in ("warm", "cold"):
     print(f"--- {mode} L2, n={n}")
     for k in sorted(names, key=lambda k: buf[k]):
         print(f"{(buf[k] - t0) / 1e3:8.2f} us  {names[k]}")
+    if buf[51]:
+        print(f"debug 4: 128 layer-3 MMAs re-issued with all other warps parked: {(buf[51] - buf[50]) / 1e3:.2f} us = {(buf[51] - buf[50]) * 1.965 / 128:.0f} cycles per MMA at 1965 MHz")
     print(f"all CTAs: first start {(buf[60] - t0) / 1e3:.2f} us, last start {(buf[62] - t0) / 1e3:.2f} us, last end {(buf[61] - t0) / 1e3:.2f} us "
           f"(launch span {(buf[61] - buf[60]) / 1e3:.2f} us)")
 for label, max_rows in (("transposed 64-env tiles (mlp_tct.cu)", 1 << 30), ("128-env row tiles (mlp_tc.cu)", 0)):

@@ -197,21 +197,25 @@ tc_gemm_kernel(const __grid_constant__ Group g) {
     const uint32_t b_lbo = P.b_mn ? 128u : (uint32_t)tile_n * 16u, b_sbo = P.b_mn ? (uint32_t)k_stage * 16u : 128u;
     const uint32_t b_step = P.b_mn ? 256u : (uint32_t)tile_n * 32u;
     const uint32_t a_hi = ptx::smem_desc_hi(a_sbo), b_hi = ptx::smem_desc_hi(b_sbo);
-    for (int s = 0; s < nst; ++s) {
-      const int slot = s % kStages;
-      ptx::mbar_wait(&full[slot], (s / kStages) & 1);
-      ptx::tc_fence_after();
-      TCU_STAMP(tr && s < 4, 3 + s);
-      if (leader) {
-        const uint32_t sa = ptx::smem_u32(smem + slot * kStageBytes), sb = sa + kHalfStage;
+    // ONE elected thread runs the whole issue loop: what the issuing thread does between two stages (a warp-wide wait, a
+    // re-convergence, rebuilding every descriptor) is not hidden by the tensor pipe's queue (measured in the actor kernel,
+    // mlp_tct.cu: 85 -> 47 cycles per MMA).  Descriptors of a stage by one addition from its first: the address field is
+    // the low 14 bits of `lo` and the ring lies below 256 KB, so no carry.  (Bulk-copy data -> MMA: both the async proxy.)
+    if (leader) {
+      for (int s = 0; s < nst; ++s) {
+        const int slot = s % kStages;
+        ptx::mbar_wait(&full[slot], (s / kStages) & 1);
+        TCU_STAMP(blockIdx.x == 0 && s < 4, 3 + s);
+        const uint32_t sa = ptx::smem_u32(smem + slot * kStageBytes);
+        const uint32_t a_lo = ptx::smem_desc_lo(sa, a_lbo), b_lo = ptx::smem_desc_lo(sa + kHalfStage, b_lbo);
         for (int kk = 0; kk < (k_stage >> 4); ++kk)
-          ptx::mma_ss(tmem, ptx::make_desc(ptx::smem_desc_lo(sa + kk * a_step, a_lbo), a_hi),
-                      ptx::make_desc(ptx::smem_desc_lo(sb + kk * b_step, b_lbo), b_hi), idesc, (s | kk) != 0);
+          ptx::mma_ss(tmem, ptx::make_desc(a_lo + kk * (a_step >> 4), a_hi), ptx::make_desc(b_lo + kk * (b_step >> 4), b_hi), idesc,
+                      (s | kk) != 0);
         ptx::mma_commit(&empty[slot]);
-        if (s == nst - 1) ptx::mma_commit(d_full);
       }
-      __syncwarp();
+      ptx::mma_commit(d_full);
     }
+    __syncwarp();
   } else {
     // ===================================================== epilogue: two warps per TMEM lane quadrant, each takes half of
     // the tile's 16-column chunks (the epilogue is the serial tail of every launch of the update's dependent chain)

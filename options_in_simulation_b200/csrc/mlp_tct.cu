@@ -402,8 +402,11 @@ tct_actor_kernel(const __grid_constant__ Args args, const __grid_constant__ EnvF
         // ---- layer 2: kb-outer; tile (mb, kb) of W2 from the ring, B = block kb of H1
 #pragma unroll 1
         for (int kb = 0; kb < 4; ++kb) {
-          wait(&h1_ready[kb], par);
-          ptx::tc_fence_after();
+          // block 0 of H1 starts the layer; the other three are written within ~0.2 us of it and are waited for together
+          // (one tcgen05 fence for the rest of the layer: a fence per block costs the tensor pipe a bubble each time)
+          if (kb == 0) wait(&h1_ready[0], par);
+          if (kb == 1) { wait(&h1_ready[1], par); wait(&h1_ready[2], par); wait(&h1_ready[3], par); }
+          if (kb < 2) ptx::tc_fence_after();
           TCT_STAMP(trl && tiles_done == 0, 4 + kb);
           const uint32_t b_lo = ptx::smem_desc_lo(hb + kb * 128 * 16, 128);
 #pragma unroll 1
@@ -429,11 +432,12 @@ tct_actor_kernel(const __grid_constant__ Args args, const __grid_constant__ EnvF
       if (leader) {
         // ---- layer 3: 128 features, K = 512 in four ring tiles, B = block kb of H2
 #pragma unroll 1
+        for (int kb = 0; kb < 4; ++kb) wait(&h2_ready[kb], par);     // (all four blocks of H2 are written within ~0.2 us)
+        ptx::tc_fence_after();
+        for (int kb = 0; kb < 4; ++kb) wait(&full[(n + kb) % kSlots], ((n + kb) / kSlots) & 1);   // all four W3 tiles are in
+#pragma unroll
         for (int kb = 0; kb < 4; ++kb, ++n) {
           const int slot = n % kSlots;
-          wait(&h2_ready[kb], par);
-          ptx::tc_fence_after();
-          wait(&full[slot], (n / kSlots) & 1);
           const uint32_t a_lo = ptx::smem_desc_lo(ring + slot * kSlotBytes, 2048);
           const uint32_t b_lo = ptx::smem_desc_lo(hb + kb * 128 * 16, 128);
 #pragma unroll

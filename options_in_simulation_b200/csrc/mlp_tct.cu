@@ -90,12 +90,15 @@ __device__ __forceinline__ void stamp(int slot) {
 
 // Suspend-time hint of every mbarrier wait below.  Measured (OIS_TCT_DEBUG_MODE=4): layer 3's MMAs take 48 cycles each with
 // the other warps parked and 108 with 16 epilogue warps re-polling d3_full at the default (short) time limit.
-constexpr uint32_t kWaitHintNs = 20000;
+#ifndef OIS_TCT_WAIT_HINT
+#define OIS_TCT_WAIT_HINT 20000
+#endif
+constexpr uint32_t kWaitHintNs = OIS_TCT_WAIT_HINT;
 // mbarrier wait that cannot hang the GPU: a protocol bug traps after ~2^27 failed polls instead of spinning forever.
 // (No printf in the product build: a kernel that contains one pays several microseconds per launch for the print FIFO.)
 __device__ __forceinline__ void wait(uint64_t* bar, uint32_t parity) {
   uint32_t polls = 0;
-  while (!ptx::mbar_try_wait_hint(bar, parity, kWaitHintNs)) {
+  while (!(kWaitHintNs ? ptx::mbar_try_wait_hint(bar, parity, kWaitHintNs) : ptx::mbar_try_wait(bar, parity))) {
     if (++polls > (1u << 24)) {
 #ifdef OIS_TCT_DEBUG
       printf("tct_actor_kernel: barrier at shared 0x%x of CTA %d never completed (warp %d)\n", ptx::smem_u32(bar), blockIdx.x,
@@ -402,11 +405,8 @@ tct_actor_kernel(const __grid_constant__ Args args, const __grid_constant__ EnvF
         // ---- layer 2: kb-outer; tile (mb, kb) of W2 from the ring, B = block kb of H1
 #pragma unroll 1
         for (int kb = 0; kb < 4; ++kb) {
-          // block 0 of H1 starts the layer; the other three are written within ~0.2 us of it and are waited for together
-          // (one tcgen05 fence for the rest of the layer: a fence per block costs the tensor pipe a bubble each time)
-          if (kb == 0) wait(&h1_ready[0], par);
-          if (kb == 1) { wait(&h1_ready[1], par); wait(&h1_ready[2], par); wait(&h1_ready[3], par); }
-          if (kb < 2) ptx::tc_fence_after();
+          wait(&h1_ready[kb], par);
+          ptx::tc_fence_after();
           TCT_STAMP(trl && tiles_done == 0, 4 + kb);
           const uint32_t b_lo = ptx::smem_desc_lo(hb + kb * 128 * 16, 128);
 #pragma unroll 1
@@ -432,12 +432,11 @@ tct_actor_kernel(const __grid_constant__ Args args, const __grid_constant__ EnvF
       if (leader) {
         // ---- layer 3: 128 features, K = 512 in four ring tiles, B = block kb of H2
 #pragma unroll 1
-        for (int kb = 0; kb < 4; ++kb) wait(&h2_ready[kb], par);     // (all four blocks of H2 are written within ~0.2 us)
-        ptx::tc_fence_after();
-        for (int kb = 0; kb < 4; ++kb) wait(&full[(n + kb) % kSlots], ((n + kb) / kSlots) & 1);   // all four W3 tiles are in
-#pragma unroll
         for (int kb = 0; kb < 4; ++kb, ++n) {
           const int slot = n % kSlots;
+          wait(&h2_ready[kb], par);
+          ptx::tc_fence_after();
+          wait(&full[slot], (n / kSlots) & 1);
           const uint32_t a_lo = ptx::smem_desc_lo(ring + slot * kSlotBytes, 2048);
           const uint32_t b_lo = ptx::smem_desc_lo(hb + kb * 128 * 16, 128);
 #pragma unroll

@@ -42,10 +42,12 @@ __device__ __forceinline__ bool mbar_try_wait_hint(uint64_t* bar, uint32_t parit
   return ok != 0;
 }
 // (a protocol bug traps after ~2^28 failed polls instead of hanging the GPU for ever)
+// (with a suspend-time hint: warps that re-poll at the default time limit while MMAs run cost the one-launch policy step
+//  1.7 us of 22 — measured, mlp_tct.cu)
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
   uint32_t polls = 0;
-  while (!mbar_try_wait(bar, parity)) {
-    if (++polls > (1u << 28)) __trap();
+  while (!mbar_try_wait_hint(bar, parity, 20000u)) {
+    if (++polls > (1u << 24)) __trap();
   }
 }
 __device__ __forceinline__ void fence_barrier_init() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }

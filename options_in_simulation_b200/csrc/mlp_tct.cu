@@ -94,12 +94,12 @@ __device__ __forceinline__ void stamp(int slot) {
 #define OIS_TCT_WAIT_HINT 20000
 #endif
 constexpr uint32_t kWaitHintNs = OIS_TCT_WAIT_HINT;
-// mbarrier wait that cannot hang the GPU: a protocol bug traps after ~2^27 failed polls instead of spinning forever.
+// mbarrier wait that cannot hang the GPU: a protocol bug traps after 2^20 failed waits instead of spinning forever.
 // (No printf in the product build: a kernel that contains one pays several microseconds per launch for the print FIFO.)
 __device__ __forceinline__ void wait(uint64_t* bar, uint32_t parity) {
   uint32_t polls = 0;
   while (!(kWaitHintNs ? ptx::mbar_try_wait_hint(bar, parity, kWaitHintNs) : ptx::mbar_try_wait(bar, parity))) {
-    if (++polls > (1u << 24)) {
+    if (++polls > (1u << 20)) {   // >= 1 s of failed waits (each up to the 20 us hint): a protocol bug, not a slow peer
 #ifdef OIS_TCT_DEBUG
       printf("tct_actor_kernel: barrier at shared 0x%x of CTA %d never completed (warp %d)\n", ptx::smem_u32(bar), blockIdx.x,
              threadIdx.x >> 5);

@@ -47,7 +47,7 @@ __device__ __forceinline__ bool mbar_try_wait_hint(uint64_t* bar, uint32_t parit
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
   uint32_t polls = 0;
   while (!mbar_try_wait_hint(bar, parity, 20000u)) {
-    if (++polls > (1u << 24)) __trap();
+    if (++polls > (1u << 20)) __trap();   // >= 1 s of failed waits (each up to the 20 us hint)
   }
 }
 __device__ __forceinline__ void fence_barrier_init() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }

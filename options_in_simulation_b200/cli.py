@@ -56,7 +56,23 @@ SCRIPTS = {
         script="train/train_kamma_4d_nofifo_random_IL.py", variant="KAMMA_g1d_g21", memory=("random", 1_000_000), ou=0.05,
         T_e=4e5, random_timesteps=80, timesteps=600_000, checkpoint_interval=400_000),
 }
-EVAL = {("kamma", "4d"): dict(script="eval/eval_kamma_4d.py", variant="KAMMA_eval", timesteps=50_000, output="tanh")}
+# src/options_sim/cli/eval.py:10-14 (EVAL_MAP); the actors of the 1d / 2d scripts end in a sigmoid
+# (eval/eval_kaddpg_1d.py:29-36), the 4d one in a tanh (eval/eval_kamma_4d.py:33-36)
+EVAL = {
+    ("kaddpg", "1d"): dict(script="eval/eval_kaddpg_1d.py", variant="KA_DDPG_1D_eval", timesteps=50_000, output="sigmoid"),
+    ("kaddpg", "2d"): dict(script="eval/eval_kaddpg_2d.py", variant="KA_DDPG_2D_eval", timesteps=50_000, output="sigmoid"),
+    ("kamma", "4d"): dict(script="eval/eval_kamma_4d.py", variant="KAMMA_eval", timesteps=50_000, output="tanh"),
+}
+# The two scripts no router entry of the reference reaches (they are run by path); ``--script`` selects them here.
+UNROUTED_TRAIN = {
+    "train/train_kamma_controller.py": dict(
+        script="train/train_kamma_controller.py", variant="KAMMA_g11_g21", memory=("random", 1_000_000), ou=0.05,
+        T_e=4e5, random_timesteps=1000, timesteps=400_000, checkpoint_interval=200_000),     # :107,144,167,174-175,180,193
+}
+UNROUTED_EVAL = {
+    "eval/eval_kamma_controller.py": dict(script="eval/eval_kamma_controller.py", variant="KAMMA_eval", timesteps=50_000,
+                                          output="sigmoid"),                                  # :37,64,192
+}
 
 
 def _legacy_parser() -> argparse.ArgumentParser:
@@ -120,11 +136,14 @@ def build(variant: str, spec: dict, legacy, *, num_envs: int, precision: str, de
 def main_train(argv=None) -> int:
     router_argv, legacy_argv = _split(list(sys.argv[1:] if argv is None else argv))
     p = argparse.ArgumentParser(prog="options-sim-train", description="KA-DDPG / KAMMA training on the B200 path")
-    p.add_argument("--algorithm", required=True, choices=["kamma", "kaddpg"])        # src/options_sim/cli/train.py:51-55
-    p.add_argument("--action-dim", required=True, choices=["1d", "2d", "4d"])
-    p.add_argument("--fifo", required=True, choices=["fifo", "nofifo"])
-    p.add_argument("--curriculum", required=True, choices=["random", "gv", "bd"])
-    p.add_argument("--learning-strategy", required=True, choices=["rlil", "il"])
+    by_path = any(x in ("--script", "--list") or x.startswith("--script=") for x in router_argv)
+    p.add_argument("--algorithm", required=not by_path, choices=["kamma", "kaddpg"])  # src/options_sim/cli/train.py:51-55
+    p.add_argument("--action-dim", required=not by_path, choices=["1d", "2d", "4d"])
+    p.add_argument("--fifo", required=not by_path, choices=["fifo", "nofifo"])
+    p.add_argument("--curriculum", required=not by_path, choices=["random", "gv", "bd"])
+    p.add_argument("--learning-strategy", required=not by_path, choices=["rlil", "il"])
+    p.add_argument("--script", default=None, choices=sorted(UNROUTED_TRAIN),
+                   help="a reference script no router key reaches, by its path (instead of the five selectors)")
     p.add_argument("--dry-run", action="store_true", help="print the resolved configuration and exit")
     p.add_argument("--list", action="store_true", help="list the script configurations this build knows")
     # not in the reference: sizing for a GPU
@@ -141,12 +160,18 @@ def main_train(argv=None) -> int:
     if a.list:
         for k, v in SCRIPTS.items():
             print("::".join(k), "->", v["script"], f"({v['variant']})")
+        for k, v in UNROUTED_TRAIN.items():
+            print("--script", k, "->", v["script"], f"({v['variant']})")
         return 0
-    key = (a.algorithm, a.action_dim, a.fifo, a.curriculum, a.learning_strategy)
-    if key not in SCRIPTS:
-        print(f"[ERROR] no B200 configuration for {'::'.join(key)}; known: {[ '::'.join(k) for k in SCRIPTS ]}", file=sys.stderr)
-        return 2                                                                      # train.py's "no script found" exit
-    spec = SCRIPTS[key]
+    if a.script is not None:
+        spec = UNROUTED_TRAIN[a.script]
+    else:
+        key = (a.algorithm, a.action_dim, a.fifo, a.curriculum, a.learning_strategy)
+        if key not in SCRIPTS:
+            print(f"[ERROR] no B200 configuration for {'::'.join(key)}; known: {[ '::'.join(k) for k in SCRIPTS ]}",
+                  file=sys.stderr)
+            return 2                                                                  # train.py's "no script found" exit
+        spec = SCRIPTS[key]
     timesteps = spec["timesteps"] if a.timesteps is None else a.timesteps
     resolved = {"reference_script": spec["script"], "variant": spec["variant"], "memory": list(spec["memory"]),
                 "num_envs": a.num_envs, "timesteps": timesteps, "precision": a.precision, "legacy_args": vars(legacy)}
@@ -178,8 +203,12 @@ def main_train(argv=None) -> int:
 def main_eval(argv=None) -> int:
     router_argv, legacy_argv = _split(list(sys.argv[1:] if argv is None else argv))
     p = argparse.ArgumentParser(prog="options-sim-eval", description="tracking-error-vs-speed eval sweep on the B200 path")
-    p.add_argument("--algorithm", "-a", required=True, choices=["kaddpg", "kamma"])   # src/options_sim/cli/eval.py:47-48
-    p.add_argument("--action-dim", "-d", required=True, choices=["1d", "2d", "4d"])
+    by_path = any(x == "--script" or x.startswith("--script=") for x in router_argv)
+    p.add_argument("--algorithm", "-a", required=not by_path, choices=["kaddpg", "kamma"])   # src/options_sim/cli/eval.py:47-48
+    p.add_argument("--action-dim", "-d", required=not by_path, choices=["1d", "2d", "4d"])
+    p.add_argument("--script", default=None, choices=sorted(UNROUTED_EVAL),
+                   help="a reference eval script no router key reaches, by its path")
+    p.add_argument("--dry-run", action="store_true", help="print the resolved configuration and exit")
     p.add_argument("--checkpoint-path", default=None, help="agent_<step>.pt written by the reference or by this package")
     p.add_argument("--num-envs", type=int, default=8192)
     p.add_argument("--timesteps", type=int, default=None, help="default: two episode lengths past the skipped first one")
@@ -189,11 +218,18 @@ def main_eval(argv=None) -> int:
     p.add_argument("--out", default=None, help="write tracking_error_vs_speed.csv here (speed, tracking_error, episodes)")
     a = p.parse_args(router_argv)
     legacy = _legacy_parser().parse_args(legacy_argv)
-    key = (a.algorithm, a.action_dim)
-    if key not in EVAL:
-        print(f"[ERROR] no B200 eval configuration for {key}; known: {list(EVAL)}", file=sys.stderr)
-        return 2
-    spec = EVAL[key]
+    if a.script is not None:
+        spec = UNROUTED_EVAL[a.script]
+    else:
+        key = (a.algorithm, a.action_dim)
+        if key not in EVAL:
+            print(f"[ERROR] no B200 eval configuration for {key}; known: {list(EVAL)}", file=sys.stderr)
+            return 2
+        spec = EVAL[key]
+    if a.dry_run:
+        print(json.dumps({"reference_script": spec["script"], "variant": spec["variant"], "output": spec["output"],
+                          "num_envs": a.num_envs, "precision": a.precision, "legacy_args": vars(legacy)}))
+        return 0
     from .evaluate import phase_lock, tracking_error_sweep
 
     task, env, mem, agent = build(spec["variant"], {"T_e": 5e4}, legacy, num_envs=a.num_envs, precision=a.precision,

@@ -39,8 +39,14 @@ VARIANTS = {
     "KAMMA_curr1": EnvVariant("KAMMA_curr1", 4, L.BLEND_SWITCH, _D, 1.0, _D, 1.0, 1, L.CMD_GV, 500000.0),
     "KAMMA_curr2": EnvVariant("KAMMA_curr2", 4, L.BLEND_SWITCH, _D, 1.0, _D, 1.0, 1, L.CMD_BD, 500000.0),
     "KAMMA_g1d_g21": EnvVariant("KAMMA_g1d_g21", 4, L.BLEND_SWITCH, _D, 1.0, _K, 1.0, 1, L.CMD_RAND, 500000.0),
-    "KAMMA_g11_g21": EnvVariant("KAMMA_g11_g21", 4, L.BLEND_SWITCH, _K, 1.0, _K, 1.0, 1, L.CMD_RAND, 500000.0),
+    "KAMMA_g11_g21": EnvVariant("KAMMA_g11_g21", 4, L.BLEND_SWITCH, _K, 1.0, _K, 1.0, 1, L.CMD_RAND, 100000.0),   # KAMMA_g11_g21.py:179
     "KAMMA_eval": EnvVariant("KAMMA_eval", 4, L.BLEND_SWITCH, _K, 0.0, _K, 0.0, 1, L.CMD_EVAL, 50000.0, eval_sums=True),
+    # eval twins of the 1d / 2d envs: gamma frozen at 0 (KA_DDPG_1D_eval.py:193), eval ramp before RandSampling
+    # (:543-548; KA_DDPG_2D_eval.py:544-549), Smoothness / Tracking error / Desired velocity sums (:224-226,685-691,857)
+    "KA_DDPG_1D_eval": EnvVariant("KA_DDPG_1D_eval", 1, L.BLEND_LINEAR, _K, 0.0, _K, 0.0, 0, L.CMD_EVAL, 50000.0,
+                                  eval_sums=True, relabel=L.RELABEL_NONE),
+    "KA_DDPG_2D_eval": EnvVariant("KA_DDPG_2D_eval", 2, L.BLEND_LINEAR, _K, 0.0, _K, 0.0, 0, L.CMD_EVAL, 50000.0,
+                                  eval_sums=True, relabel=L.RELABEL_NONE),
 }
 
 # The parts of the reference's TASK_CFG the hot path reads (KAMMA_medium.py:29-128).  Scripts deep-copy

@@ -67,8 +67,12 @@ VARIANTS = {
     "KAMMA_curr1": EnvVariant("KAMMA_curr1", 4, "switch", "decay", "decay", "post", "gv", 500000.0),
     "KAMMA_curr2": EnvVariant("KAMMA_curr2", 4, "switch", "decay", "decay", "post", "bd", 500000.0),
     "KAMMA_g1d_g21": EnvVariant("KAMMA_g1d_g21", 4, "switch", "decay", "one", "post", "rand", 500000.0),
-    "KAMMA_g11_g21": EnvVariant("KAMMA_g11_g21", 4, "switch", "one", "one", "post", "rand", 500000.0),
+    "KAMMA_g11_g21": EnvVariant("KAMMA_g11_g21", 4, "switch", "one", "one", "post", "rand", 100000.0),   # KAMMA_g11_g21.py:179
     "KAMMA_eval": EnvVariant("KAMMA_eval", 4, "switch", "zero", "zero", "post", "eval", 50000.0, eval_sums=True),
+    # eval twins of the 1d / 2d envs (KA_DDPG_1D_eval.py:57,180,193,224-226,543-548; KA_DDPG_2D_eval.py:57,180,193,544-549):
+    # gamma frozen at 0, the eval ramp wins over RandSampling, the three eval sums
+    "KA_DDPG_1D_eval": EnvVariant("KA_DDPG_1D_eval", 1, "linear", "zero", "zero", "pre", "eval", 50000.0, eval_sums=True),
+    "KA_DDPG_2D_eval": EnvVariant("KA_DDPG_2D_eval", 2, "linear", "zero", "zero", "pre", "eval", 50000.0, eval_sums=True),
 }
 
 

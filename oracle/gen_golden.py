@@ -211,6 +211,14 @@ ENV_CASES = [
     ("kamma_g1d_g21_nophys", "KAMMA_g1d_g21", 32, 3, False, None),
     ("kamma_curr2_n1_a", "KAMMA_curr2", 1, 6, False, None),        # appended: the seed of a case is 1234 + its index
     ("kamma_curr2_n1_b", "KAMMA_curr2", 1, 6, True, None),
+    ("kaddpg_1d_eval_nophys", "KA_DDPG_1D_eval", 64, 4, False, None),   # eval/eval_kaddpg_1d.py
+    ("kaddpg_1d_eval_phys", "KA_DDPG_1D_eval", 32, 3, True, None),
+    ("kaddpg_2d_eval_nophys", "KA_DDPG_2D_eval", 64, 4, False, None),   # eval/eval_kaddpg_2d.py
+    ("kaddpg_2d_eval_phys", "KA_DDPG_2D_eval", 32, 3, True, None),
+    ("kamma_nophys", "KAMMA", 64, 4, False, None),                      # train/train_kamma_4d_fifo_random_RLIL.py
+    ("kamma_g11_g21_nophys", "KAMMA_g11_g21", 32, 3, False, None),      # train/train_kamma_controller.py
+    ("kamma_g11_g21_phys", "KAMMA_g11_g21", 32, 3, True, None),
+    ("kaddpg_4d_phys", "KA_DDPG_4D", 64, 3, True, None),
 ]
 
 

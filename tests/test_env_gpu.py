@@ -73,7 +73,8 @@ def test_env_kernel_matches_reference_golden(fname):
 
 @pytest.mark.parametrize("name,n", [("KAMMA_medium", 4096), ("KA_DDPG_2D", 4096), ("KA_DDPG_1D", 64),
                                      ("KAMMA_eval", 8192), ("KAMMA_curr1", 16384), ("KAMMA_curr2", 4096), ("KAMMA_medium", 4097),
-                                     ("KAMMA_medium", 1)])
+                                     ("KAMMA_medium", 1), ("KA_DDPG_1D_eval", 8192), ("KA_DDPG_2D_eval", 4096),
+                                     ("KAMMA_g11_g21", 4096), ("KAMMA", 4096), ("KA_DDPG_4D", 4096)])
 def test_env_kernel_matches_oracle_at_bench_sizes(name, n):
     """Seeded synthetic state, 6 closed-loop steps, physics on: CUDA fp32 vs numpy oracle
     (float64 dynamics).  Ragged N (4097, 1) exercises the grid tail."""
@@ -85,7 +86,7 @@ def test_env_kernel_matches_oracle_at_bench_sizes(name, n):
     variant = VARIANTS[name]
     rng = np.random.default_rng(1234 + n)
     s0 = synth_state(variant, n, rng, physics=True)
-    fg = 0.5 if name.startswith("KA_DDPG") and variant.act_dim < 4 else None
+    fg = 0.5 if name in ("KA_DDPG_1D", "KA_DDPG_2D") else None     # the *_eval twins keep their own frozen gamma = 0
     oracle = EnvOracle(variant, s0.copy(), EnvParams(physics=True))
     if fg is not None:
         oracle.force_gamma = F(fg)

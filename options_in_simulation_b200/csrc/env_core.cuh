@@ -77,8 +77,13 @@ __device__ __forceinline__ float2 mul2(float2 a, float2 b) { return __fmul2_rn(a
 __device__ __forceinline__ float2 add2(float2 a, float2 b) { return __fadd2_rn(a, b); }
 __device__ __forceinline__ float2 bc(float s) { return make_float2(s, s); }
 __device__ __forceinline__ float2 neg2(float2 a) { return make_float2(-a.x, -a.y); }
+#ifdef OIS_DIAG_NOMUFU   // timing diagnostic only (wrong results): what the MUFU pipe costs the sub-steps
+__device__ __forceinline__ float mufu_rcp(float x) { return fmaf(x, 0.001f, 0.5f); }
+__device__ __forceinline__ float mufu_rsq(float x) { return fmaf(x, 0.001f, 0.25f); }
+#else
 __device__ __forceinline__ float mufu_rcp(float x) { float r; asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
 __device__ __forceinline__ float mufu_rsq(float x) { float r; asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
+#endif
 // 1/x for two lanes: the MUFU.RCP result (<= 1 ulp) as is; OIS_ENV_RCP_NEWTON adds one Newton step r <- r + r (1 - x r)
 #ifndef OIS_ENV_RCP_NEWTON
 #define OIS_ENV_RCP_NEWTON 0
@@ -100,13 +105,17 @@ __device__ __forceinline__ float rcp1(float x) {
 #endif
 }
 
-struct SideOut { float2 al, be, k, g, phi, kl; };
+struct SideOut { float2 al, be, k, g, phi; };
 
 // one SIDE of the vehicle (lateral position y): its front (x = +a) and rear (x = -a) wheels in the two lanes.  Pairing by
 // side keeps every packed operand in the registers it already lives in — wheel speeds and torques are stored
 // (fl, rl, fr, rr), so (fl, rl) and (fr, rr) are adjacent — where pairing by axle cost a dozen register moves per sub-step.
-__device__ __forceinline__ SideOut side(float2 w, float2 tau, float nu /* -u of this side */, float2 l, float2 l2e /* l^2 + eps^2 */,
-                                        float2 R2, float2 RR2, float2 Iwh2, float2 nc2, float2 mu2) {
+// The sub-steps' time follows their count of FMA-pipe instructions, not the MUFU count and not the issue slots
+// (profiles/r02p_variant_probe.txt, r02p_pair_probe.txt), so products are shared where the algebra allows:
+// g = (Iw/h + c) k / E is be (Iw/h + c) / R, and sum k_i l_i is taken per axle after the sides are added (skid_steps).
+__device__ __forceinline__ SideOut side(float2 w, float2 tau, float nu /* -u of this side */, float2 l2e /* l^2 + eps^2 */,
+                                        float2 R2, float2 RR2, float2 Iwh2, float2 IwhR2 /* (Iw/h + c) / R */, float2 nc2,
+                                        float2 mu2) {
   SideOut o;
   const float2 sx = fma2(R2, w, bc(nu));                   // R w - u
   const float2 n2 = fma2(sx, sx, l2e);
@@ -115,23 +124,23 @@ __device__ __forceinline__ SideOut side(float2 w, float2 tau, float nu /* -u of 
   const float2 Rk = mul2(R2, k);
   o.al = mul2(fma2(neg2(Rk), sx, fma2(nc2, w, tau)), inv);  // (tau - c w - R k sx) / E
   o.be = mul2(Rk, inv);
-  o.g = mul2(mul2(k, Iwh2), inv);
+  o.g = mul2(o.be, IwhR2);
   o.phi = mul2(k, fma2(R2, o.al, sx));
-  o.kl = mul2(k, l);
   o.k = k;
   return o;
 }
 
-// What the sub-steps need that depends on neither the torques nor the loop: three IEEE divisions and sincos(yaw).  Split
+// What the sub-steps need that depends on neither the torques nor the loop: four IEEE divisions and sincos(yaw).  Split
 // off so that a caller that has the state before it has the torques (the one-launch policy step, mlp_tct.cu) can evaluate
 // it while it waits; the arithmetic is the same either way.
-struct SkidPre { float m_h, J_h, Iw_h, sn, cs; };
+struct SkidPre { float m_h, J_h, Iw_h, IwR_h, sn, cs; };
 __device__ __forceinline__ SkidPre skid_prepare(float yaw, const OisEnvParams& p) {
   SkidPre q;
   const float h = p.sim_dt;
   q.m_h = p.mass / h;
   q.J_h = p.yaw_inertia / h;
   q.Iw_h = p.wheel_inertia / h + p.wheel_damping;
+  q.IwR_h = q.Iw_h / p.wheel_radius;
   sincosf(yaw, &q.sn, &q.cs);
   return q;
 }
@@ -143,19 +152,20 @@ __device__ __forceinline__ void skid_steps(Skid& s, const float tau[4], const Oi
   const float m_h = pre.m_h, J_h = pre.J_h, Iw_h = pre.Iw_h;
   const float eps2 = p.slip_eps * p.slip_eps, aa = a * a, bb = b * b;
   const float wmax = p.wheel_speed_max;
-  const float2 R2 = bc(R), RR2 = bc(R * R), Iwh2 = bc(Iw_h), nc2 = bc(-c), mu2 = bc(p.mu_n);
+  const float2 R2 = bc(R), RR2 = bc(R * R), Iwh2 = bc(Iw_h), IwhR2 = bc(pre.IwR_h), nc2 = bc(-c), mu2 = bc(p.mu_n);
   float2 wL = make_float2(s.w[0], s.w[1]), wR = make_float2(s.w[2], s.w[3]);   // left / right side, (front, rear)
   const float2 tL = make_float2(tau[0], tau[1]), tR = make_float2(tau[2], tau[3]);
   float sn = pre.sn, cs = pre.cs;
+  float sx_w = 0.f, sy_w = 0.f;
 #pragma unroll 1
   for (int it = 0; it < p.decimation; ++it) {
     const float vx = s.vx, vy = s.vy, r = s.r;
     const float2 l = make_float2(fmaf(r, a, vy), fmaf(-r, a, vy));     // lateral contact speed: front, rear
     const float2 l2e = fma2(l, l, bc(eps2));
-    const SideOut Lf = side(wL, tL, fmaf(r, b, -vx), l, l2e, R2, RR2, Iwh2, nc2, mu2);     // y = +b: u = vx - r b
-    const SideOut Rt = side(wR, tR, fmaf(-r, b, -vx), l, l2e, R2, RR2, Iwh2, nc2, mu2);    // y = -b: u = vx + r b
+    const SideOut Lf = side(wL, tL, fmaf(r, b, -vx), l2e, R2, RR2, Iwh2, IwhR2, nc2, mu2);     // y = +b: u = vx - r b
+    const SideOut Rt = side(wR, tR, fmaf(-r, b, -vx), l2e, R2, RR2, Iwh2, IwhR2, nc2, mu2);    // y = -b: u = vx + r b
     const float2 Sg = add2(Lf.g, Rt.g), Dg = add2(Lf.g, neg2(Rt.g)), Sk = add2(Lf.k, Rt.k);
-    const float2 Sph = add2(Lf.phi, Rt.phi), Dph = add2(Lf.phi, neg2(Rt.phi)), Skl = add2(Lf.kl, Rt.kl);
+    const float2 Sph = add2(Lf.phi, Rt.phi), Dph = add2(Lf.phi, neg2(Rt.phi)), Skl = mul2(Sk, l);   // per axle: (k_l + k_r) l
     const float gs = Sg.x + Sg.y, ks = Sk.x + Sk.y;
     const float A00 = m_h + gs, A11 = m_h + ks;
     const float A22 = fmaf(bb, gs, fmaf(aa, ks, J_h));
@@ -178,17 +188,26 @@ __device__ __forceinline__ void skid_steps(Skid& s, const float tau[4], const Oi
     wR = add2(wR, fma2(Rt.be, bc(fmaf(dr, b, dvx)), Rt.al));
     wL = make_float2(clipf(wL.x, -wmax, wmax), clipf(wL.y, -wmax, wmax));
     wR = make_float2(clipf(wR.x, -wmax, wmax), clipf(wR.y, -wmax, wmax));
-    // heading: rotate (cos, sin) by d = h*r' with a Taylor pair (|d| <= 0.01 * R wmax / b = 0.3)
+#ifdef OIS_DIAG_NOHEADING   // timing diagnostic only (wrong results)
+    s.yaw += h * s.r;
+    sx_w += s.vx;
+    continue;
+#endif
+    // heading: rotate (cos, sin) by d = h*r' with a Taylor pair.  |d| <= 0.01 * R wmax / b = 0.3: the first dropped terms,
+    // d^9 / 9! of the sine and d^8 / 8! of the cosine, are below 6e-11 and 2e-9 there (fp32 ulp of 1: 6e-8)
     const float d = h * s.r, d2 = d * d;
-    const float sd = d * (1.f + d2 * (-1.f / 6.f + d2 * (1.f / 120.f + d2 * (-1.f / 5040.f + d2 * (1.f / 362880.f)))));
-    const float cd = 1.f + d2 * (-0.5f + d2 * (1.f / 24.f + d2 * (-1.f / 720.f + d2 * (1.f / 40320.f))));
+    const float sd = d * (1.f + d2 * (-1.f / 6.f + d2 * (1.f / 120.f + d2 * (-1.f / 5040.f))));
+    const float cd = 1.f + d2 * (-0.5f + d2 * (1.f / 24.f + d2 * (-1.f / 720.f)));
     const float cn = cs * cd - sn * sd;
     sn = sn * cd + cs * sd;
     cs = cn;
     s.yaw += d;
-    s.px += h * (s.vx * cs - s.vy * sn);
-    s.py += h * (s.vx * sn + s.vy * cs);
+    // world-frame displacement / h, summed over the sub-steps and scaled once after the loop
+    sx_w = fmaf(s.vx, cs, fmaf(-s.vy, sn, sx_w));
+    sy_w = fmaf(s.vx, sn, fmaf(s.vy, cs, sy_w));
   }
+  s.px = fmaf(h, sx_w, s.px);
+  s.py = fmaf(h, sy_w, s.py);
   s.w[0] = wL.x; s.w[1] = wL.y; s.w[2] = wR.x; s.w[3] = wR.y;
 }
 __device__ __forceinline__ void skid_steps(Skid& s, const float tau[4], const OisEnvParams& p) {

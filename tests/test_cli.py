@@ -101,3 +101,19 @@ def test_eval_run_of_the_kaddpg_scripts(capsys, dim, variant):
     assert rc == 0 and d["reference_script"] == f"eval/eval_kaddpg_{dim}.py" and len(d["curve"]) == 5
     assert sum(r[2] for r in d["curve"]) >= 495
     assert all(1.0 <= r[0] <= 2.0 and r[1] >= 0.0 for r in d["curve"] if r[2] > 0)
+
+
+@pytest.mark.gpu
+def test_unrouted_scripts_run(capsys):
+    """train/train_kamma_controller.py (KAMMA_g11_g21: the pure controller; random_timesteps = learning_starts = 1000, so a short
+    run records transitions and makes no update) and eval/eval_kamma_controller.py (KAMMA_eval, sigmoid actor) by path."""
+    from options_in_simulation_b200 import cli
+
+    rc = cli.main(["train", "--script", "train/train_kamma_controller.py", "--num-envs", "128", "--timesteps", "60",
+                   "--write-interval", "0", "--checkpoint-interval", "0", "--", "--seed", "3"])
+    d = json.loads([l for l in capsys.readouterr().out.splitlines() if l.startswith("{")][-1])
+    assert rc == 0 and d["variant"] == "KAMMA_g11_g21" and d["updates"] == 0 and d["transitions"] == 60 * 128
+    rc = cli.main(["eval", "--script", "eval/eval_kamma_controller.py", "--num-envs", "495", "--bins", "5"])
+    d = json.loads([l for l in capsys.readouterr().out.splitlines() if l.startswith("{")][-1])
+    assert rc == 0 and d["reference_script"] == "eval/eval_kamma_controller.py" and len(d["curve"]) == 5
+    assert sum(r[2] for r in d["curve"]) >= 495

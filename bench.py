@@ -134,7 +134,9 @@ def ncu_traffic():
 def workload_config(wl, n, world_size):
     """The `config` object of the JSON line: identical in the GPU arm and in the reference arm."""
     return {"workload": wl["name"], "envs_per_gpu": n, "variant": wl["variant"], "act_dim": wl["act_dim"],
-            "replay": "fused append, rank-local shard", "rng": "in-kernel Philox (GPU arm) / numpy PCG64 (CPU arm)",
+            "replay": "fused append, rank-local shard",
+            "outputs": "obs, clamped obs, rew, reset, wheel_torqs, state, replay row; the task attributes nothing on the path reads "
+                       "(pre-clip torques, guiding_reward, timeout_buf) are computed but not stored (GPU arm)", "rng": "in-kernel Philox (GPU arm) / numpy PCG64 (CPU arm)",
             "l2": "GPU arm: flushed between timed steps (256 MiB memset outside the event brackets); CPU arm: n/a",
             "parallelism": f"env/replay shards x{world_size}; rollout: no data-path collective; update: critic + actor "
                            "gradient all-reduce (ddpg.py:409-410,431-432)"}
@@ -331,6 +333,7 @@ class World:
         torch.manual_seed(seed if model_seed is None else model_seed)
         cfg = script_cfg(n, seed=seed, sim_device=str(device))
         self.task = ois.TorqueDistributionTask(sim_config=cfg, variant=wl["variant"], seed=seed)
+        self.task.intermediate_outputs = False     # torques / guiding_reward / timeout_buf: computed, not stored (config.outputs)
         self.env = ois.wrap_env(self.task)
         dev = str(device)
         osp, asp = self.task.observation_space, self.task.action_space

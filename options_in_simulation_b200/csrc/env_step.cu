@@ -363,7 +363,7 @@ env_step_kernel(const __grid_constant__ OisEnvParams p, const __grid_constant__ 
     st_stream4(st.pose_vx + 4 * i, make_float4(s.px, s.py, s.yaw, s.vx));
     st_stream4(st.twist_prev + 4 * i, make_float4(s.vy, s.r, prev_lin, prev_ang));
     st_stream4(st.wheel_speed + 4 * i, make_float4(s.w[0], s.w[1], s.w[2], s.w[3]));
-    st_stream4(st.commands + 4 * i, cmd);
+    if (reset) st_stream4(st.commands + 4 * i, cmd);   // only reset_idx changes the commands
     st_stream4(st.sums_a + 4 * i, sa);
     st_stream4(st.sums_b + 4 * i, sb);
     __stcs(st.sim_steps + i, sim);

@@ -96,6 +96,10 @@ class TorqueDistributionTask:
         self.stats_log = None
         self._stats_row = 0
         self._io, self._io_key, self._io_static = None, None, None      # cached OisEnvIO block (pre_physics_step)
+        # ``torques`` (pre-clip), ``guiding_reward`` and ``timeout_buf`` are attributes of the reference task that nothing on
+        # the rollout path reads (the trainer takes ``wheel_torqs``; the wrapper reports truncated = 0).  True keeps them
+        # refreshed every step like the reference; False leaves them stale and saves their 28 B of writes per env-step.
+        self.intermediate_outputs = True
         self._replay_key, self._replay_rows = None, None
         self.extras: dict = {}
         self._supplied_mask = None
@@ -316,13 +320,15 @@ class TorqueDistributionTask:
         # critical path: at 4096 envs the GPU step is ~30 us, so every microsecond of Python here is visible)
         bufs = (self.obs_buf, self.rew_buf, self.reset_buf, self.wheel_torqs, self.timeout_buf, self.torques,
                 self.guiding_reward)
-        key = tuple(map(id, bufs))
+        key = tuple(map(id, bufs)) + (bool(self.intermediate_outputs),)
         if self._io_key != key:
             io = L.EnvIO()
             io.philox_seed = self._seed
             io.obs, io.rew, io.reset = self.obs_buf.data_ptr(), self.rew_buf.data_ptr(), self.reset_buf.data_ptr()
-            io.wheel_torqs, io.timeout = self.wheel_torqs.data_ptr(), self.timeout_buf.data_ptr()
-            io.torques, io.guiding = self.torques.data_ptr(), self.guiding_reward.data_ptr()
+            io.wheel_torqs = self.wheel_torqs.data_ptr()
+            if self.intermediate_outputs:
+                io.timeout = self.timeout_buf.data_ptr()
+                io.torques, io.guiding = self.torques.data_ptr(), self.guiding_reward.data_ptr()
             if self.variant.eval_sums:
                 io.any_reset_flags = self._any_reset_flags.data_ptr()
             self._io, self._io_key = io, key

@@ -270,3 +270,32 @@ def test_rltask_surface():
     assert len(oc) == 26 and "env0_v_delta" in oc
     with pytest.raises(ois.OisError):
         ois.RandomMemory(memory_size=4, num_envs=2, device="cpu")   # no CPU path
+
+
+def test_intermediate_outputs_off_changes_nothing_else():
+    """task.intermediate_outputs = False (bench.py, throughput runs) skips the stores of the three reference attributes nothing
+    on the path reads (pre-clip torques, guiding_reward, timeout_buf); everything else — observations, rewards, resets,
+    wheel_torqs, the whole env state, the commands of non-reset envs — is bit-identical, with the in-kernel Philox streams."""
+    import torch
+
+    n = 20_000
+    tasks = [_task("KAMMA_medium", n, seed=11) for _ in range(2)]
+    tasks[1].intermediate_outputs = False
+    for t in tasks:
+        t.post_reset()
+    g = torch.Generator(device="cuda").manual_seed(5)
+    resets = 0
+    for step in range(104):     # past the first episode end (99 steps): the reset path stores new commands
+        act = torch.rand(n, 4, device="cuda", generator=g)
+        outs = [t.step(act.clone()) for t in tasks]
+        if step % 13 == 0 or step >= 97:
+            for a, b in zip(outs[0][:3], outs[1][:3]):
+                assert torch.equal(a, b)
+            assert torch.equal(tasks[0].wheel_torqs, tasks[1].wheel_torqs)
+            sa, sb = tasks[0].dump_state(), tasks[1].dump_state()
+            for k in sa:
+                assert np.array_equal(sa[k], sb[k]), (k, step)
+            resets += int(outs[0][2].sum())
+    assert resets > 0
+    assert float(tasks[0].torques.abs().sum()) > 0 and float(tasks[1].torques.abs().sum()) == 0
+    assert float(tasks[1].guiding_reward.abs().sum()) == 0 and int(tasks[1].timeout_buf.sum()) == 0

@@ -34,6 +34,8 @@ CASES = [
     # tag, env module, trainer module, N, timesteps, batch, memory steps, random_timesteps, learning_starts, ou scale, T_e
     ("kamma_medium", "KAMMA_medium", "sequential", 16, 10, 32, 8, 2, 3, 0.05, 5e5),
     ("kaddpg_2d", "KA_DDPG_2D", "sequential_KA", 16, 8, 32, 16, 1, 2, 0.3, 7e5),
+    ("kaddpg_1d", "KA_DDPG_1D", "sequential_KA", 64, 8, 32, 16, 1, 2, 0.5, 7e5),     # BASELINE.json configs[0]: KA-DDPG-1d, N = 64
+    ("kaddpg_4d", "KA_DDPG_4D", "sequential", 16, 8, 32, 16, 1, 2, 0.15, 7e5),       # linear blend with the decaying gamma + relabel
 ]
 
 
@@ -206,7 +208,10 @@ def run_case(idx, tag, env_mod, trainer_mod, n, T, batch, mem_steps, random_ts, 
 def main():
     os.makedirs(GOLDEN, exist_ok=True)
     print("trainer cases (reference my_trainers/* over reference env + agent vs oracle/trainer_oracle.py):")
+    only = set(sys.argv[1:])            # optional: case tags to (re)generate; default all (the seed of a case is its index)
     for i, case in enumerate(CASES):
+        if only and case[0] not in only:
+            continue
         np.savez_compressed(os.path.join(GOLDEN, f"trainer_{case[0]}.npz"), **run_case(i, *case))
 
 
